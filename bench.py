@@ -1,0 +1,257 @@
+#!/usr/bin/env python
+"""Headline benchmark: LLaMA-3 8B bf16 decode tokens/s (KV cache, 2k-token prompt) at TP = --gpus.
+
+Contract (see the task statement): ``python bench.py --gpus N --steps K --warmup W`` prints ONE JSON line
+from rank 0.  A *step* is one decode step (one new token for every row of the batch) of the full model:
+embedding → 32 layers → final norm → LM head → greedy selection → sequence bookkeeping, i.e. exactly the
+body of the generate loop, replayed from its CUDA graph.  Weights are random-init bf16 of the named
+architecture, prompts are synthetic token ids (no network, no checkpoints).
+
+* ``value``           total generated tokens per second over all GPUs (device time, CUDA events, max over ranks)
+* ``e2e``             the same metric through the public API (`LLaMA.stream(...).step(feed)`): every step copies
+                      that step's input tokens from pinned host memory and reads the new tokens back.
+* ``prefill``         prompt tokens per second of the 2k-token prefill (same engine), reported alongside.
+* ``gpu_launches``    kernels of libjllama_b200.so launched inside the timed region (graph nodes x replays).
+
+The 15 GB of weights streamed per step are far larger than the 126 MB L2, so no explicit L2 flush is needed
+between timed iterations (stated in ``config.l2``).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+BASELINE_PUBLISHED = None      # the reference publishes no performance numbers
+
+
+def reference_arm(args) -> None:
+    """The reference (JAX/Flax) cannot be imported on this image: jax, flax and fire are not installed and
+    transformers 5.x ships no Flax generation mixin ("Reference arm")."""
+    why = "jax/flax not installed in this image (no index access); transformers 5.5 has no Flax classes"
+    try:
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline", "_ref"))
+        import jax_llama  # noqa: F401
+        why = "reference imported unexpectedly; no runner implemented for it"
+    except Exception as e:  # noqa: BLE001
+        why = f"reference import fails: {type(e).__name__}: {str(e)[:120]}"
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU during the timed region (NVML)."""
+
+    def __init__(self, index: int, period: float = 0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.error = None
+
+    def run(self) -> None:
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+                getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake_slowdown",
+            }
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                mask = get_reasons(h)
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+                time.sleep(self.period)
+        except Exception as e:  # noqa: BLE001
+            self.error = f"{type(e).__name__}: {e}"
+
+    def stop(self) -> dict:
+        self._stop_evt.set()
+        self.join(timeout=2)
+        out = {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+               "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+        if self.error:
+            out["error"] = self.error
+        return out
+
+
+class SyntheticTokenizer:
+    """Stands in for a tokenizer file: only the ids the generation front-end needs."""
+
+    def __init__(self, vocab: int, bos: int, eos: int):
+        self.n_words, self.bos_id, self.eos_id, self.pad_id = vocab, bos, eos, -1
+
+    def __len__(self) -> int:
+        return self.n_words
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=128)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="llama3-8b")
+    ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--prompt-len", type=int, default=2048)
+    ap.add_argument("--prefill-reps", type=int, default=3)
+    ap.add_argument("--no-graph", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import torch
+    import torch.distributed as dist
+
+    from jax_llama_b200 import LLaMA, LLaMAForCausalLM, preset
+    from jax_llama_b200.models.engine import B200Engine
+    from jax_llama_b200.ops import _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    cfg = preset(args.model)
+    B, P = args.batch, args.prompt_len
+    max_len = P + 1 + args.warmup + args.steps + 8
+    cfg.max_sequence_length = max(cfg.max_sequence_length, (max_len + 1) // 2)
+    kw = {}
+    if world > 1:
+        kw = dict(tp=world, rank=rank)
+    eng = B200Engine.random_init(cfg, dev, seed=0, use_cuda_graph=not args.no_graph, **kw)
+    model = LLaMAForCausalLM(cfg, _do_init=False)
+    params = {"engine": eng}                              # handle understood by LLaMAForCausalLM._engine_for
+    model._engines[id(params)] = eng
+    tok = SyntheticTokenizer(cfg.vocab_size, cfg.bos_token_id, -1)      # eos never fires: fixed-length runs
+    llama = LLaMA(params, model, tok)
+
+    g = torch.Generator().manual_seed(1234)
+    prompt = torch.randint(0, cfg.vocab_size, (B, P), generator=g).pin_memory()
+    mask = torch.ones(B, P, dtype=torch.int32).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------------------------------------------------------- prefill (reported alongside)
+    ids_dev = prompt.to(dev, non_blocking=True)
+    st = eng._decode_state(B, max_len)
+    prefill_ms = []
+    for i in range(1 + args.prefill_reps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        eng.prepare(st, ids_dev, None, 0)
+        e1.record()
+        torch.cuda.synchronize()
+        if i > 0:
+            prefill_ms.append(max_over_ranks(e0.elapsed_time(e1)))
+    prefill_best = min(prefill_ms)
+
+    # ---------------------------------------------------------------- device-timed decode steps
+    stream = llama.stream(prompt, mask, max_gen_len=max_len - P, temperature=0.0, top_p=1.0)
+    for _ in range(args.warmup):
+        stream.graph.replay() if stream.graph is not None else eng._decode_step(
+            stream.st, stream.cache, stream.sampling, stream.eos, stream.pad)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    launches0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        if stream.graph is not None:
+            stream.graph.replay()
+        else:
+            eng._decode_step(stream.st, stream.cache, stream.sampling, stream.eos, stream.pad)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    ms_per_step = ms_total / args.steps
+    launches_eager = _lib.launch_count() - launches0
+    per_step_launches = eng.launches_per_step(stream.st) if hasattr(eng, "launches_per_step") else None
+    gpu_launches = launches_eager if stream.graph is None else (per_step_launches or 0) * args.steps
+
+    # ---------------------------------------------------------------- end to end through the public API
+    stream2 = llama.stream(prompt, mask, max_gen_len=max_len - P, temperature=0.0, top_p=1.0)
+    feed = torch.empty(B, dtype=torch.int32).pin_memory()
+    feed.copy_(stream2.last_tokens())
+    for _ in range(args.warmup):
+        feed.copy_(stream2.step(feed))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = stream2.step(feed)          # H2D of this step's tokens (pinned) + D2H of the new tokens + sync
+        feed.copy_(out)
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+
+    if rank == 0:
+        value = B * args.steps / (ms_total / 1e3)
+        weight_bytes = sum(t.numel() * 2 for l in eng.layers for t in (l.wqkv, l.wo, l.w13, l.w2)) + eng.lm_head.numel() * 2
+        peaks = {}
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except OSError:
+            pass
+        hbm = peaks.get("hbm_gbs", 6650.0)
+        line = {
+            "metric": "decode_tokens_per_sec", "value": round(value, 2), "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": BASELINE_PUBLISHED, "dtype": "bf16",
+            "data": "synthetic token ids, random-init weights",
+            "config": {"model": args.model, "global_batch": B, "seq_len": P, "parallelism": f"tp{world}",
+                       "decode_context": f"{P}+{args.warmup}..{P + args.warmup + args.steps}",
+                       "l2": "no flush needed: per-step weight stream (%.1f GB/rank) >> 126 MB L2" % (weight_bytes / 1e9),
+                       "cuda_graph": stream.graph is not None},
+            "p50_ms_per_token": round(ms_per_step, 4),
+            "hbm_roofline_frac_of_measured": round((weight_bytes / (ms_per_step / 1e3)) / (hbm * 1e9), 4),
+            "prefill": {"tokens_per_sec": round(B * P / (prefill_best / 1e3), 1), "ms": round(prefill_best, 3),
+                        "prompt_len": P, "includes": "embedding..lm_head(last token) of the prompt"},
+            "e2e": {"value": round(B * args.steps / (e2e_ms / 1e3), 2), "unit": "tokens/s",
+                    "h2d_bytes_per_step": stream2.h2d_bytes, "d2h_bytes_per_step": stream2.d2h_bytes,
+                    "api": "LLaMA.stream(...).step(feed)"},
+            "gpu_launches": int(gpu_launches), "clocks": clocks,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

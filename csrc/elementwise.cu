@@ -1,0 +1,227 @@
+// Memory-bound building blocks: embedding gather, RMSNorm (+ fused residual add), RoPE fused with the
+// KV-cache append, stand-alone SwiGLU.  All bf16 in/out, fp32 math, 16-byte vector accesses.
+//
+// Reference ops: /root/reference/jax_llama/model.py:42-48 (RMSNorm), :58-92 (interleaved RoPE),
+// :177-199 (cache append), :338 (SwiGLU), :611-617,638 (embedding).
+#include "common.cuh"
+#include "jllama_b200.h"
+
+namespace jl {
+
+// ------------------------------------------------------------------------------------ embedding
+__global__ void embed_kernel(const int* __restrict__ ids, const uint4* __restrict__ table,
+                             uint4* __restrict__ out, int M, int H8, int V) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int m = blockIdx.x;
+  int id = ids[m];
+  id = id < 0 ? 0 : (id >= V ? V - 1 : id);       // pad id (-1) and garbage map to a valid row
+  const uint4* src = table + (size_t)id * H8;
+  uint4* dst = out + (size_t)m * H8;
+  for (int i = threadIdx.x; i < H8; i += blockDim.x) dst[i] = __ldg(src + i);
+}
+
+// ------------------------------------------------------------------------------------ RMSNorm
+// One CTA per row.  Optional `delta` is added to x first (residual add) and the sum is written to
+// `x_out` (may alias x); `out` receives the normalised row.  Up to MAXC 16-byte chunks per thread
+// stay in registers so the row is read once.
+template <int MAXC>
+__global__ void __launch_bounds__(1024)
+rmsnorm_kernel(const uint4* __restrict__ x, const uint4* __restrict__ delta, const uint4* __restrict__ w,
+               uint4* __restrict__ out, uint4* __restrict__ x_out, int H8, float inv_h, float eps) {
+  pdl_wait();
+  pdl_launch_dependents();
+  __shared__ float red[32];
+  const size_t row = (size_t)blockIdx.x * H8;
+  float v[MAXC][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int c = 0; c < MAXC; ++c) {
+    const int i = threadIdx.x + c * blockDim.x;
+    if (i < H8) {
+      uint4 a = x[row + i];
+      uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+      if (delta != nullptr) {
+        uint4 d = delta[row + i];
+        uint32_t dw[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          // the residual stream is stored in bf16, so round the sum before using it (matches x_out)
+          uint32_t s = pack_bf16(bf16_lo(aw[j]) + bf16_lo(dw[j]), bf16_hi(aw[j]) + bf16_hi(dw[j]));
+          aw[j] = s;
+        }
+        if (x_out != nullptr) x_out[row + i] = make_uint4(aw[0], aw[1], aw[2], aw[3]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[c][2 * j] = bf16_lo(aw[j]);
+        v[c][2 * j + 1] = bf16_hi(aw[j]);
+        ss += v[c][2 * j] * v[c][2 * j] + v[c][2 * j + 1] * v[c][2 * j + 1];
+      }
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x + 31) / 32 ? red[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) red[0] = rsqrtf(t * inv_h + eps);
+  }
+  __syncthreads();
+  const float r = red[0];
+#pragma unroll
+  for (int c = 0; c < MAXC; ++c) {
+    const int i = threadIdx.x + c * blockDim.x;
+    if (i < H8) {
+      uint4 g = __ldg(w + i);
+      uint32_t gw[4] = {g.x, g.y, g.z, g.w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        o[j] = pack_bf16(v[c][2 * j] * r * bf16_lo(gw[j]), v[c][2 * j + 1] * r * bf16_hi(gw[j]));
+      out[row + i] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ RoPE + KV append
+// qkv: [M, (nh + 2 nkv) · hd] straight out of the fused wqkv GEMM (q | k | v column blocks).
+// Row m = b·S + s.  slot = cache_len + s;  position = slot − pad_left[b] (≥ 0), unless `positions`
+// is given.  q is rotated in place (or into q_out), k is rotated and stored, v is stored.
+// Cache layout: [B][nkv][T][hd] for this layer.  One thread = 8 consecutive elements = 4 rotary pairs.
+__global__ void rope_kv_kernel(uint4* __restrict__ qkv, uint4* __restrict__ q_out,
+                               uint4* __restrict__ kc, uint4* __restrict__ vc,
+                               const float4* __restrict__ cos_t, const float4* __restrict__ sin_t,
+                               const int* __restrict__ cache_len_ptr, const int* __restrict__ pad_left,
+                               const int* __restrict__ positions, int S, int nh, int nkv, int hd8,
+                               int T, int max_pos) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int m = blockIdx.x;
+  const int b = m / S, s = m - b * S;
+  const int base = cache_len_ptr ? *cache_len_ptr : 0;
+  const int slot = base + s;
+  int pos = positions ? positions[m] : slot - (pad_left ? pad_left[b] : 0);
+  pos = pos < 0 ? 0 : (pos >= max_pos ? max_pos - 1 : pos);
+  const int row8 = (nh + 2 * nkv) * hd8;
+  const int hd4 = hd8;  // hd/2 floats = hd8*4 floats = hd8 float4
+  for (int i = threadIdx.x; i < row8; i += blockDim.x) {
+    const int head = i / hd8, c = i - head * hd8;
+    uint4 a = qkv[(size_t)m * row8 + i];
+    if (head < nh + nkv) {
+      const float4 cs = __ldg(cos_t + (size_t)pos * hd4 + c);
+      const float4 sn = __ldg(sin_t + (size_t)pos * hd4 + c);
+      const float cc[4] = {cs.x, cs.y, cs.z, cs.w}, ssn[4] = {sn.x, sn.y, sn.z, sn.w};
+      uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float re = bf16_lo(aw[j]), im = bf16_hi(aw[j]);
+        aw[j] = pack_bf16(re * cc[j] - im * ssn[j], re * ssn[j] + im * cc[j]);
+      }
+      a = make_uint4(aw[0], aw[1], aw[2], aw[3]);
+    }
+    if (head < nh) {
+      if (q_out) q_out[((size_t)m * nh + head) * hd8 + c] = a;
+      else qkv[(size_t)m * row8 + i] = a;
+    } else if (slot < T) {
+      const bool is_k = head < nh + nkv;
+      const int kvh = is_k ? head - nh : head - nh - nkv;
+      uint4* dst = is_k ? kc : vc;
+      dst[(((size_t)b * nkv + kvh) * T + slot) * hd8 + c] = a;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ SwiGLU
+// in: [M, 2F] with (gate, up) either interleaved column pairs or as two halves; out: [M, F].
+__global__ void swiglu_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                              size_t total8, int F, int interleaved) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int F8 = F / 8;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total8;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t m = i / F8;
+    const int c = (int)(i - m * F8);
+    const uint4* row = reinterpret_cast<const uint4*>(in + m * 2 * (size_t)F);
+    uint32_t o[4];
+    if (interleaved) {
+      uint4 p0 = row[2 * c], p1 = row[2 * c + 1];
+      uint32_t w[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        o[j] = pack_bf16(silu(bf16_lo(w[2 * j])) * bf16_hi(w[2 * j]),
+                         silu(bf16_lo(w[2 * j + 1])) * bf16_hi(w[2 * j + 1]));
+    } else {
+      uint4 g = row[c], u = row[F8 + c];
+      uint32_t gw[4] = {g.x, g.y, g.z, g.w}, uw[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        o[j] = pack_bf16(silu(bf16_lo(gw[j])) * bf16_lo(uw[j]), silu(bf16_hi(gw[j])) * bf16_hi(uw[j]));
+    }
+    reinterpret_cast<uint4*>(out)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+}  // namespace jl
+
+using namespace jl;
+
+extern "C" JL_API int jl_embed(const int* ids, const void* table, void* out, int M, int H, int V, void* stream) {
+  JL_CHECK_ARG(H % 8 == 0, "jl_embed: H=%d must be a multiple of 8", H);
+  if (M == 0) return JL_OK;
+  int threads = H / 8 < 256 ? ((H / 8 + 31) / 32) * 32 : 256;
+  JL_CUDA(launch_pdl(embed_kernel, dim3(M), dim3(threads), 0, (cudaStream_t)stream, ids,
+                     (const uint4*)table, (uint4*)out, M, H / 8, V));
+  return JL_OK;
+}
+
+extern "C" JL_API int jl_rmsnorm(const void* x, const void* delta, const void* w, void* out, void* x_out, int M,
+                          int H, float eps, void* stream) {
+  JL_CHECK_ARG(H % 8 == 0 && H <= 4 * 8 * 1024, "jl_rmsnorm: H=%d must be a multiple of 8 and <= 32768", H);
+  if (M == 0) return JL_OK;
+  const int H8 = H / 8;
+  // ≤512 threads per row CTA; wider rows keep 2 or 4 chunks per thread in registers
+  const int chunks = H8 <= 512 ? 1 : (H8 <= 1024 ? 2 : 4);
+  const int threads = (((H8 + chunks - 1) / chunks + 31) / 32) * 32;
+  auto s = (cudaStream_t)stream;
+  const float inv_h = 1.0f / (float)H;
+  cudaError_t e;
+  if (chunks == 1)
+    e = launch_pdl(rmsnorm_kernel<1>, dim3(M), dim3(threads), 0, s, (const uint4*)x, (const uint4*)delta,
+                   (const uint4*)w, (uint4*)out, (uint4*)x_out, H8, inv_h, eps);
+  else if (chunks == 2)
+    e = launch_pdl(rmsnorm_kernel<2>, dim3(M), dim3(threads), 0, s, (const uint4*)x, (const uint4*)delta,
+                   (const uint4*)w, (uint4*)out, (uint4*)x_out, H8, inv_h, eps);
+  else
+    e = launch_pdl(rmsnorm_kernel<4>, dim3(M), dim3(threads), 0, s, (const uint4*)x, (const uint4*)delta,
+                   (const uint4*)w, (uint4*)out, (uint4*)x_out, H8, inv_h, eps);
+  JL_CUDA(e);
+  return JL_OK;
+}
+
+extern "C" JL_API int jl_rope_kv_write(void* qkv, void* q_out, void* k_cache, void* v_cache, const float* cos_t,
+                                const float* sin_t, const int* cache_len_ptr, const int* pad_left,
+                                const int* positions, int B, int S, int nh, int nkv, int hd, int T,
+                                int max_pos, void* stream) {
+  JL_CHECK_ARG(hd % 8 == 0, "jl_rope_kv_write: head_dim=%d must be a multiple of 8", hd);
+  if (B * S == 0) return JL_OK;
+  const int row8 = (nh + 2 * nkv) * hd / 8;
+  int threads = row8 < 256 ? ((row8 + 31) / 32) * 32 : 256;
+  JL_CUDA(launch_pdl(rope_kv_kernel, dim3(B * S), dim3(threads), 0, (cudaStream_t)stream, (uint4*)qkv,
+                     (uint4*)q_out, (uint4*)k_cache, (uint4*)v_cache, (const float4*)cos_t,
+                     (const float4*)sin_t, cache_len_ptr, pad_left, positions, S, nh, nkv, hd / 8, T, max_pos));
+  return JL_OK;
+}
+
+extern "C" JL_API int jl_swiglu(const void* in, void* out, int M, int F, int interleaved, void* stream) {
+  JL_CHECK_ARG(F % 8 == 0, "jl_swiglu: F=%d must be a multiple of 8", F);
+  const size_t total8 = (size_t)M * (F / 8);
+  if (total8 == 0) return JL_OK;
+  int blocks = (int)((total8 + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  JL_CUDA(launch_pdl(swiglu_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream,
+                     (const __nv_bfloat16*)in, (__nv_bfloat16*)out, total8, F, interleaved));
+  return JL_OK;
+}

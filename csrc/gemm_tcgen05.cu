@@ -1,0 +1,323 @@
+// bf16 GEMM on 5th-generation tensor cores: D = A[Ra,K] · B[Rb,K]^T with fp32 accumulation in TMEM.
+//
+//   * operands are K-major and arrive by TMA (128-byte swizzle) into a multi-stage mbarrier ring;
+//   * one elected thread issues tcgen05.mma (UMMA 128 x BN x 16), completion is signalled with
+//     tcgen05.commit → mbarrier, the accumulator (double-buffered, 2·BN TMEM columns) is drained by four
+//     epilogue warps with tcgen05.ld while the next tile's MMAs run;
+//   * persistent: one CTA per SM walks the tile list, A-tile index fastest so CTAs that run together
+//     share the same weight tile through L2.
+//
+// Two orientations share the kernel:
+//   normal  (prefill, M >= 128): A = activations [M,K], B = weights [N,K]; D tile rows are tokens;
+//   swap-AB (decode, 8 < M <= 128): A = weights [N,K] (fills the 128-wide MMA M), B = activations
+//           [M,K] (MMA N = padded batch); the D tile is transposed on the way out.
+// Epilogues: plain bf16 / fp32, residual add, SwiGLU over interleaved (w1,w3) output columns.
+//
+// Replaces the cuBLAS GEMMs XLA emitted for /root/reference/jax_llama/model.py:119-150 (wq/wk/wv/wo),
+// :311-338 (w1/w2/w3) and :699-706 (lm_head).
+#include "jllama_b200.h"
+#include "tcgen05.cuh"
+
+namespace jl {
+
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_BK = 64;
+constexpr int GEMM_THREADS = 256;   // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warp3 idle, warps 4-7 epilogue
+
+enum { EPI_PLAIN = 0, EPI_RESIDUAL = 1, EPI_SWIGLU = 2 };
+
+struct GemmParams {
+  void* out;
+  const __nv_bfloat16* residual;
+  int Ra, Rb, K;            // A-side rows, B-side rows, reduction length
+  int ldo;                  // output row pitch (elements)
+  int a_blocks, b_blocks;   // tile counts
+  int stages;
+  uint64_t hint_a, hint_b;
+};
+
+__host__ __device__ constexpr int tmem_cols_for(int bn) {
+  return 2 * bn <= 32 ? 32 : (2 * bn <= 64 ? 64 : (2 * bn <= 128 ? 128 : (2 * bn <= 256 ? 256 : 512)));
+}
+
+template <int BN, int EPI, bool SWAP, bool OUT_F32>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+            const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2;
+  constexpr uint32_t B_BYTES = BN * GEMM_BK * 2;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + (B_BYTES < 1024 ? 1024 : B_BYTES);
+  constexpr uint32_t TMEM_COLS = tmem_cols_for(BN);
+  constexpr uint32_t IDESC = tc::idesc_bf16_f32(GEMM_BM, BN);
+
+  const uint32_t smem_base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int stages = p.stages;
+  const uint32_t bars = smem_base + stages * STAGE_BYTES;       // full[stages] | empty[stages] | tfull[2] | tempty[2]
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (stages + s); };
+  auto tfull_bar = [&](int s) { return bars + 8u * (2 * stages + s); };
+  auto tempty_bar = [&](int s) { return bars + 8u * (2 * stages + 2 + s); };
+  const uint32_t tmem_slot = bars + 8u * (2 * stages + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - tc::smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
+  const int num_tiles = p.a_blocks * p.b_blocks;
+
+  if (warp == 0 && lane == 0) {
+    tc::prefetch_tensormap(&tmap_a);
+    tc::prefetch_tensormap(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) { tc::mbar_init(full_bar(s), 1); tc::mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { tc::mbar_init(tfull_bar(s), 1); tc::mbar_init(tempty_bar(s), 4); }
+    tc::fence_barrier_init();
+  }
+  if (warp == 2) tc::tmem_alloc(tmem_slot, TMEM_COLS);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  pdl_wait();                 // everything above overlapped the previous kernel's tail
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int a_blk = t % p.a_blocks, b_blk = t / p.a_blocks;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tc::mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
+          tc::mbar_expect_tx(full_bar(stage), A_BYTES + B_BYTES);
+          tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM, p.hint_a);
+          tc::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * GEMM_BK, b_blk * BN, p.hint_b);
+          if (++stage == stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer (single thread)
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0; int it = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+        const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
+        tc::mbar_wait(tempty_bar(as), aphase ^ 1);          // epilogue has drained this accumulator
+        tc::fence_after_sync();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tc::mbar_wait(full_bar(stage), phase);
+          tc::fence_after_sync();
+          const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
+          const uint64_t da = tc::smem_desc_kmajor_sw128(sa), db = tc::smem_desc_kmajor_sw128(sb);
+#pragma unroll
+          for (int k = 0; k < GEMM_BK / 16; ++k)            // +32 bytes per UMMA_K inside the swizzle span
+            tc::mma_ss(d_tmem, da + 2 * k, db + 2 * k, IDESC, (kb | k) != 0);
+          tc::mma_commit(empty_bar(stage));                 // frees the smem slot when these MMAs retire
+          if (++stage == stages) { stage = 0; phase ^= 1; }
+        }
+        tc::mma_commit(tfull_bar(as));                      // accumulator complete → epilogue
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================== epilogue: TMEM → registers → global
+    const int quarter = warp & 3;                           // TMEM lanes [32·quarter, 32·quarter+32)
+    int it = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      const int a_blk = t % p.a_blocks, b_blk = t / p.a_blocks;
+      const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
+      tc::mbar_wait(tfull_bar(as), aphase);
+      tc::fence_after_sync();
+      const int ra = a_blk * GEMM_BM + quarter * 32 + lane;  // A-side row of this thread
+      const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+      constexpr int CH = BN >= 32 ? 32 : 16;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += CH) {
+        uint32_t v[CH];
+        if constexpr (CH == 32) tc::tmem_ld32(t_row + c0, reinterpret_cast<uint32_t(&)[32]>(v));
+        else tc::tmem_ld16(t_row + c0, reinterpret_cast<uint32_t(&)[16]>(v));
+        tc::tmem_ld_wait();
+        const int cb0 = b_blk * BN + c0;                    // first B-side row of this chunk
+        if constexpr (!SWAP) {
+          // thread owns one token row, CH consecutive output columns
+          if (ra < p.Ra) {
+            if constexpr (EPI == EPI_SWIGLU) {
+              __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)ra * p.ldo + cb0 / 2;
+              uint32_t w[CH / 4];
+#pragma unroll
+              for (int j = 0; j < CH / 4; ++j) {
+                float g0 = __bfloat162float(__float2bfloat16(__uint_as_float(v[4 * j])));
+                float u0 = __bfloat162float(__float2bfloat16(__uint_as_float(v[4 * j + 1])));
+                float g1 = __bfloat162float(__float2bfloat16(__uint_as_float(v[4 * j + 2])));
+                float u1 = __bfloat162float(__float2bfloat16(__uint_as_float(v[4 * j + 3])));
+                w[j] = pack_bf16(silu(g0) * u0, silu(g1) * u1);
+              }
+              if (cb0 + CH <= p.Rb) {
+#pragma unroll
+                for (int j = 0; j < CH / 16; ++j)
+                  reinterpret_cast<uint4*>(o)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+              } else {
+                for (int j = 0; j < CH / 2; ++j)
+                  if (cb0 + 2 * j + 1 < p.Rb)
+                    o[j] = reinterpret_cast<__nv_bfloat16*>(w)[j];
+              }
+            } else if constexpr (OUT_F32) {
+              float* o = reinterpret_cast<float*>(p.out) + (size_t)ra * p.ldo + cb0;
+              if (cb0 + CH <= p.Rb) {
+#pragma unroll
+                for (int j = 0; j < CH / 4; ++j)
+                  reinterpret_cast<uint4*>(o)[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+              } else {
+                for (int j = 0; j < CH; ++j) if (cb0 + j < p.Rb) o[j] = __uint_as_float(v[j]);
+              }
+            } else {
+              __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)ra * p.ldo + cb0;
+              const bool full = cb0 + CH <= p.Rb;
+              uint32_t w[CH / 2];
+              if constexpr (EPI == EPI_RESIDUAL) {
+                const __nv_bfloat16* r = p.residual + (size_t)ra * p.ldo + cb0;
+                if (full) {
+#pragma unroll
+                  for (int j = 0; j < CH / 8; ++j) {
+                    const uint4 rr = reinterpret_cast<const uint4*>(r)[j];
+                    const uint32_t rw[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                      const uint32_t acc = pack_bf16(__uint_as_float(v[8 * j + 2 * q]), __uint_as_float(v[8 * j + 2 * q + 1]));
+                      w[4 * j + q] = pack_bf16(bf16_lo(acc) + bf16_lo(rw[q]), bf16_hi(acc) + bf16_hi(rw[q]));
+                    }
+                  }
+                } else {
+                  for (int j = 0; j < CH; ++j)
+                    if (cb0 + j < p.Rb)
+                      o[j] = __float2bfloat16(__bfloat162float(__float2bfloat16(__uint_as_float(v[j]))) +
+                                              __bfloat162float(r[j]));
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < CH / 2; ++j) w[j] = pack_bf16(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+              }
+              if (full) {
+#pragma unroll
+                for (int j = 0; j < CH / 8; ++j)
+                  reinterpret_cast<uint4*>(o)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+              } else if constexpr (EPI != EPI_RESIDUAL) {
+                for (int j = 0; j < CH; ++j)
+                  if (cb0 + j < p.Rb) o[j] = reinterpret_cast<__nv_bfloat16*>(w)[j];
+              }
+            }
+          }
+        } else {
+          // swap-AB: lanes are weight rows (output features), columns are tokens → transposed store;
+          // for a fixed token the 32 lanes write 32 consecutive features (coalesced)
+#pragma unroll
+          for (int j = 0; j < CH; ++j) {
+            const int tok = cb0 + j;
+            float x = __uint_as_float(v[j]);
+            if constexpr (EPI == EPI_SWIGLU) {
+              // (gate, up) sit in adjacent lanes: even lane gets its neighbour's value
+              const float xb = __bfloat162float(__float2bfloat16(x));
+              const float up = __shfl_down_sync(0xffffffffu, xb, 1);
+              if ((lane & 1) == 0 && tok < p.Rb && ra + 1 < p.Ra)
+                reinterpret_cast<__nv_bfloat16*>(p.out)[(size_t)tok * p.ldo + ra / 2] =
+                    __float2bfloat16(silu(xb) * up);
+            } else if (tok < p.Rb && ra < p.Ra) {
+              if constexpr (OUT_F32) {
+                reinterpret_cast<float*>(p.out)[(size_t)tok * p.ldo + ra] = x;
+              } else {
+                if constexpr (EPI == EPI_RESIDUAL)
+                  x = __bfloat162float(__float2bfloat16(x)) + __bfloat162float(p.residual[(size_t)tok * p.ldo + ra]);
+                reinterpret_cast<__nv_bfloat16*>(p.out)[(size_t)tok * p.ldo + ra] = __float2bfloat16(x);
+              }
+            }
+          }
+        }
+      }
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(tempty_bar(as));
+    }
+  }
+
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+template <int BN, int EPI, bool SWAP, bool OUT_F32>
+static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int Ra, int Rb, int K, int num_sms,
+                       cudaStream_t stream) {
+  GemmParams p = p0;
+  CUtensorMap ta, tb;
+  int rc = make_tmap_2d_bf16(&ta, a, Ra, K, K, GEMM_BM);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tb, b, Rb, K, K, BN);
+  if (rc) return rc;
+  constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2;
+  constexpr uint32_t B_BYTES = BN * GEMM_BK * 2;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + (B_BYTES < 1024 ? 1024 : B_BYTES);
+  int stages = (int)((200 * 1024) / STAGE_BYTES);
+  if (stages > 10) stages = 10;
+  const int num_kb = (K + GEMM_BK - 1) / GEMM_BK;
+  if (stages > num_kb * 2) stages = num_kb * 2 < 2 ? 2 : num_kb * 2;
+  p.stages = stages;
+  p.a_blocks = (Ra + GEMM_BM - 1) / GEMM_BM;
+  p.b_blocks = (Rb + BN - 1) / BN;
+  const size_t smem = (size_t)stages * STAGE_BYTES + 8 * (2 * stages + 4) + 16 + 1024;
+  auto kern = gemm_kernel<BN, EPI, SWAP, OUT_F32>;
+  JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = p.a_blocks * p.b_blocks;
+  if (grid > num_sms) grid = num_sms;
+  JL_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), smem, stream, ta, tb, p));
+  return JL_OK;
+}
+
+template <int EPI, bool OUT_F32>
+static int dispatch_gemm(const void* x, const void* w, const GemmParams& p, int M, int N, int K, int num_sms,
+                         cudaStream_t s) {
+  if (M > 128) {
+    // normal orientation: A = activations, B = weights
+    GemmParams q = p;
+    q.Ra = M; q.Rb = N;
+    q.hint_a = tc::EVICT_LAST; q.hint_b = tc::EVICT_NORMAL;
+    if (N >= 256) return launch_gemm<256, EPI, false, OUT_F32>(x, w, q, M, N, K, num_sms, s);
+    return launch_gemm<128, EPI, false, OUT_F32>(x, w, q, M, N, K, num_sms, s);
+  }
+  // swap-AB: A = weights (streamed once → evict-first), B = activations (re-read by every CTA)
+  GemmParams q = p;
+  q.Ra = N; q.Rb = M;
+  q.hint_a = tc::EVICT_FIRST; q.hint_b = tc::EVICT_LAST;
+  if (M <= 16) return launch_gemm<16, EPI, true, OUT_F32>(w, x, q, N, M, K, num_sms, s);
+  if (M <= 32) return launch_gemm<32, EPI, true, OUT_F32>(w, x, q, N, M, K, num_sms, s);
+  if (M <= 64) return launch_gemm<64, EPI, true, OUT_F32>(w, x, q, N, M, K, num_sms, s);
+  return launch_gemm<128, EPI, true, OUT_F32>(w, x, q, N, M, K, num_sms, s);
+}
+
+}  // namespace jl
+
+using namespace jl;
+
+extern "C" JL_API int jl_gemm(const void* x, const void* w, const void* residual, void* out, int M, int N, int K,
+                       int mode, int out_f32, int num_sms, void* stream) {
+  JL_CHECK_ARG(M >= 1 && N >= 1 && K >= 8 && K % 8 == 0, "jl_gemm: bad shape M=%d N=%d K=%d (K %% 8 == 0)", M, N, K);
+  JL_CHECK_ARG(mode >= 0 && mode <= 2, "jl_gemm: bad mode %d", mode);
+  JL_CHECK_ARG(mode != EPI_SWIGLU || N % 2 == 0, "jl_gemm: SwiGLU needs an even N");
+  JL_CHECK_ARG(mode != EPI_RESIDUAL || residual != nullptr, "jl_gemm: residual pointer missing");
+  JL_CHECK_ARG(!(out_f32 && mode != EPI_PLAIN), "jl_gemm: fp32 output only in plain mode");
+  JL_CHECK_ARG(N % 8 == 0, "jl_gemm: N=%d must be a multiple of 8", N);
+  if (num_sms <= 0) num_sms = 148;
+  GemmParams p{};
+  p.out = out;
+  p.residual = (const __nv_bfloat16*)residual;
+  p.K = K;
+  p.ldo = mode == EPI_SWIGLU ? N / 2 : N;
+  auto s = (cudaStream_t)stream;
+  if (mode == EPI_PLAIN && out_f32) return dispatch_gemm<EPI_PLAIN, true>(x, w, p, M, N, K, num_sms, s);
+  if (mode == EPI_PLAIN) return dispatch_gemm<EPI_PLAIN, false>(x, w, p, M, N, K, num_sms, s);
+  if (mode == EPI_RESIDUAL) return dispatch_gemm<EPI_RESIDUAL, false>(x, w, p, M, N, K, num_sms, s);
+  return dispatch_gemm<EPI_SWIGLU, false>(x, w, p, M, N, K, num_sms, s);
+}

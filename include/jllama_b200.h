@@ -1,0 +1,86 @@
+/* C ABI of libjllama_b200.so — hand-written sm_100a kernels for LLaMA inference on NVIDIA B200.
+ *
+ * Conventions
+ *  - every entry point returns 0 on success, non-zero on failure; jl_last_error() describes the failure;
+ *  - `stream` is a cudaStream_t passed as void*; launches are asynchronous on it and are legal inside
+ *    CUDA-graph stream capture unless stated otherwise;
+ *  - activations / weights are bf16, row-major; linear weights are [N, K] (out, in) i.e. K-major;
+ *  - kernels are launched with Programmatic Dependent Launch enabled and are safe in PDL chains.
+ *
+ * Each declaration cites the reference op it replaces (paths under /root/reference/jax_llama/).
+ */
+#ifndef JLLAMA_B200_H
+#define JLLAMA_B200_H
+#include <stddef.h>
+#ifndef JL_API
+#define JL_API __attribute__((visibility("default")))
+#endif
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* jl_last_error(void);
+int jl_version(void);
+/* number of kernel launches issued through this library since load (bench.py reports it) */
+unsigned long long jl_launch_count(void);
+
+/* model.py:611-617,638 — embedding lookup. ids int32 [M]; table [V,H]; out [M,H]. */
+int jl_embed(const int* ids, const void* table, void* out, int M, int H, int V, void* stream);
+
+/* model.py:42-48 — RMSNorm over rows of x [M,H]; optional fused residual add: if `delta` is given the
+ * row normalised is x+delta and (if x_out != NULL) the sum is stored to x_out (may alias x). */
+int jl_rmsnorm(const void* x, const void* delta, const void* w, void* out, void* x_out, int M, int H,
+               float eps, void* stream);
+
+/* model.py:58-92 + 177-199 — interleaved-pair RoPE on the q|k column blocks of the fused qkv activation
+ * [B*S, (nh+2nkv)*hd] and append of k,v to this layer's cache [B][nkv][T][hd].  Token (b,s) goes to slot
+ * *cache_len_ptr + s at rotary position slot - pad_left[b] (or positions[b*S+s] if given).  q is rotated
+ * in place, or written to q_out [B*S, nh*hd] when q_out != NULL. */
+int jl_rope_kv_write(void* qkv, void* q_out, void* k_cache, void* v_cache, const float* cos_t,
+                     const float* sin_t, const int* cache_len_ptr, const int* pad_left, const int* positions,
+                     int B, int S, int nh, int nkv, int hd, int T, int max_pos, void* stream);
+
+/* model.py:338 — silu(gate)*up.  in [M,2F] (interleaved pairs if `interleaved`, else two halves). */
+int jl_swiglu(const void* in, void* out, int M, int F, int interleaved, void* stream);
+
+/* model.py:119-150,311-338,699-706 at decode — y = f(x) W^T for M <= 8 rows, weight-streaming bound.
+ * norm_w != NULL fuses RMSNorm(x)*norm_w; mode 0 plain, 1 out = residual + y, 2 SwiGLU over interleaved
+ * (w1,w3) rows (out is [M,N/2]); out_f32 selects fp32 output (plain mode). */
+int jl_gemv(const void* x, const void* w, const void* norm_w, const void* residual, void* out, int M, int N,
+            int K, float eps, int mode, int out_f32, int num_sms, void* stream);
+
+/* Same linear layers for any M on the tcgen05 tensor cores (TMA-fed, TMEM accumulators).  M > 128 runs
+ * token-major tiles (prefill); M <= 128 runs swap-AB so the weight rows fill the 128-wide MMA and the
+ * batch is the MMA N (decode at batch 9..128).  Modes / out_f32 as in jl_gemv.  N % 8 == 0, K % 8 == 0;
+ * SwiGLU needs N % 16 == 0. */
+int jl_gemm(const void* x, const void* w, const void* residual, void* out, int M, int N, int K, int mode,
+            int out_f32, int num_sms, void* stream);
+
+/* model.py:194-198,263-288 at S=1 — split-KV GQA decode attention over [pad_left[b], *cache_len+n_new).
+ * q [B,nh,hd] with batch pitch q_bstride elements (0 = dense; lets q live inside the fused qkv
+ * activation); caches [B][nkv][T][hd]; out [B,nh*hd].  `scratch` must hold
+ * jl_decode_attn_scratch_bytes(B,nh,hd,splits) bytes when splits > 1. */
+size_t jl_decode_attn_scratch_bytes(int B, int nh, int hd, int splits);
+int jl_decode_attn_splits(int B, int nkv, int max_len, int num_sms);
+int jl_decode_attn(const void* q, const void* k_cache, const void* v_cache, const int* cache_len_ptr,
+                   const int* pad_left, void* scratch, void* out, int B, int nh, int nkv, int hd, int T,
+                   int n_new, float scale, int splits, int q_bstride, void* stream);
+
+/* generation.py:28-41 (HF warpers + categorical/argmax) — logits fp32 [B, ld] (V valid columns). */
+int jl_argmax(const float* logits, int B, int V, int ld, int idx_offset, float* out_val, int* out_idx,
+              void* stream);
+int jl_topk(const float* logits, int B, int V, int ld, int idx_offset, int k, float* cand_val, int* cand_idx,
+            void* stream);
+int jl_sample(const float* cand_val, const int* cand_idx, int B, int n_lists, size_t list_stride, int k,
+              int top_k, float top_p, float temperature, unsigned long long seed, const int* step_ptr,
+              int* out_tok, void* stream);
+/* HF _sample/_greedy_search body: pad finished rows, mark EOS, append to sequences,
+ * advance cur_len / cache_len / step on device. */
+int jl_decode_advance(const int* tok, int* next_ids, int* finished, int* sequences, int B, int max_len,
+                      int eos, int pad, int* cur_len, int* cache_len, int* step, int* n_unfinished,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -20,6 +20,14 @@ from .parallel.layout import Mesh, P, with_named_sharding_constraint
 logger = logging.getLogger(__name__)
 
 
+def _leaves(tree: Dict[str, Any]):
+    for v in tree.values():
+        if isinstance(v, dict):
+            yield from _leaves(v)
+        else:
+            yield v
+
+
 @dataclass
 class LLaMA:
     params: Dict[str, Any]
@@ -40,6 +48,21 @@ class LLaMA:
             temperature=temperature if temperature != 0.0 else 1.0, top_k=top_k, top_p=top_p,
             pad_token_id=self.tokenizer.eos_id, eos_token_id=self.tokenizer.eos_id, seed=seed)
         return with_named_sharding_constraint(out.sequences, self.mesh, P("dp", None))
+
+    def stream(self, tokens: torch.Tensor, attention_mask: torch.Tensor, max_gen_len: int,
+               temperature: float = 0.8, top_p: float = 0.95, top_k: Optional[int] = 50, seed: int = 0) -> Any:
+        """Token-at-a-time variant of `generate` for interactive serving (CUDA parameters only).
+
+        Returns a handle whose ``step(feed=None)`` produces one token per row and hands it back in pinned
+        host memory; ``last_tokens()`` is the first generated token right after the prefill."""
+        dev = next(iter(_leaves(self.params))).device
+        if dev.type != "cuda":
+            raise NotImplementedError("LLaMA.stream needs parameters on a CUDA device")
+        eng = self.model._engine_for(self.params)
+        return eng.begin_stream(torch.as_tensor(tokens).to(dev), torch.as_tensor(attention_mask).to(dev),
+                                max_length=max_gen_len + tokens.shape[1], do_sample=temperature != 0.0,
+                                temperature=temperature if temperature != 0.0 else 1.0, top_k=top_k, top_p=top_p,
+                                pad_token_id=self.tokenizer.eos_id, eos_token_id=self.tokenizer.eos_id, seed=seed)
 
     def encode_prompts(self, prompts: Sequence[str]) -> tuple:
         """Tokenise with BOS and left-pad with eos_id; returns (tokens [B,P] int64, mask, per-row ids)."""

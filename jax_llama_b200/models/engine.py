@@ -1,0 +1,453 @@
+"""B200 execution engine: kernel-ready weights, device-resident KV cache, CUDA-graph decode.
+
+What XLA/GSPMD did implicitly for the reference (fused elementwise kernels, cuBLAS GEMMs, a compiled
+`lax.while_loop` decode body — SURVEY §3.2/§3.3) is explicit here:
+
+* weights are repacked once into the layouts the kernels want: fused ``wqkv`` ``[(nh+2nkv)·hd, H]``,
+  ``w13`` with (w1, w3) rows interleaved so SwiGLU happens in the GEMM epilogue, everything ``[N, K]``;
+* a decode step is a fixed sequence of ~7 launches per layer (RMSNorm fused into the GEMV prologue,
+  residual / SwiGLU fused into epilogues, RoPE fused with the KV append, split-KV GQA attention, on-device
+  sampling and sequence bookkeeping) captured once into a CUDA graph and replayed per token with no
+  host synchronisation; kernels are chained with programmatic dependent launch;
+* the step's moving parts (``cache_len``, ``cur_len``, RNG step, finished flags) live in device memory so
+  the same graph serves every position.
+
+Model math: /root/reference/jax_llama/model.py:201-300 (attention), :337-340 (MLP), :374-398 (block),
+:622-741 (backbone + head); decode loop semantics: HF Flax `_sample` as configured by generation.py:28-41.
+"""
+from __future__ import annotations
+
+import logging
+from dataclasses import dataclass, field
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+
+from ..config import LLaMAConfig
+from ..ops import _lib
+from ..ops import kernels as K
+from .reference import KVCache, ModelOutput, rope_cos_sin
+
+logger = logging.getLogger(__name__)
+
+Tree = Dict[str, Any]
+MAX_TOPK = 64
+
+
+@dataclass
+class DeviceKVCache(KVCache):
+    """KV cache whose fill level also lives on the device (read by kernels, advanced by kernels)."""
+
+    len_dev: Optional[torch.Tensor] = None      # int32 [1]
+
+    def set_index(self, value: int) -> None:
+        self.index = int(value)
+        self.len_dev.fill_(int(value))
+
+
+@dataclass
+class LayerWeights:
+    attn_norm: torch.Tensor
+    wqkv: torch.Tensor
+    wo: torch.Tensor
+    ffn_norm: torch.Tensor
+    w13: torch.Tensor
+    w2: torch.Tensor
+
+
+def interleave_rows(w1: torch.Tensor, w3: torch.Tensor) -> torch.Tensor:
+    """[F, H], [F, H] → [2F, H] with row 2j = w1[j], row 2j+1 = w3[j]."""
+    f, h = w1.shape
+    return torch.stack([w1, w3], dim=1).reshape(2 * f, h).contiguous()
+
+
+@dataclass
+class DecodeState:
+    """Static buffers of one captured decode configuration."""
+
+    B: int
+    max_len: int
+    ids: torch.Tensor
+    x: torch.Tensor
+    qkv: torch.Tensor
+    attn: torch.Tensor
+    mlp: torch.Tensor
+    logits: torch.Tensor
+    cand_val: torch.Tensor
+    cand_idx: torch.Tensor
+    tok: torch.Tensor
+    finished: torch.Tensor
+    sequences: torch.Tensor
+    cur_len: torch.Tensor
+    step: torch.Tensor
+    n_unfinished: torch.Tensor
+    splits: int
+    scratch: Optional[torch.Tensor]
+    graphs: Dict[Tuple, torch.cuda.CUDAGraph] = field(default_factory=dict)
+
+
+class B200Engine:
+    def __init__(self, config: LLaMAConfig, embedding: torch.Tensor, layers: List[LayerWeights],
+                 final_norm: torch.Tensor, lm_head: torch.Tensor, *, use_cuda_graph: bool = True):
+        self.config = config
+        self.device = embedding.device
+        if self.device.type != "cuda":
+            raise ValueError("B200Engine needs CUDA tensors")
+        _lib.lib()                                      # fail here, loudly, if the native library is absent
+        self.embedding = embedding
+        self.layers = layers
+        self.final_norm = final_norm
+        self.lm_head = lm_head
+        self.use_cuda_graph = use_cuda_graph
+        self.nh = config.num_attention_heads
+        self.nkv = config.num_key_value_heads
+        self.hd = config.head_dim
+        cos, sin = rope_cos_sin(self.hd, 2 * config.max_sequence_length, config.rope_theta)
+        self.cos, self.sin = cos.to(self.device), sin.to(self.device)
+        self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
+        self.warned_slow_prefill = False
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def from_tree(cls, config: LLaMAConfig, params: Tree, **kw: Any) -> "B200Engine":
+        """Repack a canonical (``[in, out]``) tree that already lives on a CUDA device."""
+        t = params["transformer"]
+        bf = lambda x: x.to(torch.bfloat16)          # noqa: E731
+        layers = []
+        for i in range(config.num_hidden_layers):
+            l = t["h"][str(i)]
+            a, f = l["attention"], l["feed_forward"]
+            wqkv = torch.cat([bf(a["wq"]["kernel"]).t(), bf(a["wk"]["kernel"]).t(), bf(a["wv"]["kernel"]).t()], 0)
+            layers.append(LayerWeights(
+                attn_norm=bf(l["attention_norm"]["kernel"]).contiguous(), wqkv=wqkv.contiguous(),
+                wo=bf(a["wo"]["kernel"]).t().contiguous(), ffn_norm=bf(l["ffn_norm"]["kernel"]).contiguous(),
+                w13=interleave_rows(bf(f["w1"]["kernel"]).t(), bf(f["w3"]["kernel"]).t()),
+                w2=bf(f["w2"]["kernel"]).t().contiguous()))
+        emb = bf(t["wte"]["embedding"]).contiguous()
+        head = emb if config.tie_word_embeddings else bf(params["lm_head"]["kernel"]).t().contiguous()
+        return cls(config, emb, layers, bf(t["ln_f"]["kernel"]).contiguous(), head, **kw)
+
+    @classmethod
+    def random_init(cls, config: LLaMAConfig, device: Any = "cuda", seed: int = 0, **kw: Any) -> "B200Engine":
+        """Random weights generated directly in kernel layout on the device (benchmarks; no host copy)."""
+        dev = torch.device(device)
+        g = torch.Generator(device=dev).manual_seed(seed)
+        std = config.initializer_range
+        h, f, v = config.hidden_size, config.intermediate_size, config.vocab_size
+        nh, nkv, hd = config.num_attention_heads, config.num_key_value_heads, config.head_dim
+
+        def mat(n: int, k: int) -> torch.Tensor:
+            return (torch.randn(n, k, generator=g, device=dev, dtype=torch.float32) * std).to(torch.bfloat16)
+
+        ones = lambda: torch.ones(h, dtype=torch.bfloat16, device=dev)     # noqa: E731
+        layers = [LayerWeights(ones(), mat((nh + 2 * nkv) * hd, h), mat(h, nh * hd), ones(), mat(2 * f, h),
+                               mat(h, f)) for _ in range(config.num_hidden_layers)]
+        emb = mat(v, h)
+        head = emb if config.tie_word_embeddings else mat(v, h)
+        return cls(config, emb, layers, ones(), head, **kw)
+
+    def to_tree(self) -> Tree:
+        """Inverse of `from_tree` (canonical names / ``[in, out]`` layout) for export and tests."""
+        c = self.config
+        q, kv = self.nh * self.hd, self.nkv * self.hd
+        layers = {}
+        for i, l in enumerate(self.layers):
+            layers[str(i)] = {
+                "attention": {"wq": {"kernel": l.wqkv[:q].t().contiguous()},
+                              "wk": {"kernel": l.wqkv[q:q + kv].t().contiguous()},
+                              "wv": {"kernel": l.wqkv[q + kv:].t().contiguous()},
+                              "wo": {"kernel": l.wo.t().contiguous()}},
+                "feed_forward": {"w1": {"kernel": l.w13[0::2].t().contiguous()},
+                                 "w3": {"kernel": l.w13[1::2].t().contiguous()},
+                                 "w2": {"kernel": l.w2.t().contiguous()}},
+                "attention_norm": {"kernel": l.attn_norm}, "ffn_norm": {"kernel": l.ffn_norm}}
+        tree: Tree = {"transformer": {"wte": {"embedding": self.embedding}, "ln_f": {"kernel": self.final_norm},
+                                      "h": layers}}
+        if not c.tie_word_embeddings:
+            tree["lm_head"] = {"kernel": self.lm_head.t().contiguous()}
+        return tree
+
+    # ------------------------------------------------------------------ cache
+    def new_cache(self, batch: int, max_length: int) -> DeviceKVCache:
+        shape = (self.config.num_hidden_layers, batch, self.nkv, max_length, self.hd)
+        return DeviceKVCache(
+            k=torch.zeros(shape, dtype=torch.bfloat16, device=self.device),
+            v=torch.zeros(shape, dtype=torch.bfloat16, device=self.device), index=0,
+            pad_left=torch.zeros(batch, dtype=torch.int32, device=self.device),
+            len_dev=torch.zeros(1, dtype=torch.int32, device=self.device))
+
+    @staticmethod
+    def pad_left_from_mask(attention_mask: Optional[torch.Tensor], batch: int, seq: int,
+                           device: torch.device) -> torch.Tensor:
+        """Left-padding count per row.  The fast path supports exactly the masks the generation front-end
+        produces (zeros then ones, generation.py:55-60); anything else must use the reference backend."""
+        if attention_mask is None:
+            return torch.zeros(batch, dtype=torch.int32, device=device)
+        m = attention_mask[:, :seq].to(torch.int32)
+        pad = (m == 0).to(torch.int32).sum(-1)
+        expect = (torch.arange(seq, device=m.device)[None, :] >= pad[:, None]).to(torch.int32)
+        if not torch.equal(m, expect):
+            raise NotImplementedError("the B200 engine supports left-padding masks only; use the reference "
+                                      "backend (CPU tensors or output_attentions=True) for arbitrary masks")
+        return pad.to(torch.int32).to(device)
+
+    # ------------------------------------------------------------------ layer stack (eager; any S)
+    def _layers(self, x: torch.Tensor, B: int, S: int, cache: DeviceKVCache,
+                positions: Optional[torch.Tensor], ws: Optional[DecodeState] = None) -> torch.Tensor:
+        """x [B·S, H] → x after all blocks.  Appends S slots at cache.len_dev (does not advance it)."""
+        c = self.config
+        eps = c.rms_norm_eps
+        nh, nkv, hd = self.nh, self.nkv, self.hd
+        start = cache.index
+        for i, l in enumerate(self.layers):
+            kc, vc = cache.k[i], cache.v[i]
+            qkv = K.linear(x, l.wqkv, norm_w=l.attn_norm, eps=eps, out=ws.qkv if ws else None)
+            q_rot = None
+            if S > 1:       # prefill: rotated q goes to its own dense [B·S, nh·hd] buffer for the flash kernel
+                q_rot = torch.empty((B * S, nh * hd), dtype=qkv.dtype, device=qkv.device)
+            K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
+                            pad_left=cache.pad_left, positions=positions, q_out=q_rot)
+            if S == 1:
+                q = qkv.view(B, nh + 2 * nkv, hd)[:, :nh]          # strided view: q stays inside qkv
+                attn = K.decode_attn(q, kc, vc, cache.len_dev, cache.pad_left, 1,
+                                     ws.splits if ws else 1, ws.scratch if ws else None,
+                                     out=ws.attn if ws else None)
+            else:
+                attn = self._prefill_attn(q_rot.view(B, S, nh, hd), kc, vc, start, S, cache).view(B * S, nh * hd)
+            x = K.linear(attn, l.wo, residual=x, mode=K.RESIDUAL, out=x)
+            h = K.linear(x, l.w13, norm_w=l.ffn_norm, eps=eps, mode=K.SWIGLU, out=ws.mlp if ws else None)
+            x = K.linear(h, l.w2, residual=x, mode=K.RESIDUAL, out=x)
+        return x
+
+    def _prefill_attn(self, q: torch.Tensor, kc: torch.Tensor, vc: torch.Tensor, start: int, S: int,
+                      cache: DeviceKVCache) -> torch.Tensor:
+        if _lib.has("jl_flash_prefill") and self.hd == 128:
+            return K.prefill_attn(q, kc, vc, start, S, cache.pad_left, cache.len_dev)
+        if not self.warned_slow_prefill:
+            logger.warning("flash prefill kernel unavailable for head_dim=%d: using the dense PyTorch "
+                           "statement (correct, O(S^2) memory)", self.hd)
+            self.warned_slow_prefill = True
+        return K.prefill_attn_ref(q, kc, vc, start, S, cache.pad_left)
+
+    # ------------------------------------------------------------------ public forward
+    @torch.no_grad()
+    def forward(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
+                position_ids: Optional[torch.Tensor] = None, cache: Optional[DeviceKVCache] = None,
+                with_head: bool = True, last_only: bool = False) -> ModelOutput:
+        B, S = input_ids.shape
+        c = self.config
+        own_cache = cache is None
+        if own_cache:
+            cache = self.new_cache(B, S)
+        if cache.index + S > cache.capacity:
+            raise ValueError(f"KV cache overflow: {cache.index}+{S} > capacity {cache.capacity}")
+        if attention_mask is not None and cache.index == 0:
+            cache.pad_left.copy_(self.pad_left_from_mask(attention_mask, B, S, self.device))
+        positions = None
+        if position_ids is not None:
+            positions = position_ids.to(torch.int32).reshape(-1).contiguous()
+        x = K.embed(input_ids.reshape(-1), self.embedding)
+        x = self._layers(x, B, S, cache, positions)
+        cache.set_index(cache.index + S)
+        out = ModelOutput(past_key_values=None if own_cache else cache)
+        if last_only:
+            x = x.view(B, S, c.hidden_size)[:, -1].contiguous()
+            rows = 1
+        else:
+            rows = S
+        if with_head:
+            logits = K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True)
+            out.logits = logits.view(B, rows, c.vocab_size)
+            out.last_hidden_state = None
+        else:
+            out.last_hidden_state = K.rmsnorm(x, self.final_norm, c.rms_norm_eps).view(B, rows, c.hidden_size)
+        return out
+
+    # ------------------------------------------------------------------ decode state + graph
+    def _decode_state(self, B: int, max_len: int) -> DecodeState:
+        key = (B, max_len)
+        if key in self._decode_states:
+            return self._decode_states[key]
+        c, dev = self.config, self.device
+        i32 = dict(dtype=torch.int32, device=dev)
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        splits, scratch = K.decode_attn_plan(B, self.nh, self.nkv, self.hd, max_len, dev)
+        st = DecodeState(
+            B=B, max_len=max_len, ids=torch.zeros(B, **i32), x=torch.zeros(B, c.hidden_size, **bf),
+            qkv=torch.zeros(B, (self.nh + 2 * self.nkv) * self.hd, **bf),
+            attn=torch.zeros(B, self.nh * self.hd, **bf), mlp=torch.zeros(B, c.intermediate_size, **bf),
+            logits=torch.zeros(B, c.vocab_size, dtype=torch.float32, device=dev),
+            cand_val=torch.zeros(B, MAX_TOPK, dtype=torch.float32, device=dev),
+            cand_idx=torch.zeros(B, MAX_TOPK, **i32), tok=torch.zeros(B, **i32),
+            finished=torch.zeros(B, **i32), sequences=torch.zeros(B, max_len, **i32),
+            cur_len=torch.zeros(1, **i32), step=torch.zeros(1, **i32), n_unfinished=torch.zeros(1, **i32),
+            splits=splits, scratch=scratch)
+        self._decode_states[key] = st
+        return st
+
+    def _select_and_advance(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int) -> None:
+        """logits → token (greedy or temperature/top-k/top-p) → sequences / finished / counters, on device."""
+        do_sample, temperature, top_k, top_p, seed = sampling
+        if not do_sample:
+            K.argmax(st.logits, out=st.tok)
+        else:
+            k = MAX_TOPK if not top_k or top_k > MAX_TOPK else int(top_k)
+            vals, idx = st.cand_val[:, :k], st.cand_idx[:, :k]
+            if k != MAX_TOPK:
+                vals, idx = st.cand_val.view(-1)[:st.B * k].view(st.B, k), st.cand_idx.view(-1)[:st.B * k].view(st.B, k)
+            K.topk_candidates(st.logits, k, out=(vals, idx))
+            K.sample_candidates(vals, idx, top_k=k, top_p=top_p, temperature=temperature, seed=seed,
+                                step=st.step, out=st.tok)
+        _lib.check(_lib.lib().jl_decode_advance(
+            st.tok.data_ptr(), st.ids.data_ptr(), st.finished.data_ptr(), st.sequences.data_ptr(), st.B,
+            st.max_len, int(eos), int(pad), st.cur_len.data_ptr(), cache.len_dev.data_ptr(), st.step.data_ptr(),
+            st.n_unfinished.data_ptr(), K._stream()), "jl_decode_advance")
+
+    def _decode_step(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int) -> None:
+        """One token for every row: ids → logits → next ids.  All state on device; capturable."""
+        c = self.config
+        K.embed(st.ids, self.embedding, out=st.x)
+        x = self._layers(st.x, st.B, 1, cache, None, ws=st)
+        K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True, out=st.logits)
+        self._select_and_advance(st, cache, sampling, eos, pad)
+
+    def _graph_for(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int
+                   ) -> Optional[torch.cuda.CUDAGraph]:
+        if not self.use_cuda_graph:
+            return None
+        key = (cache.k.data_ptr(), sampling, eos, pad)
+        if key in st.graphs:
+            return st.graphs[key]
+        # warm up outside capture on a side stream (first-use initialisation, cudaFuncSetAttribute, …);
+        # the step is re-playable because a snapshot of the mutable state is restored afterwards
+        snap = [t.clone() for t in (st.ids, st.finished, st.sequences, st.cur_len, st.step, st.n_unfinished,
+                                    cache.len_dev)]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            self._decode_step(st, cache, sampling, eos, pad)
+        torch.cuda.current_stream().wait_stream(side)
+        for t, s in zip((st.ids, st.finished, st.sequences, st.cur_len, st.step, st.n_unfinished, cache.len_dev), snap):
+            t.copy_(s)
+        g = torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count()
+        with torch.cuda.graph(g):
+            self._decode_step(st, cache, sampling, eos, pad)
+        st.kernels_per_step = _lib.launch_count() - n0      # kernel nodes in the captured step
+        for t, s in zip((st.ids, st.finished, st.sequences, st.cur_len, st.step, st.n_unfinished, cache.len_dev), snap):
+            t.copy_(s)
+        st.graphs[key] = g
+        return g
+
+    def launches_per_step(self, st: DecodeState) -> Optional[int]:
+        """Native kernel launches in one decode step (graph nodes when the step is graph-replayed)."""
+        return getattr(st, "kernels_per_step", None)
+
+    # ------------------------------------------------------------------ generation
+    @torch.no_grad()
+    def generate(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, *,
+                 max_length: int, do_sample: bool = False, temperature: float = 1.0,
+                 top_k: Optional[int] = 50, top_p: float = 1.0, pad_token_id: int = 0, eos_token_id: int = -1,
+                 seed: int = 0, check_every: int = 16) -> torch.Tensor:
+        """Prefill + graph-replayed decode.  Returns [B, max_length] int64 (pad-filled), like HF generate."""
+        B, S = input_ids.shape
+        if max_length > 2 * self.config.max_sequence_length:
+            raise ValueError(f"max_length {max_length} exceeds the rotary table (2 x max_sequence_length)")
+        st = self._decode_state(B, max_length)
+        cache = self.prepare(st, input_ids, attention_mask, pad_token_id)
+        sampling = (bool(do_sample), float(temperature), int(top_k or 0), float(top_p), int(seed))
+        # first new token comes from the prefill logits
+        self._select_and_advance_after_prefill(st, cache, sampling, eos_token_id, pad_token_id)
+        remaining = max_length - S - 1
+        graph = self._graph_for(st, cache, sampling, eos_token_id, pad_token_id) if remaining > 0 else None
+        done = 0
+        while done < remaining:
+            n = min(check_every, remaining - done)
+            for _ in range(n):
+                if graph is not None:
+                    graph.replay()
+                else:
+                    self._decode_step(st, cache, sampling, eos_token_id, pad_token_id)
+            done += n
+            if done < remaining and int(st.n_unfinished.item()) == 0:      # one sync per `check_every` tokens
+                break
+        cache.index = int(cache.len_dev.item())
+        return st.sequences.to(torch.long)
+
+    def prepare(self, st: DecodeState, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor],
+                pad: int) -> DeviceKVCache:
+        """Reset the decode state for a new request batch and run the prefill."""
+        B, S = input_ids.shape
+        cache = getattr(st, "_cache", None)
+        if cache is None:
+            cache = self.new_cache(B, st.max_len)
+            st._cache = cache
+        cache.set_index(0)
+        st.sequences.fill_(int(pad))
+        st.sequences[:, :S] = input_ids.to(torch.int32)
+        st.finished.zero_()
+        st.cur_len.fill_(S)
+        st.step.zero_()
+        st.n_unfinished.fill_(B)
+        out = self.forward(input_ids, attention_mask=attention_mask, cache=cache, last_only=True)
+        st.logits.copy_(out.logits.view(B, -1))
+        return cache
+
+    def _select_and_advance_after_prefill(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple,
+                                          eos: int, pad: int) -> None:
+        # the prefill already advanced cache.len_dev by S; `advance` adds one more for the *next* token's
+        # slot only after that token is written, so compensate here
+        self._select_and_advance(st, cache, sampling, eos, pad)
+        cache.len_dev.sub_(1)
+
+    # ------------------------------------------------------------------ streaming (token-at-a-time) API
+    @torch.no_grad()
+    def begin_stream(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, *,
+                     max_length: int, do_sample: bool = False, temperature: float = 1.0,
+                     top_k: Optional[int] = 50, top_p: float = 1.0, pad_token_id: int = 0,
+                     eos_token_id: int = -1, seed: int = 0) -> "EngineStream":
+        """Prefill and select the first new token; subsequent tokens come from `EngineStream.step`."""
+        B, S = input_ids.shape
+        st = self._decode_state(B, max_length)
+        cache = self.prepare(st, input_ids, attention_mask, pad_token_id)
+        sampling = (bool(do_sample), float(temperature), int(top_k or 0), float(top_p), int(seed))
+        self._select_and_advance_after_prefill(st, cache, sampling, eos_token_id, pad_token_id)
+        graph = self._graph_for(st, cache, sampling, eos_token_id, pad_token_id)
+        return EngineStream(self, st, cache, sampling, eos_token_id, pad_token_id, graph, S + 1)
+
+
+class EngineStream:
+    """Handle of one in-flight request batch: one `step()` = one token per row, result on the host."""
+
+    def __init__(self, engine: B200Engine, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int,
+                 pad: int, graph: Optional[torch.cuda.CUDAGraph], produced_upto: int):
+        self.engine, self.st, self.cache = engine, st, cache
+        self.sampling, self.eos, self.pad, self.graph = sampling, eos, pad, graph
+        self.length = produced_upto
+        self.host_tok = torch.empty(st.B, dtype=torch.int32).pin_memory()
+        self.host_tok.copy_(st.ids)                       # first token (from the prefill)
+        self.h2d_bytes = st.B * 4
+        self.d2h_bytes = st.B * 4
+
+    def last_tokens(self) -> torch.Tensor:
+        return self.host_tok
+
+    def step(self, feed: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Advance every row by one token.  `feed` (pinned int32 [B] on the host) overrides the input
+        token of this step — the interactive case where the host owns the sequence; otherwise the token
+        selected on the device in the previous step is used.  Returns the new tokens in pinned memory."""
+        if self.length >= self.st.max_len:
+            raise RuntimeError("stream is at max_length")
+        if feed is not None:
+            self.st.ids.copy_(feed, non_blocking=True)
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self.engine._decode_step(self.st, self.cache, self.sampling, self.eos, self.pad)
+        self.host_tok.copy_(self.st.ids, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        self.length += 1
+        return self.host_tok
+
+    def sequences(self) -> torch.Tensor:
+        return self.st.sequences[:, :self.length].to(torch.long)

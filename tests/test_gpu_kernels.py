@@ -1,0 +1,208 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 statement of the same op."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from jax_llama_b200.models import reference as ref      # noqa: E402
+from jax_llama_b200.ops import kernels as K             # noqa: E402
+
+DEV = "cuda"
+
+
+def rel_err(got: torch.Tensor, want: torch.Tensor) -> float:
+    got, want = got.float().cpu(), want.float().cpu()
+    return ((got - want).abs().max() / (want.abs().max() + 1e-6)).item()
+
+
+def rnd(*shape, scale=1.0, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(torch.bfloat16)
+
+
+def test_library_loads_and_counts_launches():
+    from jax_llama_b200.ops import _lib
+    assert _lib.lib().jl_version() == 100
+    before = _lib.launch_count()
+    K.swiglu(rnd(4, 64).to(DEV))
+    assert _lib.launch_count() == before + 1
+
+
+def test_embed():
+    table = rnd(1000, 256)
+    ids = torch.tensor([0, 5, 999, 17, -1, 5000])
+    got = K.embed(ids.to(DEV), table.to(DEV))
+    want = table[ids.clamp(0, 999)]
+    assert torch.equal(got.cpu(), want)
+
+
+@pytest.mark.parametrize("H", [256, 4096, 5120, 8192])
+def test_rmsnorm(H):
+    x, w, d = rnd(7, H, seed=1), rnd(H, seed=2) * 0.1 + 1, rnd(7, H, seed=3)
+    want = ref.rms_norm(x.float(), w.float(), 1e-5)
+    got = K.rmsnorm(x.to(DEV), w.to(DEV), 1e-5)
+    assert rel_err(got, want) < 1e-2
+    xd = x.to(DEV).clone()
+    got2 = K.rmsnorm(xd, w.to(DEV), 1e-5, delta=d.to(DEV))
+    s = (x.float() + d.float()).to(torch.bfloat16)
+    assert torch.equal(xd.cpu(), s)                                     # residual stream updated in place
+    assert rel_err(got2, ref.rms_norm(s.float(), w.float(), 1e-5)) < 1e-2
+
+
+@pytest.mark.parametrize("nh,nkv,hd", [(8, 2, 128), (4, 4, 64)])
+def test_rope_kv_write(nh, nkv, hd):
+    B, S, T = 2, 5, 16
+    qkv = rnd(B * S, (nh + 2 * nkv) * hd, seed=4)
+    cos, sin = ref.rope_cos_sin(hd, 64, 10000.0)
+    pad = torch.tensor([0, 2], dtype=torch.int32)
+    clen = torch.tensor([3], dtype=torch.int32)
+    kc, vc = torch.zeros(B, nkv, T, hd, dtype=torch.bfloat16), torch.zeros(B, nkv, T, hd, dtype=torch.bfloat16)
+    want_qkv = qkv.clone()
+    K.rope_kv_write(want_qkv, kc, vc, cos, sin, B, S, nh, nkv, hd, cache_len=clen, pad_left=pad)   # CPU statement
+    # the CPU statement itself against the complex-number oracle
+    x = qkv.view(B, S, nh + 2 * nkv, hd)
+    pos = (3 + torch.arange(S)[None] - pad[:, None].long()).clamp(min=0)
+    f = ref.precompute_freqs_cis(hd, 64)[pos]
+    oq, ok = ref.apply_rotary_emb(x[:, :, :nh].float(), x[:, :, nh:nh + nkv].float(), f)
+    assert rel_err(want_qkv.view(B, S, -1, hd)[:, :, :nh], oq) < 1e-2
+    assert rel_err(kc[:, :, 3:8].transpose(1, 2), ok) < 1e-2
+    g_qkv, gk, gv = qkv.to(DEV), torch.zeros_like(kc).to(DEV), torch.zeros_like(vc).to(DEV)
+    K.rope_kv_write(g_qkv, gk, gv, cos.to(DEV), sin.to(DEV), B, S, nh, nkv, hd, cache_len=clen.to(DEV),
+                    pad_left=pad.to(DEV))
+    assert rel_err(g_qkv, want_qkv) < 1e-2 and rel_err(gk, kc) < 1e-2 and torch.equal(gv.cpu(), vc)
+    assert gk[:, :, :3].abs().sum() == 0 and gk[:, :, 8:].abs().sum() == 0
+    # explicit positions + separate q buffer
+    q_out = torch.zeros(B * S, nh * hd, dtype=torch.bfloat16, device=DEV)
+    g2 = qkv.to(DEV)
+    K.rope_kv_write(g2, gk, gv, cos.to(DEV), sin.to(DEV), B, S, nh, nkv, hd, cache_len=clen.to(DEV),
+                    positions=pos.reshape(-1).to(DEV), q_out=q_out)
+    assert rel_err(q_out.view(B, S, nh, hd), want_qkv.view(B, S, -1, hd)[:, :, :nh]) < 1e-2
+    assert torch.equal(g2.cpu(), qkv)                                   # untouched when q_out is given
+
+
+@pytest.mark.parametrize("interleaved", [True, False])
+def test_swiglu(interleaved):
+    x = rnd(9, 2 * 768, seed=5)
+    assert rel_err(K.swiglu(x.to(DEV), interleaved), K.swiglu(x.float(), interleaved)) < 1e-2
+
+
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("N,K_", [(512, 256), (1536, 4096), (4096, 14336), (1000, 520)])
+def test_gemv_modes(M, N, K_):
+    x, w = rnd(M, K_, seed=6), rnd(N, K_, scale=0.05, seed=7)
+    g = rnd(K_, seed=8) * 0.1 + 1
+    res = rnd(M, N, seed=9)
+    xd, wd = x.to(DEV), w.to(DEV)
+    for norm in (None, g):
+        nd = None if norm is None else norm.to(DEV)
+        want = K.linear(x, w, norm_w=norm, eps=1e-5)
+        assert rel_err(K.linear(xd, wd, norm_w=nd, eps=1e-5, force="gemv"), want) < 1.5e-2
+    want = K.linear(x, w, residual=res, mode=K.RESIDUAL)
+    assert rel_err(K.linear(xd, wd, residual=res.to(DEV), mode=K.RESIDUAL, force="gemv"), want) < 1.5e-2
+    want = K.linear(x, w, norm_w=g, mode=K.SWIGLU)
+    assert rel_err(K.linear(xd, wd, norm_w=g.to(DEV), mode=K.SWIGLU, force="gemv"), want) < 2e-2
+    want = K.linear(x, w, out_f32=True)
+    got = K.linear(xd, wd, out_f32=True, force="gemv")
+    assert got.dtype == torch.float32 and rel_err(got, want) < 1e-3
+
+
+@pytest.mark.parametrize("M,N,K_", [
+    (128, 256, 64), (128, 128, 256), (256, 512, 512),        # single / few tiles, normal orientation... (M>128)
+    (300, 1000, 520), (2048, 6144, 4096), (1024, 4096, 14336),
+    (16, 256, 256), (9, 512, 4096), (32, 1536, 4096), (64, 4096, 1024), (100, 1000, 520), (128, 28672, 4096)])
+def test_gemm_tcgen05(M, N, K_):
+    x, w = rnd(M, K_, seed=10), rnd(N, K_, scale=0.05, seed=11)
+    want = x.float() @ w.float().t()
+    got = K.linear(x.to(DEV), w.to(DEV), force="gemm")
+    assert rel_err(got, want) < 1e-2
+    got32 = K.linear(x.to(DEV), w.to(DEV), out_f32=True, force="gemm")
+    assert rel_err(got32, want) < 2e-3
+
+
+@pytest.mark.parametrize("M", [24, 384])
+def test_gemm_epilogues(M):
+    N, K_ = 1024, 512
+    x, w, res = rnd(M, K_, seed=12), rnd(N, K_, scale=0.05, seed=13), rnd(M, N, seed=14)
+    xd, wd = x.to(DEV), w.to(DEV)
+    want = K.linear(x, w, residual=res, mode=K.RESIDUAL)
+    r = res.to(DEV).clone()
+    got = K.linear(xd, wd, residual=r, mode=K.RESIDUAL, out=r, force="gemm")      # in place on the residual
+    assert rel_err(got, want) < 1.5e-2
+    want = K.linear(x, w, mode=K.SWIGLU)
+    assert rel_err(K.linear(xd, wd, mode=K.SWIGLU, force="gemm"), want) < 2e-2
+    g = rnd(K_, seed=15) * 0.1 + 1
+    want = K.linear(x, w, norm_w=g)
+    assert rel_err(K.linear(xd, wd, norm_w=g.to(DEV), force="gemm"), want) < 1.5e-2
+
+
+@pytest.mark.parametrize("nh,nkv,hd", [(8, 8, 128), (8, 2, 128), (8, 1, 128), (4, 2, 64), (16, 8, 128)])
+@pytest.mark.parametrize("B,length,splits", [(1, 1, 1), (2, 77, 1), (2, 700, 4), (3, 2049, 7)])
+def test_decode_attention(nh, nkv, hd, B, length, splits):
+    T = length + 5
+    q = rnd(B, nh, hd, seed=16)
+    kc, vc = rnd(B, nkv, T, hd, seed=17), rnd(B, nkv, T, hd, seed=18)
+    pad = torch.tensor([0, 3, 0][:B], dtype=torch.int32).clamp(max=length - 1)
+    clen = torch.tensor([length - 1], dtype=torch.int32)
+    want = K.decode_attn(q.float(), kc.float(), vc.float(), clen, pad)
+    scratch = torch.empty(B * nh * splits * (hd + 2), dtype=torch.float32, device=DEV) if splits > 1 else None
+    got = K.decode_attn(q.to(DEV), kc.to(DEV), vc.to(DEV), clen.to(DEV), pad.to(DEV), splits=splits, scratch=scratch)
+    assert rel_err(got, want) < 1.5e-2
+    # q living inside a wider buffer (batch pitch > nh*hd)
+    wide = torch.zeros(B, nh + 2 * nkv, hd, dtype=torch.bfloat16)
+    wide[:, :nh] = q
+    got2 = K.decode_attn(wide.to(DEV)[:, :nh], kc.to(DEV), vc.to(DEV), clen.to(DEV), pad.to(DEV), splits=splits,
+                         scratch=scratch)
+    assert rel_err(got2, want) < 1.5e-2
+
+
+def test_decode_attention_plan():
+    splits, scratch = K.decode_attn_plan(1, 32, 8, 128, 2304, torch.device(DEV))
+    assert 1 <= splits <= 64 and (scratch is None) == (splits == 1)
+
+
+def test_argmax_and_topk():
+    g = torch.Generator().manual_seed(19)
+    logits = torch.randn(3, 128256, generator=g)
+    logits[1, 77] = logits[1, 99] = 50.0                      # tie → lowest index
+    d = logits.to(DEV)
+    assert K.argmax(d).cpu().tolist() == [int(logits[0].argmax()), 77, int(logits[2].argmax())]
+    for k in (1, 50, 64):
+        v, i = K.topk_candidates(d, k, idx_offset=1000)
+        wv, wi = torch.topk(logits, k, dim=-1)
+        assert torch.equal(v.cpu(), wv)
+        assert torch.equal(torch.sort(i.cpu() - 1000, -1).values[0], torch.sort(wi, -1).values[0].to(torch.int32))
+    v, i = K.topk_candidates(d[:, :40].contiguous(), 50)     # fewer entries than k → padded with -inf / -1
+    assert (i[:, 40:] == -1).all() and torch.isinf(v[:, 40:]).all()
+
+
+def test_sampling_distribution_and_greedy():
+    p = torch.tensor([0.5, 0.25, 0.15, 0.07, 0.03])
+    B = 4096
+    logits = torch.log(p)[None].repeat(B, 1).contiguous()
+    v, i = K.topk_candidates(logits.to(DEV), 5)
+    step = torch.zeros(1, dtype=torch.int32, device=DEV)
+    tok = K.sample_candidates(v, i, top_k=5, top_p=1.0, temperature=1.0, seed=1, step=step)
+    freq = torch.bincount(tok.cpu().long(), minlength=5).float() / B
+    assert torch.allclose(freq, p, atol=0.03)
+    tok = K.sample_candidates(v, i, top_k=5, top_p=0.7, temperature=1.0, seed=2, step=step)   # keeps {0,1}
+    freq = torch.bincount(tok.cpu().long(), minlength=5).float() / B
+    assert freq[2:].sum() == 0 and abs(freq[0] - 2 / 3) < 0.03
+    tok = K.sample_candidates(v, i, top_k=3, top_p=1.0, temperature=0.5, seed=3, step=step)
+    freq = torch.bincount(tok.cpu().long(), minlength=5).float() / B
+    want = torch.tensor([0.25, 0.0625, 0.0225]) / 0.335
+    assert freq[3:].sum() == 0 and torch.allclose(freq[:3], want, atol=0.03)
+    a = K.sample_candidates(v, i, top_k=5, seed=7, step=step)
+    b = K.sample_candidates(v, i, top_k=5, seed=7, step=step)
+    assert torch.equal(a, b)                                                  # counter-based RNG: repeatable
+    step.fill_(1)
+    assert not torch.equal(a, K.sample_candidates(v, i, top_k=5, seed=7, step=step))
+    assert (K.sample_candidates(v, i, top_k=5, temperature=0.0) == 0).all()   # greedy
+    # cross-rank merge: two vocab shards' candidate lists give the same answer as the full row
+    full = torch.randn(2, 1000, generator=torch.Generator().manual_seed(5))
+    va, ia = K.topk_candidates(full[:, :500].contiguous().to(DEV), 8, idx_offset=0)
+    vb, ib = K.topk_candidates(full[:, 500:].contiguous().to(DEV), 8, idx_offset=500)
+    vals, idx = torch.stack([va, vb]), torch.stack([ia, ib])
+    tok = K.sample_candidates(vals, idx, n_lists=2, top_k=8, temperature=0.0)
+    assert tok.cpu().tolist() == full.argmax(-1).tolist()
