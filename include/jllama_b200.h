@@ -66,6 +66,13 @@ int jl_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
                    const int* pad_left, void* scratch, void* out, int B, int nh, int nkv, int hd, int T,
                    int n_new, float scale, int splits, int q_bstride, void* stream);
 
+/* model.py:236-288 at S>1 — causal flash attention of S new tokens per row (cache slots start..start+S,
+ * already appended) on tcgen05: q [B*S, nh*hd] rotated, caches [B][nkv][T][hd], out [B*S, nh*hd].
+ * Keys [pad_left[b], slot of the query] are visible.  head_dim 128 only.  cache_len_ptr is reserved. */
+int jl_flash_prefill(const void* q, const void* k_cache, const void* v_cache, const int* cache_len_ptr,
+                     const int* pad_left, void* out, int B, int S, int nh, int nkv, int hd, int T, int start,
+                     float scale, void* stream);
+
 /* generation.py:28-41 (HF warpers + categorical/argmax) — logits fp32 [B, ld] (V valid columns). */
 int jl_argmax(const float* logits, int B, int V, int ld, int idx_offset, float* out_val, int* out_idx,
               void* stream);

@@ -11,6 +11,7 @@ run basic "library or embed or rmsnorm or rope or swiglu" tests/test_gpu_kernels
 run gemv "gemv" tests/test_gpu_kernels.py
 run gemm "gemm" tests/test_gpu_kernels.py
 run attn "decode_attention" tests/test_gpu_kernels.py
+run flash "flash" tests/test_gpu_kernels.py
 run sampling "argmax or sampling" tests/test_gpu_kernels.py
 run engine "" tests/test_gpu_engine.py
 for f in tests/test_gpu_*.py; do
