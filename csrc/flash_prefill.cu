@@ -75,7 +75,9 @@ flash_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
   const int q_hi = min(q0 + FA_BM, p.S) - 1;                 // last valid query row of the tile
   const int first_tile = pad / FA_BN;
   const int last_tile = (p.start + q_hi) / FA_BN;
-  const int n_tiles = last_tile - first_tile + 1;
+  // a tile whose queries are all left padding sees no key at all: n_tiles <= 0, every role skips its
+  // loop and the epilogue writes zeros (those rows are don't-care)
+  const int n_tiles = last_tile - first_tile + 1 > 0 ? last_tile - first_tile + 1 : 0;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -110,7 +112,7 @@ flash_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
         tc::mma_commit(s_full(j & 1));
       };
       tc::mbar_wait(q_full, 0);
-      issue_s(0);
+      if (n_tiles > 0) issue_s(0);
       for (int j = 0; j < n_tiles; ++j) {
         if (j + 1 < n_tiles) issue_s(j + 1);           // tensor core computes S_{j+1} during softmax_j
         tc::mbar_wait(p_full, j & 1);
