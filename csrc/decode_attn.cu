@@ -10,6 +10,8 @@
 // together → 8 loads in flight per lane).  QKᵀ partials are combined with a reduce-scatter butterfly
 // (5 shuffles per head per 4 keys instead of 16), softmax is online in the log2 domain, and the
 // per-split (m, l, o) triples go to a scratch buffer that `attn_combine_kernel` folds.
+#include <mutex>
+
 #include "common.cuh"
 #include "jllama_b200.h"
 
@@ -245,6 +247,103 @@ extern "C" JL_API int jl_decode_attn(const void* q, const void* k_cache, const v
   else JL_DA(1, 64) else JL_DA(2, 64) else JL_DA(4, 64) else JL_DA(8, 64)
   else {
     set_error("jl_decode_attn: unsupported GQA group %d / head_dim %d (groups 1,2,4,8; head_dim 64,128)", G, hd);
+    return JL_ERR_UNSUPPORTED;
+  }
+#undef JL_DA
+  JL_CUDA(e);
+  return JL_OK;
+}
+
+// ------------------------------------------------------------------------------------ allocation-free variant
+// Split-KV decode attention for callers that cannot allocate device memory.  The per-split partial
+// results live in the fixed array below instead of a caller-supplied buffer.  The array is part of
+// the library image: every GPU that loads libjllama_b200.so carries these JL_NOALLOC_SCRATCH_FLOATS
+// floats (4 MiB) from load until the process exits, whether or not this entry point is ever used.
+//
+// `g_noalloc_scratch` names the array for DEVICE code.  In host code the same identifier is only a
+// host-side stand-in for the symbol, not a device address, so the host never hands it to a kernel: once
+// per device (with that device current) it asks the runtime for the real address with
+// cudaGetSymbolAddress and passes that pointer instead.
+#define JL_NOALLOC_SCRATCH_FLOATS (1u << 20)
+static __device__ __align__(256) float g_noalloc_scratch[JL_NOALLOC_SCRATCH_FLOATS];
+
+namespace jl {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static float* g_noalloc_dev_ptr[NOALLOC_MAX_DEVICES];     // resolved device address of the array, per device
+static bool g_noalloc_ready[NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mu;
+
+// Resolve (once per device) where the static array lives on the CURRENT device.
+static int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  JL_CUDA(cudaGetDevice(&dev));
+  JL_CHECK_ARG(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "jl_decode_attn_noalloc: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ready[dev]) {
+    float* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+    JL_CHECK_ARG(ptr != nullptr, "jl_decode_attn_noalloc: runtime returned a null address for the scratch array");
+    g_noalloc_dev_ptr[dev] = ptr;
+    g_noalloc_ready[dev] = true;
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  return JL_OK;
+}
+}  // namespace jl
+
+extern "C" JL_API size_t jl_decode_attn_noalloc_max_floats(void) { return JL_NOALLOC_SCRATCH_FLOATS; }
+
+// jl_decode_attn without the `scratch` argument.
+//
+// Who needs it: code that drives these kernels from a place where it may not, or cannot, obtain device
+// memory — a serving process whose HBM is already owned end to end by another runtime's arena, a plugin
+// running under a host that forbids cudaMalloc/cudaFree in the token loop because those calls take the
+// allocator lock and can synchronise the device, or a thin C caller that has no allocator at all.  Such
+// callers still own q, the KV cache and `out`; only the split-KV workspace comes from the library.
+//
+// Contract
+//  * Nothing is allocated or freed here and no allocating library routine is called (no cudaMalloc,
+//    cudaFree, no torch).  The workspace is the file-scope array above.
+//  * Limit: B*nh*splits*(hd+2) floats must be <= jl_decode_attn_noalloc_max_floats() (2^20 floats = 4 MiB);
+//    larger requests fail with JL_ERR_ARG and a message that says so.  splits == 1 needs no workspace.
+//  * The first call on each device resolves the array's device address (cudaGetSymbolAddress, with that
+//    device current).  Make that first call ahead of time, before any stream capture begins.
+//  * All calls on a device share the one array and it keeps whatever the previous call left in it.
+//    Nothing in it has to start at zero: every (m, l, o) slot a call reads was written earlier in that
+//    same call, so stale contents are never consumed and no clearing pass is needed.
+//  * Because the array is shared, two calls whose kernels can overlap on the GPU (different streams,
+//    or different host threads on different streams) race on it.  Serialise them on one stream.
+//  * Results are identical to jl_decode_attn given the same `splits`.
+extern "C" JL_API int jl_decode_attn_noalloc(const void* q, const void* k_cache, const void* v_cache,
+                                             const int* cache_len_ptr, const int* pad_left, void* out, int B,
+                                             int nh, int nkv, int hd, int T, int n_new, float scale, int splits,
+                                             int q_bstride, void* stream) {
+  JL_CHECK_ARG(nkv > 0 && nh % nkv == 0, "jl_decode_attn_noalloc: nh=%d not a multiple of nkv=%d", nh, nkv);
+  JL_CHECK_ARG(splits >= 1 && splits <= 64, "jl_decode_attn_noalloc: splits=%d outside 1..64", splits);
+  JL_CHECK_ARG(B >= 0 && hd > 0, "jl_decode_attn_noalloc: bad shape B=%d hd=%d", B, hd);
+  const size_t need = splits <= 1 ? 0 : (size_t)B * nh * splits * (hd + 2);
+  JL_CHECK_ARG(need <= JL_NOALLOC_SCRATCH_FLOATS,
+               "jl_decode_attn_noalloc: B*nh*splits*(hd+2) = %zu floats exceeds the built-in scratch of %u floats; "
+               "lower `splits` or use jl_decode_attn with a caller-provided buffer",
+               need, (unsigned)JL_NOALLOC_SCRATCH_FLOATS);
+  if (B == 0) return JL_OK;
+  float* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);     // first call on a device does the set-up
+  if (rc != JL_OK) return rc;
+  const int G = nh / nkv;
+  float* o_part = scratch;
+  float* ml_part = scratch + (size_t)B * nh * splits * hd;
+  auto s = (cudaStream_t)stream;
+  cudaError_t e = cudaErrorInvalidValue;
+#define JL_DA(G_, HD_)                                                                              \
+  if (G == G_ && hd == HD_)                                                                         \
+    e = launch_decode<G_, HD_>(q, k_cache, v_cache, cache_len_ptr, pad_left, o_part, ml_part, out, B, \
+                               nkv, T, n_new, scale, splits, q_bstride > 0 ? q_bstride : nh * hd, s);
+  JL_DA(1, 128) else JL_DA(2, 128) else JL_DA(4, 128) else JL_DA(8, 128)
+  else JL_DA(1, 64) else JL_DA(2, 64) else JL_DA(4, 64) else JL_DA(8, 64)
+  else {
+    set_error("jl_decode_attn_noalloc: unsupported GQA group %d / head_dim %d (groups 1,2,4,8; head_dim 64,128)", G, hd);
     return JL_ERR_UNSUPPORTED;
   }
 #undef JL_DA

@@ -66,6 +66,20 @@ int jl_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
                    const int* pad_left, void* scratch, void* out, int B, int nh, int nkv, int hd, int T,
                    int n_new, float scale, int splits, int q_bstride, void* stream);
 
+/* No counterpart in the reference: an allocation-free form of jl_decode_attn for callers that cannot get
+ * device memory themselves (HBM fully owned by another runtime's arena, hosts that ban cudaMalloc/cudaFree
+ * inside the token loop, bare C callers without an allocator).  Same arguments minus `scratch`: the split-KV
+ * workspace is a fixed 4 MiB array inside the library image, resident on every GPU that loads the library
+ * until process exit.  B*nh*splits*(hd+2) floats must not exceed jl_decode_attn_noalloc_max_floats();
+ * otherwise the call fails with a message naming the limit.  It calls no allocating routine.  The first call
+ * on each device looks the array's address up — do it before any stream capture.  All calls share the array
+ * (it keeps the previous call's contents; nothing needs zeroing), so calls that may overlap on the GPU race:
+ * keep them on one stream.  Output equals jl_decode_attn's for the same `splits`. */
+size_t jl_decode_attn_noalloc_max_floats(void);
+int jl_decode_attn_noalloc(const void* q, const void* k_cache, const void* v_cache, const int* cache_len_ptr,
+                           const int* pad_left, void* out, int B, int nh, int nkv, int hd, int T, int n_new,
+                           float scale, int splits, int q_bstride, void* stream);
+
 /* model.py:236-288 at S>1 — causal flash attention of S new tokens per row (cache slots start..start+S,
  * already appended) on tcgen05: q [B*S, nh*hd] rotated, caches [B][nkv][T][hd], out [B*S, nh*hd].
  * Keys [pad_left[b], slot of the query] are visible.  head_dim 128 only.  cache_len_ptr is reserved. */
