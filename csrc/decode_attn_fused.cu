@@ -1,0 +1,317 @@
+// One-launch decode attention: RoPE(q, k_new) + KV-cache append + split-KV GQA attention + split merge.
+//
+// Replaces three launches of the unfused path (rope_kv_kernel → decode_attn_kernel → attn_combine_kernel)
+// per layer; at batch 1 those launches cost more than the 8 MB of K/V they move.  Differences from
+// decode_attn.cu:
+//   * q and the new token's k, v are read straight from the fused qkv activation; the rotation is applied
+//     in registers from the fp32 cos/sin table (position = cache_len − pad_left[b]);
+//   * the new token is appended to the cache by split 0 and folded into its online softmax from registers,
+//     so the streamed range is [pad_left, cache_len) and nothing written in this launch is re-read;
+//   * many more, shorter splits (64 keys each at 2k context) to cover the load latency with parallelism;
+//   * the last CTA of each (batch, kv-head) to finish — found with an atomic ticket — merges the partial
+//     (m, l, o) triples, so there is no separate combine kernel.  The ticket counter is reset by that CTA.
+// Reference semantics: /root/reference/jax_llama/model.py:201-300 at S = 1.
+#include "common.cuh"
+#include "jllama_b200.h"
+
+namespace jl {
+
+constexpr int DF_WARPS = 4;
+constexpr int DF_KPI = 4;
+
+struct FusedAttnParams {
+  const __nv_bfloat16* qkv;      // [B, (nh + 2 nkv) · hd], not rotated
+  __nv_bfloat16* kc;             // [B][nkv][T][hd]
+  __nv_bfloat16* vc;
+  const float* cos_t;            // [max_pos, hd/2]
+  const float* sin_t;
+  const int* cache_len_ptr;
+  const int* pad_left;
+  float* o_part;                 // [B·nh][splits][hd]
+  float* ml_part;                // [B·nh][splits][2]
+  int* tickets;                  // [B·nkv], zero on entry, zero on exit
+  __nv_bfloat16* out;            // [B, nh·hd]
+  int nkv, T, max_pos, splits;
+  float scale_log2;
+};
+
+template <int G, int HD>
+__global__ void __launch_bounds__(DF_WARPS * 32) decode_attn_fused_kernel(const FusedAttnParams p) {
+  constexpr int LPK = HD / 8;
+  constexpr int GPW = 32 / LPK;
+  constexpr int NG = DF_WARPS * GPW;
+  constexpr int KEYS_PER_ITER = NG * DF_KPI;
+  __shared__ float s_o[NG][G][HD];
+  __shared__ float s_ml[NG][G][2];
+  __shared__ int s_last;
+
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+  const int nh = p.nkv * G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lig = lane % LPK;
+  const int gid = warp * GPW + lane / LPK;
+  const int group_base = lane - lig;
+  const int kidx = ((lig / (LPK / 2)) & 1) * 2 + ((lig / (LPK / 4)) & 1);
+
+  int len = *p.cache_len_ptr;                          // slots already filled; the new token takes slot `len`
+  len = len > p.T ? p.T : len;
+  const int first = p.pad_left ? p.pad_left[b] : 0;
+  const int valid = len - first > 0 ? len - first : 0;
+  int pos = len - first;
+  pos = pos < 0 ? 0 : (pos >= p.max_pos ? p.max_pos - 1 : pos);
+  int chunk = (valid + p.splits - 1) / p.splits;
+  chunk = ((chunk + KEYS_PER_ITER - 1) / KEYS_PER_ITER) * KEYS_PER_ITER;
+  const int lo = first + split * chunk;
+  const int hi = lo + chunk < len ? lo + chunk : len;
+
+  // rotation factors of this lane's 4 pairs
+  const float4 cs4 = __ldg(reinterpret_cast<const float4*>(p.cos_t) + (size_t)pos * LPK + lig);
+  const float4 sn4 = __ldg(reinterpret_cast<const float4*>(p.sin_t) + (size_t)pos * LPK + lig);
+  const float cs[4] = {cs4.x, cs4.y, cs4.z, cs4.w}, sn[4] = {sn4.x, sn4.y, sn4.z, sn4.w};
+  const __nv_bfloat16* row = p.qkv + (size_t)b * (nh + 2 * p.nkv) * HD;
+
+  float qf[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const uint4 a = *reinterpret_cast<const uint4*>(row + (size_t)(kvh * G + g) * HD + lig * 8);
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float re = bf16_lo(aw[j]), im = bf16_hi(aw[j]);
+      // round the rotated q to bf16 like the unfused path does, then fold the softmax scale in
+      const uint32_t r = pack_bf16(re * cs[j] - im * sn[j], re * sn[j] + im * cs[j]);
+      qf[g][2 * j] = bf16_lo(r) * p.scale_log2;
+      qf[g][2 * j + 1] = bf16_hi(r) * p.scale_log2;
+    }
+  }
+  float m[G], l[G], o[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    m[g] = -INFINITY;
+    l[g] = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) o[g][e] = 0.f;
+  }
+
+  const size_t head_off = ((size_t)b * p.nkv + kvh) * (size_t)p.T * HD;
+  const __nv_bfloat16* kbase = p.kc + head_off + lig * 8;
+  const __nv_bfloat16* vbase = p.vc + head_off + lig * 8;
+
+  for (int base = lo; base < hi; base += KEYS_PER_ITER) {          // warp-uniform trip count
+    const int key0 = base + gid * DF_KPI;
+    uint4 kr[DF_KPI], vr[DF_KPI];
+#pragma unroll
+    for (int i = 0; i < DF_KPI; ++i) {
+      const bool ok = key0 + i < hi;
+      kr[i] = ok ? ldg_stream(kbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
+      vr[i] = ok ? ldg_stream(vbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
+    }
+    float part[G][DF_KPI];
+#pragma unroll
+    for (int i = 0; i < DF_KPI; ++i) {
+      const float kf[8] = {bf16_lo(kr[i].x), bf16_hi(kr[i].x), bf16_lo(kr[i].y), bf16_hi(kr[i].y),
+                           bf16_lo(kr[i].z), bf16_hi(kr[i].z), bf16_lo(kr[i].w), bf16_hi(kr[i].w)};
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        float s = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s = fmaf(qf[g][e], kf[e], s);
+        part[g][i] = s;
+      }
+    }
+    float pr[G][DF_KPI];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const bool up = (lig & (LPK / 2)) != 0;
+      float k0 = up ? part[g][2] : part[g][0], k1 = up ? part[g][3] : part[g][1];
+      const float s0 = up ? part[g][0] : part[g][2], s1 = up ? part[g][1] : part[g][3];
+      k0 += __shfl_xor_sync(0xffffffffu, s0, LPK / 2);
+      k1 += __shfl_xor_sync(0xffffffffu, s1, LPK / 2);
+      const bool up2 = (lig & (LPK / 4)) != 0;
+      float s = up2 ? k1 : k0;
+      const float snd = up2 ? k0 : k1;
+      s += __shfl_xor_sync(0xffffffffu, snd, LPK / 4);
+#pragma unroll
+      for (int off = LPK / 8; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+      if (key0 + kidx >= hi) s = -INFINITY;
+      float mx = fmaxf(s, __shfl_xor_sync(0xffffffffu, s, LPK / 2));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, LPK / 4));
+      const float m_new = fmaxf(m[g], mx);
+      const float m_safe = m_new == -INFINITY ? 0.f : m_new;
+      const float corr = exp2f(m[g] - m_safe);
+      const float pe = exp2f(s - m_safe);
+      m[g] = m_new;
+      float psum = 0.f;
+#pragma unroll
+      for (int i = 0; i < DF_KPI; ++i) {
+        pr[g][i] = __shfl_sync(0xffffffffu, pe, group_base + (i >> 1) * (LPK / 2) + (i & 1) * (LPK / 4));
+        psum += pr[g][i];
+      }
+      l[g] = l[g] * corr + psum;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[g][e] *= corr;
+    }
+#pragma unroll
+    for (int i = 0; i < DF_KPI; ++i) {
+      const float vf[8] = {bf16_lo(vr[i].x), bf16_hi(vr[i].x), bf16_lo(vr[i].y), bf16_hi(vr[i].y),
+                           bf16_lo(vr[i].z), bf16_hi(vr[i].z), bf16_lo(vr[i].w), bf16_hi(vr[i].w)};
+#pragma unroll
+      for (int g = 0; g < G; ++g)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[g][e] = fmaf(pr[g][i], vf[e], o[g][e]);
+    }
+  }
+
+  // ---- the new token: rotate k, append k and v to the cache, fold it in from registers (split 0, warp 0)
+  if (split == 0 && warp == 0) {
+    const uint4 ka = *reinterpret_cast<const uint4*>(row + (size_t)(nh + kvh) * HD + lig * 8);
+    const uint4 va = *reinterpret_cast<const uint4*>(row + (size_t)(nh + p.nkv + kvh) * HD + lig * 8);
+    const uint32_t kw[4] = {ka.x, ka.y, ka.z, ka.w};
+    uint32_t kr4[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float re = bf16_lo(kw[j]), im = bf16_hi(kw[j]);
+      kr4[j] = pack_bf16(re * cs[j] - im * sn[j], re * sn[j] + im * cs[j]);
+    }
+    if (gid == 0 && len < p.T) {
+      *reinterpret_cast<uint4*>(p.kc + head_off + (size_t)len * HD + lig * 8) = make_uint4(kr4[0], kr4[1], kr4[2], kr4[3]);
+      *reinterpret_cast<uint4*>(p.vc + head_off + (size_t)len * HD + lig * 8) = va;
+    }
+    const float kf[8] = {bf16_lo(kr4[0]), bf16_hi(kr4[0]), bf16_lo(kr4[1]), bf16_hi(kr4[1]),
+                         bf16_lo(kr4[2]), bf16_hi(kr4[2]), bf16_lo(kr4[3]), bf16_hi(kr4[3])};
+    const float vf[8] = {bf16_lo(va.x), bf16_hi(va.x), bf16_lo(va.y), bf16_hi(va.y),
+                         bf16_lo(va.z), bf16_hi(va.z), bf16_lo(va.w), bf16_hi(va.w)};
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      float s = 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s = fmaf(qf[g][e], kf[e], s);
+#pragma unroll
+      for (int off = LPK / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+      if (gid != 0) s = -INFINITY;                       // counted once, by lane-group 0
+      const float m_new = fmaxf(m[g], s);
+      const float m_safe = m_new == -INFINITY ? 0.f : m_new;
+      const float corr = exp2f(m[g] - m_safe);
+      const float pe = exp2f(s - m_safe);
+      m[g] = m_new;
+      l[g] = l[g] * corr + pe;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[g][e] = o[g][e] * corr + pe * vf[e];
+    }
+  }
+
+  // ---- fold the lane-groups of this CTA
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s_o[gid][g][lig * 8 + e] = o[g][e];
+    if (lig == 0) { s_ml[gid][g][0] = m[g]; s_ml[gid][g][1] = l[g]; }
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < G * HD; idx += DF_WARPS * 32) {
+    const int g = idx / HD, d = idx - g * HD;
+    float M = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < NG; ++j) M = fmaxf(M, s_ml[j][g][0]);
+    const float Ms = M == -INFINITY ? 0.f : M;
+    float acc = 0.f, L = 0.f;
+#pragma unroll
+    for (int j = 0; j < NG; ++j) {
+      const float w = exp2f(s_ml[j][g][0] - Ms);
+      acc += w * s_o[j][g][d];
+      L += w * s_ml[j][g][1];
+    }
+    const int h = kvh * G + g;
+    if (p.splits == 1) {
+      p.out[((size_t)b * nh + h) * HD + d] = __float2bfloat16(L > 0.f ? acc / L : 0.f);
+    } else {
+      const size_t pi = ((size_t)b * nh + h) * p.splits + split;
+      p.o_part[pi * HD + d] = acc;
+      if (d == 0) { p.ml_part[pi * 2] = M; p.ml_part[pi * 2 + 1] = L; }
+    }
+  }
+  if (p.splits == 1) return;
+
+  // ---- ticket: the last CTA of this (b, kv head) merges all splits
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int* t = p.tickets + b * p.nkv + kvh;
+    const int prev = atomicAdd(t, 1);
+    s_last = prev == p.splits - 1;
+    if (s_last) *t = 0;                                  // everyone has arrived: safe to re-arm for the next launch
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int idx = threadIdx.x; idx < G * HD; idx += DF_WARPS * 32) {
+    const int g = idx / HD, d = idx - g * HD;
+    const size_t bh = (size_t)b * nh + kvh * G + g;
+    float M = -INFINITY;
+    for (int s = 0; s < p.splits; ++s) M = fmaxf(M, __ldcg(p.ml_part + (bh * p.splits + s) * 2));
+    const float Ms = M == -INFINITY ? 0.f : M;
+    float acc = 0.f, L = 0.f;
+    for (int s = 0; s < p.splits; ++s) {
+      const float w = exp2f(__ldcg(p.ml_part + (bh * p.splits + s) * 2) - Ms);
+      if (w > 0.f) {
+        acc += w * __ldcg(p.o_part + (bh * p.splits + s) * HD + d);
+        L += w * __ldcg(p.ml_part + (bh * p.splits + s) * 2 + 1);
+      }
+    }
+    p.out[bh * HD + d] = __float2bfloat16(L > 0.f ? acc / L : 0.f);
+  }
+}
+
+}  // namespace jl
+
+using namespace jl;
+
+extern "C" JL_API size_t jl_decode_attn_fused_scratch_bytes(int B, int nh, int nkv, int hd, int splits) {
+  const size_t parts = splits <= 1 ? 0 : (size_t)B * nh * splits * (hd + 2) * sizeof(float);
+  return parts + (size_t)B * nkv * sizeof(int);
+}
+
+extern "C" JL_API int jl_decode_attn_fused_splits(int B, int nkv, int max_len, int num_sms) {
+  if (num_sms <= 0) num_sms = 148;
+  int want = (4 * num_sms + B * nkv - 1) / (B * nkv);
+  const int cap = (max_len + 63) / 64;                   // at least 64 keys per split
+  int s = want < cap ? want : cap;
+  return s < 1 ? 1 : (s > 64 ? 64 : s);
+}
+
+extern "C" JL_API int jl_decode_attn_fused(const void* qkv, void* k_cache, void* v_cache, const float* cos_t,
+                                           const float* sin_t, const int* cache_len_ptr, const int* pad_left,
+                                           void* scratch, void* out, int B, int nh, int nkv, int hd, int T,
+                                           int max_pos, float scale, int splits, void* stream) {
+  JL_CHECK_ARG(nkv > 0 && nh % nkv == 0, "jl_decode_attn_fused: nh=%d not a multiple of nkv=%d", nh, nkv);
+  JL_CHECK_ARG(splits >= 1 && splits <= 64, "jl_decode_attn_fused: splits=%d outside 1..64", splits);
+  JL_CHECK_ARG(scratch != nullptr && cache_len_ptr != nullptr, "jl_decode_attn_fused: scratch and cache_len are required");
+  if (B == 0) return JL_OK;
+  const int G = nh / nkv;
+  FusedAttnParams p{};
+  p.qkv = (const __nv_bfloat16*)qkv; p.kc = (__nv_bfloat16*)k_cache; p.vc = (__nv_bfloat16*)v_cache;
+  p.cos_t = cos_t; p.sin_t = sin_t; p.cache_len_ptr = cache_len_ptr; p.pad_left = pad_left;
+  const size_t part_floats = splits <= 1 ? 0 : (size_t)B * nh * splits * hd;
+  p.o_part = (float*)scratch;
+  p.ml_part = p.o_part + part_floats;
+  p.tickets = (int*)(p.ml_part + (splits <= 1 ? 0 : (size_t)B * nh * splits * 2));
+  p.out = (__nv_bfloat16*)out;
+  p.nkv = nkv; p.T = T; p.max_pos = max_pos; p.splits = splits;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  auto s = (cudaStream_t)stream;
+  cudaError_t e = cudaErrorInvalidValue;
+#define JL_DF(G_, HD_) \
+  if (G == G_ && hd == HD_) e = launch_pdl(decode_attn_fused_kernel<G_, HD_>, dim3(splits, nkv, B), dim3(DF_WARPS * 32), 0, s, p);
+  JL_DF(1, 128) else JL_DF(2, 128) else JL_DF(4, 128) else JL_DF(8, 128)
+  else JL_DF(1, 64) else JL_DF(2, 64) else JL_DF(4, 64) else JL_DF(8, 64)
+  else {
+    set_error("jl_decode_attn_fused: unsupported GQA group %d / head_dim %d (groups 1,2,4,8; head_dim 64,128)", G, hd);
+    return JL_ERR_UNSUPPORTED;
+  }
+#undef JL_DF
+  JL_CUDA(e);
+  return JL_OK;
+}

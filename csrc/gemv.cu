@@ -13,8 +13,8 @@
 namespace jl {
 
 constexpr int GEMV_THREADS = 512;   // 16 warps, one persistent CTA per SM
-constexpr int GEMV_R = 2;           // weight rows per warp work-unit (a SwiGLU pair)
-constexpr int GEMV_U = 4;           // 16-byte loads per row per step  → R·U = 8 in flight per lane
+// rows per warp work-unit R (2 = a SwiGLU pair, 1 = finer balance) is a template parameter; each lane keeps
+// R·U = 8 16-byte loads in flight per step
 
 struct GemvParams {
   const __nv_bfloat16* x;         // [M, K]
@@ -28,30 +28,31 @@ struct GemvParams {
 
 enum { MODE_PLAIN = 0, MODE_RESIDUAL = 1, MODE_SWIGLU = 2 };
 
-template <int M, int MODE, bool OUT_F32>
+template <int M, int MODE, bool OUT_F32, int R>
 __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams p) {
+  constexpr int U = 8 / R;        // 16-byte loads per row per step: R·U = 8 loads in flight per lane
   extern __shared__ __align__(16) uint8_t smem_raw[];
   uint4* xs = reinterpret_cast<uint4*>(smem_raw);             // [M][K/8] normalised activations (bf16)
   __shared__ float red[M][GEMV_THREADS / 32];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int K8 = p.K >> 3;
-  const int steps_per_unit = (K8 + 32 * GEMV_U - 1) / (32 * GEMV_U);
-  const int n_units = (p.N + GEMV_R - 1) / GEMV_R;
+  const int steps_per_unit = (K8 + 32 * U - 1) / (32 * U);
+  const int n_units = (p.N + R - 1) / R;
   const int total_warps = gridDim.x * (GEMV_THREADS / 32);
   const int gw = blockIdx.x * (GEMV_THREADS / 32) + warp;     // warps of one CTA take adjacent units
   const uint4* wbase = reinterpret_cast<const uint4*>(p.w);
 
   // flattened (unit, step) iteration for this warp, software-pipelined one step ahead
   int unit = gw, step = 0;
-  uint4 cur[GEMV_R][GEMV_U], nxt[GEMV_R][GEMV_U];
-  auto load = [&](uint4 (&dst)[GEMV_R][GEMV_U], int u, int s) {
+  uint4 cur[R][U], nxt[R][U];
+  auto load = [&](uint4 (&dst)[R][U], int u, int s) {
 #pragma unroll
-    for (int r = 0; r < GEMV_R; ++r) {
-      const int row = u * GEMV_R + r;
+    for (int r = 0; r < R; ++r) {
+      const int row = u * R + r;
 #pragma unroll
-      for (int j = 0; j < GEMV_U; ++j) {
-        const int c = (s * GEMV_U + j) * 32 + lane;
+      for (int j = 0; j < U; ++j) {
+        const int c = (s * U + j) * 32 + lane;
         if (row < p.N && c < K8) dst[r][j] = ldg_stream(wbase + (size_t)row * K8 + c);
         else dst[r][j] = make_uint4(0, 0, 0, 0);
       }
@@ -115,11 +116,11 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
   }
   __syncthreads();
 
-  float acc[M][GEMV_R];
+  float acc[M][R];
 #pragma unroll
   for (int m = 0; m < M; ++m)
 #pragma unroll
-    for (int r = 0; r < GEMV_R; ++r) acc[m][r] = 0.f;
+    for (int r = 0; r < R; ++r) acc[m][r] = 0.f;
 
   while (unit < n_units) {
     // prefetch the following step (possibly of the next unit) before consuming the current one
@@ -128,12 +129,12 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
     if (nunit < n_units) load(nxt, nunit, nstep);
 
 #pragma unroll
-    for (int j = 0; j < GEMV_U; ++j) {
-      const int c = (step * GEMV_U + j) * 32 + lane;
+    for (int j = 0; j < U; ++j) {
+      const int c = (step * U + j) * 32 + lane;
       if (c < K8) {
-        float wf[GEMV_R][8];
+        float wf[R][8];
 #pragma unroll
-        for (int r = 0; r < GEMV_R; ++r) {
+        for (int r = 0; r < R; ++r) {
           const uint4 wv = cur[r][j];
           wf[r][0] = bf16_lo(wv.x); wf[r][1] = bf16_hi(wv.x); wf[r][2] = bf16_lo(wv.y); wf[r][3] = bf16_hi(wv.y);
           wf[r][4] = bf16_lo(wv.z); wf[r][5] = bf16_hi(wv.z); wf[r][6] = bf16_lo(wv.w); wf[r][7] = bf16_hi(wv.w);
@@ -144,7 +145,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
           const float xf[8] = {bf16_lo(a.x), bf16_hi(a.x), bf16_lo(a.y), bf16_hi(a.y),
                                bf16_lo(a.z), bf16_hi(a.z), bf16_lo(a.w), bf16_hi(a.w)};
 #pragma unroll
-          for (int r = 0; r < GEMV_R; ++r)
+          for (int r = 0; r < R; ++r)
 #pragma unroll
             for (int e = 0; e < 8; ++e) acc[m][r] = fmaf(wf[r][e], xf[e], acc[m][r]);
         }
@@ -156,12 +157,12 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
 #pragma unroll
       for (int m = 0; m < M; ++m)
 #pragma unroll
-        for (int r = 0; r < GEMV_R; ++r) acc[m][r] = warp_sum(acc[m][r]);
+        for (int r = 0; r < R; ++r) acc[m][r] = warp_sum(acc[m][r]);
       if (lane == 0) {
-        const int row0 = unit * GEMV_R;
+        const int row0 = unit * R;
 #pragma unroll
         for (int m = 0; m < M; ++m) {
-          if (MODE == MODE_SWIGLU) {
+          if constexpr (MODE == MODE_SWIGLU) {
             // rows (2j, 2j+1) hold (w1_j, w3_j): emit silu(gate)·up; round the two GEMM outputs to bf16
             // first so the result is bit-compatible with the unfused GEMM → SwiGLU sequence
             float g = __bfloat162float(__float2bfloat16(acc[m][0]));
@@ -170,7 +171,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
                 __float2bfloat16(silu(g) * u);
           } else {
 #pragma unroll
-            for (int r = 0; r < GEMV_R; ++r) {
+            for (int r = 0; r < R; ++r) {
               const int row = row0 + r;
               if (row < p.N) {
                 float v = acc[m][r];
@@ -187,23 +188,23 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
 #pragma unroll
       for (int m = 0; m < M; ++m)
 #pragma unroll
-        for (int r = 0; r < GEMV_R; ++r) acc[m][r] = 0.f;
+        for (int r = 0; r < R; ++r) acc[m][r] = 0.f;
     }
 #pragma unroll
-    for (int r = 0; r < GEMV_R; ++r)
+    for (int r = 0; r < R; ++r)
 #pragma unroll
-      for (int j = 0; j < GEMV_U; ++j) cur[r][j] = nxt[r][j];
+      for (int j = 0; j < U; ++j) cur[r][j] = nxt[r][j];
     unit = nunit;
     step = nstep;
   }
 }
 
-template <int M>
+template <int M, int R>
 static cudaError_t gemv_launch(const GemvParams& p, int mode, bool out_f32, int grid, size_t smem,
                                cudaStream_t s) {
 #define JL_GEMV_CASE(MODE_, F32_)                                                              \
   {                                                                                            \
-    auto k = gemv_kernel<M, MODE_, F32_>;                                                      \
+    auto k = gemv_kernel<M, MODE_, F32_, R>;                                                   \
     cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     if (e != cudaSuccess) return e;                                                            \
     return launch_pdl(k, dim3(grid), dim3(GEMV_THREADS), smem, s, p);                          \
@@ -211,8 +212,36 @@ static cudaError_t gemv_launch(const GemvParams& p, int mode, bool out_f32, int 
   if (mode == MODE_PLAIN && !out_f32) JL_GEMV_CASE(MODE_PLAIN, false)
   if (mode == MODE_PLAIN && out_f32) JL_GEMV_CASE(MODE_PLAIN, true)
   if (mode == MODE_RESIDUAL) JL_GEMV_CASE(MODE_RESIDUAL, false)
-  JL_GEMV_CASE(MODE_SWIGLU, false)
+  if constexpr (R == 2) JL_GEMV_CASE(MODE_SWIGLU, false)
+  return cudaErrorInvalidValue;
 #undef JL_GEMV_CASE
+}
+
+// Work-unit shape and grid size.  The kernel is HBM-bound, so what matters is (a) every resident warp
+// gets the same number of units — a warp with one unit more than the others sets the kernel time — and
+// (b) enough bytes stay in flight.  Pick rows-per-unit R ∈ {2, 1} and a grid in [3/4·SMs, SMs] that
+// maximise  units / (waves · grid · warps_per_cta).
+static void gemv_plan(int N, int mode, int num_sms, int* r_out, int* grid_out) {
+  const int wpc = GEMV_THREADS / 32;
+  double best = -1.0;
+  int best_r = 2, best_g = num_sms;
+  for (int r = 2; r >= 1; --r) {
+    if (mode == MODE_SWIGLU && r != 2) break;
+    const int units = (N + r - 1) / r;
+    if (units <= (num_sms * 3 / 4) * wpc) {            // small layer: one unit per warp, as many CTAs as needed
+      const double eff = 1.0 - 0.01 * (2 - r);         // prefer R = 2 on ties
+      if (eff > best) { best = eff; best_r = r; best_g = (units + wpc - 1) / wpc; }
+      continue;
+    }
+    for (int g = num_sms; g >= num_sms * 3 / 4; --g) {
+      const int slots = g * wpc;
+      const int waves = (units + slots - 1) / slots;
+      const double eff = (double)units / ((double)waves * slots) * (0.97 + 0.03 * g / num_sms) - 0.005 * (2 - r);
+      if (eff > best) { best = eff; best_r = r; best_g = g; }
+    }
+  }
+  *r_out = best_r;
+  *grid_out = best_g < 1 ? 1 : best_g;
 }
 
 }  // namespace jl
@@ -231,21 +260,22 @@ extern "C" JL_API int jl_gemv(const void* x, const void* w, const void* norm_w, 
   JL_CHECK_ARG(smem <= 220 * 1024, "jl_gemv: M*K=%d*%d does not fit in shared memory", M, K);
   GemvParams p{(const __nv_bfloat16*)x, (const __nv_bfloat16*)w, (const __nv_bfloat16*)norm_w,
                (const __nv_bfloat16*)residual, out, N, K, eps};
-  const int n_units = (N + GEMV_R - 1) / GEMV_R;
-  int grid = (n_units + GEMV_THREADS / 32 - 1) / (GEMV_THREADS / 32);
   if (num_sms <= 0) num_sms = 148;
-  if (grid > num_sms) grid = num_sms;
+  int r = 2, grid = num_sms;
+  gemv_plan(N, mode, num_sms, &r, &grid);
+  auto s = (cudaStream_t)stream;
   cudaError_t e;
+#define JL_GEMV_M(M_)                                                                   \
+  case M_:                                                                              \
+    e = r == 2 ? gemv_launch<M_, 2>(p, mode, out_f32, grid, smem, s)                    \
+               : gemv_launch<M_, 1>(p, mode, out_f32, grid, smem, s);                   \
+    break;
   switch (M) {
-    case 1: e = gemv_launch<1>(p, mode, out_f32, grid, smem, (cudaStream_t)stream); break;
-    case 2: e = gemv_launch<2>(p, mode, out_f32, grid, smem, (cudaStream_t)stream); break;
-    case 3: e = gemv_launch<3>(p, mode, out_f32, grid, smem, (cudaStream_t)stream); break;
-    case 4: e = gemv_launch<4>(p, mode, out_f32, grid, smem, (cudaStream_t)stream); break;
-    case 5: e = gemv_launch<5>(p, mode, out_f32, grid, smem, (cudaStream_t)stream); break;
-    case 6: e = gemv_launch<6>(p, mode, out_f32, grid, smem, (cudaStream_t)stream); break;
-    case 7: e = gemv_launch<7>(p, mode, out_f32, grid, smem, (cudaStream_t)stream); break;
-    default: e = gemv_launch<8>(p, mode, out_f32, grid, smem, (cudaStream_t)stream); break;
+    JL_GEMV_M(1) JL_GEMV_M(2) JL_GEMV_M(3) JL_GEMV_M(4) JL_GEMV_M(5) JL_GEMV_M(6) JL_GEMV_M(7)
+    default: e = r == 2 ? gemv_launch<8, 2>(p, mode, out_f32, grid, smem, s)
+                        : gemv_launch<8, 1>(p, mode, out_f32, grid, smem, s);
   }
+#undef JL_GEMV_M
   JL_CUDA(e);
   return JL_OK;
 }

@@ -66,6 +66,17 @@ int jl_decode_attn(const void* q, const void* k_cache, const void* v_cache, cons
                    const int* pad_left, void* scratch, void* out, int B, int nh, int nkv, int hd, int T,
                    int n_new, float scale, int splits, int q_bstride, void* stream);
 
+/* model.py:201-300 at S=1 in ONE launch — RoPE of q and of the new token's k, append of (k,v) at slot
+ * *cache_len, split-KV GQA attention over [pad_left[b], *cache_len] and the split merge (last-arriving CTA,
+ * atomic ticket).  qkv [B,(nh+2nkv)*hd] is the un-rotated fused projection; out [B,nh*hd].  `scratch` must
+ * hold jl_decode_attn_fused_scratch_bytes(...) bytes and be ZERO when first used (ticket counters; the kernel
+ * leaves them zero).  *cache_len is not advanced here. */
+size_t jl_decode_attn_fused_scratch_bytes(int B, int nh, int nkv, int hd, int splits);
+int jl_decode_attn_fused_splits(int B, int nkv, int max_len, int num_sms);
+int jl_decode_attn_fused(const void* qkv, void* k_cache, void* v_cache, const float* cos_t, const float* sin_t,
+                         const int* cache_len_ptr, const int* pad_left, void* scratch, void* out, int B, int nh,
+                         int nkv, int hd, int T, int max_pos, float scale, int splits, void* stream);
+
 /* No counterpart in the reference: an allocation-free form of jl_decode_attn for callers that cannot get
  * device memory themselves (HBM fully owned by another runtime's arena, hosts that ban cudaMalloc/cudaFree
  * inside the token loop, bare C callers without an allocator).  Same arguments minus `scratch`: the split-KV

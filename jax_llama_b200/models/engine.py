@@ -202,17 +202,21 @@ class B200Engine:
         for i, l in enumerate(self.layers):
             kc, vc = cache.k[i], cache.v[i]
             qkv = K.linear(x, l.wqkv, norm_w=l.attn_norm, eps=eps, out=ws.qkv if ws else None)
-            q_rot = None
-            if S > 1:       # prefill: rotated q goes to its own dense [B·S, nh·hd] buffer for the flash kernel
-                q_rot = torch.empty((B * S, nh * hd), dtype=qkv.dtype, device=qkv.device)
-            K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
-                            pad_left=cache.pad_left, positions=positions, q_out=q_rot)
-            if S == 1:
-                q = qkv.view(B, nh + 2 * nkv, hd)[:, :nh]          # strided view: q stays inside qkv
-                attn = K.decode_attn(q, kc, vc, cache.len_dev, cache.pad_left, 1,
-                                     ws.splits if ws else 1, ws.scratch if ws else None,
-                                     out=ws.attn if ws else None)
+            if S == 1 and positions is None:
+                # decode: RoPE + KV append + split-KV attention + merge in one launch
+                attn = K.decode_attn_fused(qkv, kc, vc, self.cos, self.sin, cache.len_dev, cache.pad_left, nh, nkv,
+                                           hd, ws.splits if ws else 1, ws.scratch if ws else None,
+                                           out=ws.attn if ws else None)
+            elif S == 1:
+                # explicit position_ids: rotate with the caller's positions, then the unfused attention
+                K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
+                                pad_left=cache.pad_left, positions=positions)
+                attn = K.decode_attn(qkv.view(B, nh + 2 * nkv, hd)[:, :nh], kc, vc, cache.len_dev, cache.pad_left, 1)
             else:
+                # prefill: rotated q goes to its own dense [B·S, nh·hd] buffer for the flash kernel
+                q_rot = torch.empty((B * S, nh * hd), dtype=qkv.dtype, device=qkv.device)
+                K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
+                                pad_left=cache.pad_left, positions=positions, q_out=q_rot)
                 attn = self._prefill_attn(q_rot.view(B, S, nh, hd), kc, vc, start, S, cache).view(B * S, nh * hd)
             x = K.linear(attn, l.wo, residual=x, mode=K.RESIDUAL, out=x)
             h = K.linear(x, l.w13, norm_w=l.ffn_norm, eps=eps, mode=K.SWIGLU, out=ws.mlp if ws else None)
@@ -271,7 +275,7 @@ class B200Engine:
         c, dev = self.config, self.device
         i32 = dict(dtype=torch.int32, device=dev)
         bf = dict(dtype=torch.bfloat16, device=dev)
-        splits, scratch = K.decode_attn_plan(B, self.nh, self.nkv, self.hd, max_len, dev)
+        splits, scratch = K.decode_attn_fused_plan(B, self.nh, self.nkv, self.hd, max_len, dev)
         st = DecodeState(
             B=B, max_len=max_len, ids=torch.zeros(B, **i32), x=torch.zeros(B, c.hidden_size, **bf),
             qkv=torch.zeros(B, (self.nh + 2 * self.nkv) * self.hd, **bf),

@@ -214,6 +214,39 @@ def decode_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
     return out
 
 
+def decode_attn_fused_plan(B: int, nh: int, nkv: int, hd: int, max_len: int, device: torch.device
+                           ) -> Tuple[int, torch.Tensor]:
+    """(splits, zeroed scratch) for `decode_attn_fused` at this shape."""
+    L = _lib.lib()
+    splits = int(L.jl_decode_attn_fused_splits(B, nkv, max_len, num_sms(device)))
+    nbytes = int(L.jl_decode_attn_fused_scratch_bytes(B, nh, nkv, hd, splits))
+    return splits, torch.zeros((nbytes + 3) // 4, dtype=torch.int32, device=device)
+
+
+def decode_attn_fused(qkv: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, cos: torch.Tensor,
+                      sin: torch.Tensor, cache_len: torch.Tensor, pad_left: Optional[torch.Tensor], nh: int,
+                      nkv: int, hd: int, splits: int = 1, scratch: Optional[torch.Tensor] = None,
+                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """RoPE + KV append + GQA decode attention + split merge in one launch.  qkv [B, (nh+2nkv)·hd] is the
+    raw fused projection of the new token; the caches are updated in place at slot `cache_len`."""
+    B = qkv.shape[0]
+    if not qkv.is_cuda:
+        work = qkv.clone()
+        rope_kv_write(work, k_cache, v_cache, cos, sin, B, 1, nh, nkv, hd, cache_len=cache_len, pad_left=pad_left)
+        return decode_attn(work.view(B, nh + 2 * nkv, hd)[:, :nh], k_cache, v_cache, cache_len, pad_left, 1)
+    _bf16c(qkv, "qkv"); _bf16c(k_cache, "k_cache"); _bf16c(v_cache, "v_cache")
+    if scratch is None:
+        splits, scratch = 1, torch.zeros(max(B * nkv, 1), dtype=torch.int32, device=qkv.device)
+    if out is None:
+        out = torch.empty((B, nh * hd), dtype=qkv.dtype, device=qkv.device)
+    _lib.check(_lib.lib().jl_decode_attn_fused(qkv.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+                                               cos.data_ptr(), sin.data_ptr(), cache_len.data_ptr(), _p(pad_left),
+                                               scratch.data_ptr(), out.data_ptr(), B, nh, nkv, hd,
+                                               k_cache.shape[2], cos.shape[0], 1.0 / math.sqrt(hd), splits,
+                                               _stream()), "jl_decode_attn_fused")
+    return out
+
+
 # --------------------------------------------------------------------------- prefill attention
 def prefill_attn_ref(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, start: int, S: int,
                      pad_left: Optional[torch.Tensor]) -> torch.Tensor:

@@ -10,7 +10,8 @@ run() {  # name, pytest -k expression, file
 run basic "library or embed or rmsnorm or rope or swiglu" tests/test_gpu_kernels.py
 run gemv "gemv" tests/test_gpu_kernels.py
 run gemm "gemm" tests/test_gpu_kernels.py
-run attn "decode_attention" tests/test_gpu_kernels.py
+run attn "decode_attention and not fused" tests/test_gpu_kernels.py
+run attnfused "decode_attention_fused" tests/test_gpu_kernels.py
 run flash "flash" tests/test_gpu_kernels.py
 run sampling "argmax or sampling" tests/test_gpu_kernels.py
 run engine "" tests/test_gpu_engine.py

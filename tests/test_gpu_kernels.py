@@ -176,6 +176,28 @@ def test_flash_prefill(B, S, start, nh, nkv, pads):
     assert ((g - w).abs().max() / (w.abs().max() + 1e-6)).item() < 2e-2
 
 
+@pytest.mark.parametrize("nh,nkv,hd", [(8, 2, 128), (8, 8, 128), (8, 1, 128), (4, 2, 64)])
+@pytest.mark.parametrize("B,filled,max_len", [(1, 0, 64), (2, 77, 256), (1, 2048, 2304), (3, 700, 4096)])
+def test_decode_attention_fused(nh, nkv, hd, B, filled, max_len):
+    """RoPE + append + attention + merge in one launch == the three separate CPU statements."""
+    T = max_len
+    qkv = rnd(B, (nh + 2 * nkv) * hd, seed=30)
+    kc, vc = rnd(B, nkv, T, hd, seed=31), rnd(B, nkv, T, hd, seed=32)
+    cos, sin = ref.rope_cos_sin(hd, 2 * max_len, 500000.0)
+    pad = torch.tensor([0, 3, 1][:B], dtype=torch.int32).clamp(max=max(filled - 1, 0))
+    clen = torch.tensor([filled], dtype=torch.int32)
+    kc_ref, vc_ref = kc.float(), vc.float()
+    want = K.decode_attn_fused(qkv.float(), kc_ref, vc_ref, cos, sin, clen, pad, nh, nkv, hd)
+    splits, scratch = K.decode_attn_fused_plan(B, nh, nkv, hd, max_len, torch.device(DEV))
+    gk, gv = kc.to(DEV), vc.to(DEV)
+    for _ in range(2):                                   # twice: the ticket counters must re-arm themselves
+        got = K.decode_attn_fused(qkv.to(DEV), gk, gv, cos.to(DEV), sin.to(DEV), clen.to(DEV), pad.to(DEV), nh, nkv,
+                                  hd, splits, scratch)
+        assert rel_err(got, want) < 1.5e-2
+    assert rel_err(gk[:, :, filled], kc_ref[:, :, filled]) < 1e-2 and rel_err(gv[:, :, filled], vc_ref[:, :, filled]) < 1e-2
+    assert torch.equal(gk[:, :, :filled].cpu(), kc[:, :, :filled]) and (scratch[-B * nkv:] == 0).all()
+
+
 def test_decode_attention_plan():
     splits, scratch = K.decode_attn_plan(1, 32, 8, 128, 2304, torch.device(DEV))
     assert 1 <= splits <= 64 and (scratch is None) == (splits == 1)
