@@ -100,69 +100,81 @@ __global__ void __launch_bounds__(DF_WARPS * 32) decode_attn_fused_kernel(const 
   const __nv_bfloat16* kbase = p.kc + head_off + lig * 8;
   const __nv_bfloat16* vbase = p.vc + head_off + lig * 8;
 
-  for (int base = lo; base < hi; base += KEYS_PER_ITER) {          // warp-uniform trip count
-    const int key0 = base + gid * DF_KPI;
-    uint4 kr[DF_KPI], vr[DF_KPI];
-#pragma unroll
-    for (int i = 0; i < DF_KPI; ++i) {
-      const bool ok = key0 + i < hi;
-      kr[i] = ok ? ldg_stream(kbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
-      vr[i] = ok ? ldg_stream(vbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
-    }
-    float part[G][DF_KPI];
-#pragma unroll
-    for (int i = 0; i < DF_KPI; ++i) {
-      const float kf[8] = {bf16_lo(kr[i].x), bf16_hi(kr[i].x), bf16_lo(kr[i].y), bf16_hi(kr[i].y),
-                           bf16_lo(kr[i].z), bf16_hi(kr[i].z), bf16_lo(kr[i].w), bf16_hi(kr[i].w)};
-#pragma unroll
-      for (int g = 0; g < G; ++g) {
-        float s = 0.f;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) s = fmaf(qf[g][e], kf[e], s);
-        part[g][i] = s;
-      }
-    }
-    float pr[G][DF_KPI];
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      const bool up = (lig & (LPK / 2)) != 0;
-      float k0 = up ? part[g][2] : part[g][0], k1 = up ? part[g][3] : part[g][1];
-      const float s0 = up ? part[g][0] : part[g][2], s1 = up ? part[g][1] : part[g][3];
-      k0 += __shfl_xor_sync(0xffffffffu, s0, LPK / 2);
-      k1 += __shfl_xor_sync(0xffffffffu, s1, LPK / 2);
-      const bool up2 = (lig & (LPK / 4)) != 0;
-      float s = up2 ? k1 : k0;
-      const float snd = up2 ? k0 : k1;
-      s += __shfl_xor_sync(0xffffffffu, snd, LPK / 4);
-#pragma unroll
-      for (int off = LPK / 8; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
-      if (key0 + kidx >= hi) s = -INFINITY;
-      float mx = fmaxf(s, __shfl_xor_sync(0xffffffffu, s, LPK / 2));
-      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, LPK / 4));
-      const float m_new = fmaxf(m[g], mx);
-      const float m_safe = m_new == -INFINITY ? 0.f : m_new;
-      const float corr = exp2f(m[g] - m_safe);
-      const float pe = exp2f(s - m_safe);
-      m[g] = m_new;
-      float psum = 0.f;
+  // one online-softmax update with DF_KPI keys per lane-group (K/V rows already in registers)
+  auto process = [&](const uint4 (&kr)[DF_KPI], const uint4 (&vr)[DF_KPI], const int key0) {
+      float part[G][DF_KPI];
 #pragma unroll
       for (int i = 0; i < DF_KPI; ++i) {
-        pr[g][i] = __shfl_sync(0xffffffffu, pe, group_base + (i >> 1) * (LPK / 2) + (i & 1) * (LPK / 4));
-        psum += pr[g][i];
+        const float kf[8] = {bf16_lo(kr[i].x), bf16_hi(kr[i].x), bf16_lo(kr[i].y), bf16_hi(kr[i].y),
+                             bf16_lo(kr[i].z), bf16_hi(kr[i].z), bf16_lo(kr[i].w), bf16_hi(kr[i].w)};
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          float s = 0.f;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) s = fmaf(qf[g][e], kf[e], s);
+          part[g][i] = s;
+        }
       }
-      l[g] = l[g] * corr + psum;
+      float pr[G][DF_KPI];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) o[g][e] *= corr;
+      for (int g = 0; g < G; ++g) {
+        const bool up = (lig & (LPK / 2)) != 0;
+        float k0 = up ? part[g][2] : part[g][0], k1 = up ? part[g][3] : part[g][1];
+        const float s0 = up ? part[g][0] : part[g][2], s1 = up ? part[g][1] : part[g][3];
+        k0 += __shfl_xor_sync(0xffffffffu, s0, LPK / 2);
+        k1 += __shfl_xor_sync(0xffffffffu, s1, LPK / 2);
+        const bool up2 = (lig & (LPK / 4)) != 0;
+        float s = up2 ? k1 : k0;
+        const float snd = up2 ? k0 : k1;
+        s += __shfl_xor_sync(0xffffffffu, snd, LPK / 4);
+#pragma unroll
+        for (int off = LPK / 8; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        if (key0 + kidx >= hi) s = -INFINITY;
+        float mx = fmaxf(s, __shfl_xor_sync(0xffffffffu, s, LPK / 2));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, LPK / 4));
+        const float m_new = fmaxf(m[g], mx);
+        const float m_safe = m_new == -INFINITY ? 0.f : m_new;
+        const float corr = exp2f(m[g] - m_safe);
+        const float pe = exp2f(s - m_safe);
+        m[g] = m_new;
+        float psum = 0.f;
+#pragma unroll
+        for (int i = 0; i < DF_KPI; ++i) {
+          pr[g][i] = __shfl_sync(0xffffffffu, pe, group_base + (i >> 1) * (LPK / 2) + (i & 1) * (LPK / 4));
+          psum += pr[g][i];
+        }
+        l[g] = l[g] * corr + psum;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[g][e] *= corr;
+      }
+#pragma unroll
+      for (int i = 0; i < DF_KPI; ++i) {
+        const float vf[8] = {bf16_lo(vr[i].x), bf16_hi(vr[i].x), bf16_lo(vr[i].y), bf16_hi(vr[i].y),
+                             bf16_lo(vr[i].z), bf16_hi(vr[i].z), bf16_lo(vr[i].w), bf16_hi(vr[i].w)};
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) o[g][e] = fmaf(pr[g][i], vf[e], o[g][e]);
+      }
+  };
+
+  // UNR iterations' worth of K/V loads are issued back to back before any of them is consumed, so a
+  // 64-key split is a single memory round trip (warp-uniform trip count; tails are predicated)
+  constexpr int UNR = G <= 4 ? 2 : 1;
+  for (int base = lo; base < hi; base += UNR * KEYS_PER_ITER) {
+    uint4 kr[UNR][DF_KPI], vr[UNR][DF_KPI];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const int key0 = base + u * KEYS_PER_ITER + gid * DF_KPI;
+#pragma unroll
+      for (int i = 0; i < DF_KPI; ++i) {
+        const bool ok = key0 + i < hi;
+        kr[u][i] = ok ? ldg_stream(kbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
+        vr[u][i] = ok ? ldg_stream(vbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
+      }
     }
 #pragma unroll
-    for (int i = 0; i < DF_KPI; ++i) {
-      const float vf[8] = {bf16_lo(vr[i].x), bf16_hi(vr[i].x), bf16_lo(vr[i].y), bf16_hi(vr[i].y),
-                           bf16_lo(vr[i].z), bf16_hi(vr[i].z), bf16_lo(vr[i].w), bf16_hi(vr[i].w)};
-#pragma unroll
-      for (int g = 0; g < G; ++g)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) o[g][e] = fmaf(pr[g][i], vf[e], o[g][e]);
-    }
+    for (int u = 0; u < UNR; ++u) process(kr[u], vr[u], base + u * KEYS_PER_ITER + gid * DF_KPI);
   }
 
   // ---- the new token: rotate k, append k and v to the cache, fold it in from registers (split 0, warp 0)
@@ -247,19 +259,32 @@ __global__ void __launch_bounds__(DF_WARPS * 32) decode_attn_fused_kernel(const 
   __syncthreads();
   if (!s_last) return;
   __threadfence();
+  // stage the (m, l) pairs of all splits in shared memory (one parallel round trip), then every thread
+  // folds its outputs with independent, unrolled loads
+  float* s_m = &s_o[0][0][0];                       // reuse: G*splits floats each, far below NG*G*HD
+  float* s_l = s_m + G * 64;
+  __syncthreads();
+  for (int i = threadIdx.x; i < G * p.splits; i += DF_WARPS * 32) {
+    const int g = i / p.splits, sp = i - g * p.splits;
+    const size_t bh = (size_t)b * nh + kvh * G + g;
+    s_m[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2);
+    s_l[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2 + 1);
+  }
+  __syncthreads();
   for (int idx = threadIdx.x; idx < G * HD; idx += DF_WARPS * 32) {
     const int g = idx / HD, d = idx - g * HD;
     const size_t bh = (size_t)b * nh + kvh * G + g;
     float M = -INFINITY;
-    for (int s = 0; s < p.splits; ++s) M = fmaxf(M, __ldcg(p.ml_part + (bh * p.splits + s) * 2));
+    for (int sp = 0; sp < p.splits; ++sp) M = fmaxf(M, s_m[g * 64 + sp]);
     const float Ms = M == -INFINITY ? 0.f : M;
     float acc = 0.f, L = 0.f;
-    for (int s = 0; s < p.splits; ++s) {
-      const float w = exp2f(__ldcg(p.ml_part + (bh * p.splits + s) * 2) - Ms);
-      if (w > 0.f) {
-        acc += w * __ldcg(p.o_part + (bh * p.splits + s) * HD + d);
-        L += w * __ldcg(p.ml_part + (bh * p.splits + s) * 2 + 1);
-      }
+    const float* op = p.o_part + bh * p.splits * HD + d;
+#pragma unroll 8
+    for (int sp = 0; sp < p.splits; ++sp) {
+      const float w = exp2f(s_m[g * 64 + sp] - Ms);
+      const float ov = __ldcg(op + (size_t)sp * HD);
+      acc += w > 0.f ? w * ov : 0.f;
+      L += w * s_l[g * 64 + sp];
     }
     p.out[bh * HD + d] = __float2bfloat16(L > 0.f ? acc / L : 0.f);
   }
@@ -277,7 +302,7 @@ extern "C" JL_API size_t jl_decode_attn_fused_scratch_bytes(int B, int nh, int n
 extern "C" JL_API int jl_decode_attn_fused_splits(int B, int nkv, int max_len, int num_sms) {
   if (num_sms <= 0) num_sms = 148;
   int want = (4 * num_sms + B * nkv - 1) / (B * nkv);
-  const int cap = (max_len + 63) / 64;                   // at least 64 keys per split
+  const int cap = (max_len + 127) / 128;                 // at least 128 keys per split
   int s = want < cap ? want : cap;
   return s < 1 ? 1 : (s > 64 ? 64 : s);
 }

@@ -49,6 +49,12 @@ int jl_swiglu(const void* in, void* out, int M, int F, int interleaved, void* st
 int jl_gemv(const void* x, const void* w, const void* norm_w, const void* residual, void* out, int M, int N,
             int K, float eps, int mode, int out_f32, int num_sms, void* stream);
 
+/* jl_gemv for M <= 4 with the weights streamed by TMA bulk copies (cp.async.bulk + mbarrier) through a
+ * shared-memory ring that starts filling before the programmatic-dependent-launch wait.  Returns 3
+ * (unsupported, nothing launched) when the activations leave no room for the ring: call jl_gemv then. */
+int jl_gemv_tma(const void* x, const void* w, const void* norm_w, const void* residual, void* out, int M, int N,
+                int K, float eps, int mode, int out_f32, int num_sms, void* stream);
+
 /* Same linear layers for any M on the tcgen05 tensor cores (TMA-fed, TMEM accumulators).  M > 128 runs
  * token-major tiles (prefill); M <= 128 runs swap-AB so the weight rows fill the 128-wide MMA and the
  * batch is the MMA N (decode at batch 9..128).  Modes / out_f32 as in jl_gemv.  N % 8 == 0, K % 8 == 0;

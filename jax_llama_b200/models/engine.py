@@ -88,8 +88,20 @@ class DecodeState:
 
 class B200Engine:
     def __init__(self, config: LLaMAConfig, embedding: torch.Tensor, layers: List[LayerWeights],
-                 final_norm: torch.Tensor, lm_head: torch.Tensor, *, use_cuda_graph: bool = True):
+                 final_norm: torch.Tensor, lm_head: torch.Tensor, *, use_cuda_graph: bool = True,
+                 tp: int = 1, rank: int = 0, comm: Any = None):
+        """`layers` / `lm_head` hold this rank's tensor-parallel slice (Megatron layout of
+        parallel/layout.py: wqkv/w13 cut on output rows, wo/w2 on the reduction dim, lm_head on vocab);
+        the embedding table and the norm scales are replicated."""
         self.config = config
+        self.tp, self.rank = int(tp), int(rank)
+        if self.tp > 1:
+            from ..parallel.layout import check_tp_divisibility
+            check_tp_divisibility(config, self.tp)
+            if comm is None:
+                from ..parallel.comm import PeerComm
+                comm = PeerComm(self.tp, self.rank, embedding.device)
+        self.comm = comm
         self.device = embedding.device
         if self.device.type != "cuda":
             raise ValueError("B200Engine needs CUDA tensors")
@@ -99,9 +111,10 @@ class B200Engine:
         self.final_norm = final_norm
         self.lm_head = lm_head
         self.use_cuda_graph = use_cuda_graph
-        self.nh = config.num_attention_heads
-        self.nkv = config.num_key_value_heads
+        self.nh = config.num_attention_heads // self.tp          # local (per-rank) head counts
+        self.nkv = config.num_key_value_heads // self.tp
         self.hd = config.head_dim
+        self.v_local = lm_head.shape[0]
         cos, sin = rope_cos_sin(self.hd, 2 * config.max_sequence_length, config.rope_theta)
         self.cos, self.sin = cos.to(self.device), sin.to(self.device)
         self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
@@ -124,17 +137,25 @@ class B200Engine:
                 w13=interleave_rows(bf(f["w1"]["kernel"]).t(), bf(f["w3"]["kernel"]).t()),
                 w2=bf(f["w2"]["kernel"]).t().contiguous()))
         emb = bf(t["wte"]["embedding"]).contiguous()
+        tp = int(kw.get("tp", 1))
         head = emb if config.tie_word_embeddings else bf(params["lm_head"]["kernel"]).t().contiguous()
+        if tp > 1 and emb.shape[0] != config.vocab_size:
+            # the layout rules shard the table on vocab; the engine keeps it whole on every rank
+            import torch.distributed as dist
+            parts = [torch.empty_like(emb) for _ in range(tp)]
+            dist.all_gather(parts, emb)
+            emb = torch.cat(parts, 0)
         return cls(config, emb, layers, bf(t["ln_f"]["kernel"]).contiguous(), head, **kw)
 
     @classmethod
     def random_init(cls, config: LLaMAConfig, device: Any = "cuda", seed: int = 0, **kw: Any) -> "B200Engine":
         """Random weights generated directly in kernel layout on the device (benchmarks; no host copy)."""
         dev = torch.device(device)
-        g = torch.Generator(device=dev).manual_seed(seed)
+        tp, rank = int(kw.get("tp", 1)), int(kw.get("rank", 0))
+        g = torch.Generator(device=dev).manual_seed(seed * 1000 + rank)
         std = config.initializer_range
-        h, f, v = config.hidden_size, config.intermediate_size, config.vocab_size
-        nh, nkv, hd = config.num_attention_heads, config.num_key_value_heads, config.head_dim
+        h, f, v = config.hidden_size, config.intermediate_size // tp, config.vocab_size // tp
+        nh, nkv, hd = config.num_attention_heads // tp, config.num_key_value_heads // tp, config.head_dim
 
         def mat(n: int, k: int) -> torch.Tensor:
             return (torch.randn(n, k, generator=g, device=dev, dtype=torch.float32) * std).to(torch.bfloat16)
@@ -142,8 +163,9 @@ class B200Engine:
         ones = lambda: torch.ones(h, dtype=torch.bfloat16, device=dev)     # noqa: E731
         layers = [LayerWeights(ones(), mat((nh + 2 * nkv) * hd, h), mat(h, nh * hd), ones(), mat(2 * f, h),
                                mat(h, f)) for _ in range(config.num_hidden_layers)]
-        emb = mat(v, h)
-        head = emb if config.tie_word_embeddings else mat(v, h)
+        ge = torch.Generator(device=dev).manual_seed(seed * 1000 + 999)      # same table on every rank
+        emb = (torch.randn(config.vocab_size, h, generator=ge, device=dev, dtype=torch.float32) * std).to(torch.bfloat16)
+        head = emb if (config.tie_word_embeddings and tp == 1) else mat(v, h)
         return cls(config, emb, layers, ones(), head, **kw)
 
     def to_tree(self) -> Tree:
@@ -218,10 +240,23 @@ class B200Engine:
                 K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
                                 pad_left=cache.pad_left, positions=positions, q_out=q_rot)
                 attn = self._prefill_attn(q_rot.view(B, S, nh, hd), kc, vc, start, S, cache).view(B * S, nh * hd)
-            x = K.linear(attn, l.wo, residual=x, mode=K.RESIDUAL, out=x)
+            x = self._row_parallel(attn, l.wo, x)
             h = K.linear(x, l.w13, norm_w=l.ffn_norm, eps=eps, mode=K.SWIGLU, out=ws.mlp if ws else None)
-            x = K.linear(h, l.w2, residual=x, mode=K.RESIDUAL, out=x)
+            x = self._row_parallel(h, l.w2, x)
         return x
+
+    def _row_parallel(self, a: torch.Tensor, w: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+        """x += a · wᵀ summed over tensor-parallel ranks (the reference's GSPMD all-reduce after wo / w2)."""
+        if self.tp == 1:
+            return K.linear(a, w, residual=x, mode=K.RESIDUAL, out=x)
+        m = a.numel() // w.shape[1]
+        if m <= 8:
+            # decode: GEMV + one-shot all-reduce over NVLink peer memory + residual, one kernel
+            return self.comm.gemv_allreduce(a, w, x, out=x)
+        # larger M: tcgen05 GEMM, then the NCCL baseline all-reduce (fused GEMM→reduce-scatter: see parallel/)
+        y = K.linear(a, w)
+        self.comm.allreduce_nccl(y)
+        return x.add_(y)
 
     def _prefill_attn(self, q: torch.Tensor, kc: torch.Tensor, vc: torch.Tensor, start: int, S: int,
                       cache: DeviceKVCache) -> torch.Tensor:
@@ -250,8 +285,12 @@ class B200Engine:
         positions = None
         if position_ids is not None:
             positions = position_ids.to(torch.int32).reshape(-1).contiguous()
+        if self.comm is not None:
+            self.comm.begin_sequence()
         x = K.embed(input_ids.reshape(-1), self.embedding)
         x = self._layers(x, B, S, cache, positions)
+        if self.comm is not None:
+            self.comm.end_sequence()
         cache.set_index(cache.index + S)
         out = ModelOutput(past_key_values=None if own_cache else cache)
         if last_only:
@@ -261,6 +300,13 @@ class B200Engine:
             rows = S
         if with_head:
             logits = K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True)
+            if self.tp > 1:
+                # API parity: `.logits` is the full vocabulary.  This gather is off the generate() path,
+                # which exchanges only top-k candidates (see _select_and_advance).
+                import torch.distributed as dist
+                parts = [torch.empty_like(logits) for _ in range(self.tp)]
+                dist.all_gather(parts, logits.contiguous(), group=self.comm.group)
+                logits = torch.cat(parts, dim=-1)
             out.logits = logits.view(B, rows, c.vocab_size)
             out.last_hidden_state = None
         else:
@@ -279,20 +325,40 @@ class B200Engine:
         st = DecodeState(
             B=B, max_len=max_len, ids=torch.zeros(B, **i32), x=torch.zeros(B, c.hidden_size, **bf),
             qkv=torch.zeros(B, (self.nh + 2 * self.nkv) * self.hd, **bf),
-            attn=torch.zeros(B, self.nh * self.hd, **bf), mlp=torch.zeros(B, c.intermediate_size, **bf),
-            logits=torch.zeros(B, c.vocab_size, dtype=torch.float32, device=dev),
+            attn=torch.zeros(B, self.nh * self.hd, **bf), mlp=torch.zeros(B, c.intermediate_size // self.tp, **bf),
+            logits=torch.zeros(B, self.v_local, dtype=torch.float32, device=dev),
             cand_val=torch.zeros(B, MAX_TOPK, dtype=torch.float32, device=dev),
             cand_idx=torch.zeros(B, MAX_TOPK, **i32), tok=torch.zeros(B, **i32),
             finished=torch.zeros(B, **i32), sequences=torch.zeros(B, max_len, **i32),
             cur_len=torch.zeros(1, **i32), step=torch.zeros(1, **i32), n_unfinished=torch.zeros(1, **i32),
             splits=splits, scratch=scratch)
+        if self.tp > 1:
+            # packed (values | indices) candidate lists: local and gathered-over-ranks
+            st.cand_local = torch.zeros(2 * B * MAX_TOPK, dtype=torch.int32, device=dev)
+            st.cand_all = torch.zeros(self.tp * 2 * B * MAX_TOPK, dtype=torch.int32, device=dev)
         self._decode_states[key] = st
         return st
 
     def _select_and_advance(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int) -> None:
         """logits → token (greedy or temperature/top-k/top-p) → sequences / finished / counters, on device."""
         do_sample, temperature, top_k, top_p, seed = sampling
-        if not do_sample:
+        if self.tp > 1:
+            # vocab-parallel head: each rank extracts its local top-k (value, global index) pairs, the pairs
+            # are exchanged through peer memory, and every rank runs the identical final selection — the
+            # [B, V] logits are never gathered (SURVEY §2.6 O17)
+            B = st.B
+            k = 2 if not do_sample else (MAX_TOPK if not top_k or top_k > MAX_TOPK else max(2, int(top_k)))
+            n = B * k
+            vals = st.cand_local[:n].view(torch.float32).view(B, k)
+            idx = st.cand_local[n:2 * n].view(B, k)
+            K.topk_candidates(st.logits, k, idx_offset=self.rank * self.v_local, out=(vals, idx))
+            gathered = st.cand_all[:self.tp * 2 * n]
+            self.comm.allgather_small(st.cand_local[:2 * n], gathered)
+            K.sample_candidates(gathered[:n].view(torch.float32).view(B, k), gathered[n:2 * n].view(B, k),
+                                n_lists=self.tp, list_stride=2 * n, top_k=(top_k if do_sample else 1) or k,
+                                top_p=top_p, temperature=temperature if do_sample else 0.0, seed=seed,
+                                step=st.step, out=st.tok)
+        elif not do_sample:
             K.argmax(st.logits, out=st.tok)
         else:
             k = MAX_TOPK if not top_k or top_k > MAX_TOPK else int(top_k)
@@ -310,10 +376,14 @@ class B200Engine:
     def _decode_step(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int) -> None:
         """One token for every row: ids → logits → next ids.  All state on device; capturable."""
         c = self.config
+        if self.comm is not None:
+            self.comm.begin_sequence()
         K.embed(st.ids, self.embedding, out=st.x)
         x = self._layers(st.x, st.B, 1, cache, None, ws=st)
         K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True, out=st.logits)
         self._select_and_advance(st, cache, sampling, eos, pad)
+        if self.comm is not None:
+            self.comm.end_sequence()
 
     def _graph_for(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int
                    ) -> Optional[torch.cuda.CUDAGraph]:

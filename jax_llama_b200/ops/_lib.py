@@ -25,6 +25,7 @@ _SIGNATURES = {
     "jl_rope_kv_write": (i32, [vp, vp, vp, vp, fp, fp, ip, ip, ip, i32, i32, i32, i32, i32, i32, i32, vp]),
     "jl_swiglu": (i32, [vp, vp, i32, i32, i32, vp]),
     "jl_gemv": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, i32, vp]),
+    "jl_gemv_tma": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, f32, i32, i32, i32, vp]),
     "jl_gemm": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "jl_decode_attn_scratch_bytes": (sz, [i32, i32, i32, i32]),
     "jl_decode_attn_splits": (i32, [i32, i32, i32, i32]),

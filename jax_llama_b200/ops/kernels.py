@@ -151,8 +151,9 @@ def _linear_ref(x, w, norm_w, eps, residual, mode, out_f32):
 def linear(x: torch.Tensor, w: torch.Tensor, *, norm_w: Optional[torch.Tensor] = None, eps: float = 1e-5,
            residual: Optional[torch.Tensor] = None, mode: int = PLAIN, out_f32: bool = False,
            out: Optional[torch.Tensor] = None, force: Optional[str] = None) -> torch.Tensor:
-    """y = f(x) Wᵀ with W [N, K].  Dispatch by token count: M ≤ 4 → weight-streaming GEMV (RMSNorm fused),
-    otherwise the tcgen05 GEMM (swap-AB up to M = 128).  `force` ∈ {"gemv", "gemm"} pins the kernel."""
+    """y = f(x) Wᵀ with W [N, K].  Dispatch by token count: M ≤ 4 → TMA-streamed GEMV (RMSNorm fused; falls
+    back to the register-streaming GEMV when the activations do not fit next to the ring), otherwise the
+    tcgen05 GEMM (swap-AB up to M = 128).  `force` ∈ {"gemv_tma", "gemv", "gemm"} pins the kernel."""
     if not x.is_cuda:
         return _linear_ref(x, w, norm_w, eps, residual, mode, out_f32)
     _bf16c(x, "x"); _bf16c(w, "w")
@@ -162,18 +163,30 @@ def linear(x: torch.Tensor, w: torch.Tensor, *, norm_w: Optional[torch.Tensor] =
     if out is None:
         out = torch.empty((m, odim), dtype=torch.float32 if out_f32 else x.dtype, device=x.device)
     sms = num_sms(x.device)
-    use_gemv = (m <= 4) if force is None else (force == "gemv")
+    if force is None:
+        path = "gemv_tma" if m <= 4 else "gemm"
+    else:
+        path = force
     L = _lib.lib()
-    if use_gemv:
+    if path == "gemv_tma":
+        rc = L.jl_gemv_tma(x.data_ptr(), w.data_ptr(), _p(norm_w), _p(residual), out.data_ptr(), m, n, k,
+                           float(eps), mode, int(out_f32), sms, _stream())
+        if rc == 3 and force is None:
+            path = "gemv"                      # activations too large for the TMA ring: register-streaming kernel
+        else:
+            _lib.check(rc, "jl_gemv_tma")
+    if path == "gemv":
         if m > 8:
             raise ValueError("gemv path handles at most 8 rows")
         _lib.check(L.jl_gemv(x.data_ptr(), w.data_ptr(), _p(norm_w), _p(residual), out.data_ptr(), m, n, k,
                              float(eps), mode, int(out_f32), sms, _stream()), "jl_gemv")
-    else:
+    elif path == "gemm":
         if norm_w is not None:
             x = rmsnorm(x.view(m, k), norm_w, eps)
         _lib.check(L.jl_gemm(x.data_ptr(), w.data_ptr(), _p(residual), out.data_ptr(), m, n, k, mode,
                              int(out_f32), sms, _stream()), "jl_gemm")
+    elif path != "gemv_tma":
+        raise ValueError(f"unknown linear path {path!r}")
     return out
 
 

@@ -1,0 +1,189 @@
+"""Process bootstrap and NVLink peer memory for tensor parallelism.
+
+The reference never names a collective: GSPMD derives NCCL all-reduces / all-gathers from the parameter
+sharding.  Here communication is a first-class component:
+
+* `init_distributed` — one process per GPU (torchrun env), `torch.distributed` used for bootstrap and as
+  the measured NCCL baseline only;
+* `PeerComm` — every rank allocates an *inbox* and a flag array with `cudaMalloc`, exports them with CUDA
+  IPC, and maps every peer's pair.  The fused kernels in `csrc/comm.cu` store partial results straight into
+  peers' inboxes over NVLink and synchronise with release/acquire flags that carry a monotonically
+  increasing epoch (a device-side counter + the call's index since the last bump, so CUDA-graph replays need
+  no host involvement).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+import os
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+from ..ops import kernels as K
+
+logger = logging.getLogger(__name__)
+
+MAX_TP = 8
+
+_EXTRA_SIGNATURES = {
+    "jl_ipc_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]),
+    "jl_ipc_open": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "jl_ipc_close": (C.c_int, [C.c_void_p]),
+    "jl_ipc_free": (C.c_int, [C.c_void_p]),
+    "jl_gemv_allreduce": (C.c_int, [C.c_void_p] * 4 + [C.c_int] * 5 + [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int,
+                                                                          C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "jl_gemv_allreduce_flags": (C.c_int, [C.c_int]),
+    "jl_allgather_small": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                     C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    "jl_comm_bump": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+}
+
+
+def _L() -> C.CDLL:
+    lib = _lib.lib()
+    if not getattr(lib, "_comm_ready", False):
+        for name, (res, args) in _EXTRA_SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        lib._comm_ready = True
+    return lib
+
+
+def init_distributed(backend: Optional[str] = None) -> Tuple[int, int, int]:
+    """Join the job described by RANK / WORLD_SIZE / LOCAL_RANK / MASTER_*.  Returns (rank, world, local)."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group(backend, device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend)
+    return rank, world, local
+
+
+class PeerComm:
+    """Peer-mapped inbox + flags of one tensor-parallel group, and the fused collectives that use them."""
+
+    def __init__(self, tp: int, rank: int, device: torch.device, inbox_bytes: int = 8 << 20,
+                 n_flags: int = 1 << 16, group: Optional[dist.ProcessGroup] = None):
+        if not 1 <= tp <= MAX_TP:
+            raise ValueError(f"tensor-parallel degree {tp} outside 1..{MAX_TP}")
+        self.tp, self.rank, self.device, self.group = tp, rank, device, group
+        self.parity_bytes = (inbox_bytes // 2) // 256 * 256
+        self.n_flags = n_flags
+        L = _L()
+        self._own_inbox, h_inbox = self._alloc(2 * self.parity_bytes)
+        self._own_flags, h_flags = self._alloc(n_flags * 4)
+        if tp > 1:
+            gathered: list = [None] * tp
+            dist.all_gather_object(gathered, (rank, h_inbox, h_flags), group=group)
+        else:
+            gathered = [(rank, h_inbox, h_flags)]
+        self._opened = []
+        inbox, flags = [0] * MAX_TP, [0] * MAX_TP
+        for r, hi, hf in gathered:
+            if r == rank:
+                inbox[r], flags[r] = self._own_inbox, self._own_flags
+            else:
+                inbox[r], flags[r] = self._open(hi), self._open(hf)
+        self.inbox_ptrs = (C.c_void_p * MAX_TP)(*inbox)
+        self.flag_ptrs = (C.c_void_p * MAX_TP)(*flags)
+        self.seq = torch.zeros(1, dtype=torch.int32, device=device)     # device epoch counter
+        self.call_index = 0                                               # collectives since the last bump
+        self._flag_blocks: Dict[Tuple, int] = {}
+        self._flag_top = 0
+        if tp > 1:
+            dist.barrier(group=group)          # everyone has mapped everyone before the first kernel runs
+        del L
+
+    # ------------------------------------------------------------------ IPC helpers
+    def _alloc(self, nbytes: int) -> Tuple[int, bytes]:
+        ptr = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        _lib.check(_L().jl_ipc_alloc(nbytes, C.byref(ptr), handle), "jl_ipc_alloc")
+        return ptr.value, handle.raw
+
+    def _open(self, handle: bytes) -> int:
+        ptr = C.c_void_p()
+        _lib.check(_L().jl_ipc_open(C.create_string_buffer(handle, 64), C.byref(ptr)), "jl_ipc_open")
+        self._opened.append(ptr.value)
+        return ptr.value
+
+    def close(self) -> None:
+        L = _L()
+        torch.cuda.synchronize(self.device)
+        for p in self._opened:
+            L.jl_ipc_close(p)
+        self._opened = []
+        for p in (self._own_inbox, self._own_flags):
+            if p:
+                L.jl_ipc_free(p)
+        self._own_inbox = self._own_flags = 0
+
+    def flag_block(self, key: Tuple, count: int) -> int:
+        """Disjoint flag range per call-site layout (different slice counts must not alias)."""
+        if key not in self._flag_blocks:
+            if self._flag_top + count > self.n_flags:
+                raise RuntimeError("out of communication flags")
+            self._flag_blocks[key] = self._flag_top
+            self._flag_top += count
+        return self._flag_blocks[key]
+
+    # ------------------------------------------------------------------ epochs
+    def begin_sequence(self) -> None:
+        """Start counting collectives of one step / forward (host side)."""
+        self.call_index = 0
+
+    def end_sequence(self) -> None:
+        """Advance the device epoch counter past the collectives issued since `begin_sequence`."""
+        if self.call_index:
+            _lib.check(_L().jl_comm_bump(self.seq.data_ptr(), self.call_index, K._stream()), "jl_comm_bump")
+        self.call_index = 0
+
+    # ------------------------------------------------------------------ fused collectives
+    def gemv_allreduce(self, x: torch.Tensor, w: torch.Tensor, residual: torch.Tensor,
+                       out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """out = residual + all_reduce_sum(x_local · w_localᵀ) for M ≤ 8 rows, in one kernel per rank."""
+        n, k = w.shape
+        m = x.numel() // k
+        if out is None:
+            out = torch.empty((m, n), dtype=x.dtype, device=x.device)
+        L = _L()
+        need = self.tp * m * n * 4
+        if need > self.parity_bytes:
+            raise ValueError(f"inbox too small for a {m}x{n} all-reduce ({need} > {self.parity_bytes} bytes)")
+        off = self.flag_block(("gemv_ar", n), int(L.jl_gemv_allreduce_flags(n)))
+        _lib.check(L.jl_gemv_allreduce(x.data_ptr(), w.data_ptr(), residual.data_ptr(), out.data_ptr(), m, n, k,
+                                       self.tp, self.rank, self.inbox_ptrs, self.flag_ptrs, self.parity_bytes // 4,
+                                       off, self.seq.data_ptr(), self.call_index, K.num_sms(x.device), K._stream()),
+                   "jl_gemv_allreduce")
+        self.call_index += 1
+        return out
+
+    def allgather_small(self, src: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """out[r] = src of rank r for a small, 16-byte-multiple buffer (top-k candidates)."""
+        nbytes = src.numel() * src.element_size()
+        if nbytes % 16:
+            raise ValueError("allgather_small needs a multiple of 16 bytes")
+        L = _L()
+        off = self.flag_block(("ag",), MAX_TP)
+        _lib.check(L.jl_allgather_small(src.data_ptr(), out.data_ptr(), nbytes, nbytes, self.tp, self.rank,
+                                        self.inbox_ptrs, self.flag_ptrs, self.parity_bytes, off,
+                                        self.seq.data_ptr(), self.call_index, K._stream()), "jl_allgather_small")
+        self.call_index += 1
+        return out
+
+    # ------------------------------------------------------------------ NCCL baseline (measured, not the product)
+    def allreduce_nccl(self, t: torch.Tensor) -> torch.Tensor:
+        if self.tp > 1:
+            dist.all_reduce(t, group=self.group)
+        return t

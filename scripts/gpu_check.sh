@@ -8,7 +8,8 @@ run() {  # name, pytest -k expression, file
   echo "$1: exit $? :: $(tail -1 gpurun_out/test_$1.log)"
 }
 run basic "library or embed or rmsnorm or rope or swiglu" tests/test_gpu_kernels.py
-run gemv "gemv" tests/test_gpu_kernels.py
+run gemv "gemv_modes" tests/test_gpu_kernels.py
+run gemvtma "gemv_tma" tests/test_gpu_kernels.py
 run gemm "gemm" tests/test_gpu_kernels.py
 run attn "decode_attention and not fused" tests/test_gpu_kernels.py
 run attnfused "decode_attention_fused" tests/test_gpu_kernels.py

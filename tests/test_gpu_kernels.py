@@ -110,6 +110,27 @@ def test_gemv_modes(M, N, K_):
     assert got.dtype == torch.float32 and rel_err(got, want) < 1e-3
 
 
+@pytest.mark.parametrize("M", [1, 2, 3, 4])
+@pytest.mark.parametrize("N,K_", [(512, 256), (1536, 4096), (4096, 14336), (1000, 520), (28672, 4096), (6144, 4096)])
+def test_gemv_tma_modes(M, N, K_):
+    x, w = rnd(M, K_, seed=6), rnd(N, K_, scale=0.05, seed=7)
+    g = rnd(K_, seed=8) * 0.1 + 1
+    res = rnd(M, N, seed=9)
+    xd, wd = x.to(DEV), w.to(DEV)
+    for norm in (None, g):
+        nd = None if norm is None else norm.to(DEV)
+        want = K.linear(x, w, norm_w=norm, eps=1e-5)
+        assert rel_err(K.linear(xd, wd, norm_w=nd, eps=1e-5, force="gemv_tma"), want) < 1.5e-2
+    want = K.linear(x, w, residual=res, mode=K.RESIDUAL)
+    r = res.to(DEV).clone()
+    assert rel_err(K.linear(xd, wd, residual=r, mode=K.RESIDUAL, out=r, force="gemv_tma"), want) < 1.5e-2
+    want = K.linear(x, w, norm_w=g, mode=K.SWIGLU)
+    assert rel_err(K.linear(xd, wd, norm_w=g.to(DEV), mode=K.SWIGLU, force="gemv_tma"), want) < 2e-2
+    want = K.linear(x, w, out_f32=True)
+    got = K.linear(xd, wd, out_f32=True, force="gemv_tma")
+    assert got.dtype == torch.float32 and rel_err(got, want) < 1e-3
+
+
 @pytest.mark.parametrize("M,N,K_", [
     (128, 256, 64), (128, 128, 256), (256, 512, 512),        # single / few tiles, normal orientation... (M>128)
     (300, 1000, 520), (2048, 6144, 4096), (1024, 4096, 14336),
