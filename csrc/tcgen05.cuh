@@ -197,6 +197,9 @@ __device__ __forceinline__ void mma_commit(uint32_t bar) {
 // and 128-byte swizzle.  Returns 0 on success (tensormap.cu).
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
                       uint32_t box_rows);
+// Un-swizzled variant with a {box_cols <= 256, box_rows <= 256} box: the tile lands row-major in smem.
+int make_tmap_2d_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                            uint32_t box_cols, uint32_t box_rows);
 // 3-D variant: [d2, rows, cols] with element strides (ld2, ld1, 1); box {64, box_rows, 1}.
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t d2, uint64_t rows, uint64_t cols,
                       uint64_t ld2, uint64_t ld1, uint32_t box_rows);
