@@ -15,6 +15,7 @@ namespace jl {
 // ---------------------------------------------------------------- host-side error plumbing
 void set_error(const char* fmt, ...);          // error.cu
 void count_launch();                           // error.cu: bumps the counter behind jl_launch_count()
+bool pdl_enabled();                            // error.cu: false when JLLAMA_NO_PDL is set
 int cuda_fail(cudaError_t e, const char* what); // records + returns JL_ERR_CUDA
 
 #define JL_CHECK_ARG(cond, ...)                  \
@@ -45,7 +46,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;      // JLLAMA_NO_PDL=1 turns the attribute off (A/B measurements)
   count_launch();
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }

@@ -1,6 +1,7 @@
 // Error reporting and launch accounting shared by every entry point.
 #include <atomic>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -29,3 +30,13 @@ int cuda_fail(cudaError_t e, const char* what) {
 extern "C" JL_API const char* jl_last_error(void) { return jl::g_err; }
 extern "C" JL_API int jl_version(void) { return 100; }
 extern "C" JL_API unsigned long long jl_launch_count(void) { return jl::launches(); }
+
+namespace jl {
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("JLLAMA_NO_PDL");
+    return !(e && e[0] && e[0] != '0');
+  }();
+  return on;
+}
+}  // namespace jl

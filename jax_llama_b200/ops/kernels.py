@@ -17,6 +17,7 @@ from . import _lib
 
 PLAIN, RESIDUAL, SWIGLU = 0, 1, 2
 _NUM_SMS = {}
+_SMALL_M_PATH = __import__("os").environ.get("JLLAMA_SMALL_M", "gemv")    # measured faster in the graph-replayed step than "gemv_tma"
 
 
 def _stream() -> int:
@@ -164,7 +165,7 @@ def linear(x: torch.Tensor, w: torch.Tensor, *, norm_w: Optional[torch.Tensor] =
         out = torch.empty((m, odim), dtype=torch.float32 if out_f32 else x.dtype, device=x.device)
     sms = num_sms(x.device)
     if force is None:
-        path = "gemv_tma" if m <= 4 else "gemm"
+        path = ("gemv_tma" if _SMALL_M_PATH == "gemv_tma" else "gemv") if m <= 4 else "gemm"
     else:
         path = force
     L = _lib.lib()
