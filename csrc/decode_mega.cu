@@ -1,0 +1,685 @@
+// Persistent whole-model decode step ("megakernel") for small batches (M <= 4 tokens).
+//
+// Why: a decode step of an 8B model is ~225 dependent kernels whose useful work is 5-40 µs each.  Measured
+// with ncu on B200, every one of them loses 5-10 µs to CTA launch ramp, prologue and tail (SMs active for
+// only ~50% of a 19 µs `wo` GEMV), and programmatic dependent launch does not recover it because the
+// streaming kernels fill the SM.  Here ONE cooperative kernel with one CTA per SM runs the entire step:
+//
+//   * warp 0 is a TMA producer that streams every weight matrix of the model, layer after layer, through a
+//     shared-memory ring (16 KB stages, 4 tensor-map boxes of [8 rows x 256 cols] each).  It depends on
+//     nothing but free ring slots, so it runs ahead across op boundaries: while the consumers sit in a grid
+//     barrier or do attention, the next op's weights are already landing.  HBM never idles.
+//   * warps 1..8 are consumers: RMSNorm + GEMV (one weight row per warp per stage), residual / SwiGLU
+//     epilogues, RoPE + KV append + split-KV GQA attention (one (batch, kv-head, split) item per CTA, merge
+//     by the last-arriving CTA), final norm + LM head.
+//   * ops are separated by a grid-wide barrier (monotonic atomic counter, acquire spin with a watchdog);
+//     activations cross CTAs through L2 (ld.global.cg), never through stale L1 lines.
+//   * rows of each GEMV are cut into 148 contiguous, near-equal ranges (±1 group of 8 rows).
+//
+// Weights of all layers are stacked per op ([L·N, K]) so five tensor maps describe the whole model.
+// Math is identical to the unfused kernels (gemv.cu, decode_attn_fused.cu); the tests compare the two.
+// Reference: the body of HF Flax `_sample`'s while-loop that /root/reference/jax_llama/generation.py:28-41
+// runs as one compiled XLA program — this is the hand-written equivalent.
+#include <cooperative_groups.h>
+
+#include "jllama_b200.h"
+#include "tcgen05.cuh"
+
+namespace jl {
+
+constexpr int MG_CONSUMERS = 8;
+constexpr int MG_THREADS = (MG_CONSUMERS + 1) * 32;
+constexpr int MG_CT = MG_CONSUMERS * 32;           // consumer threads
+constexpr int MG_GROUP = 8;                        // weight rows per stage (one per consumer warp)
+constexpr int MG_KS = 1024;                        // K elements per stage
+constexpr int MG_BOX_BYTES = MG_GROUP * 256 * 2;   // 4 KB box [8 rows x 256 cols]
+constexpr int MG_STAGE_BYTES = 4 * MG_BOX_BYTES;   // 16 KB
+constexpr int MG_HD = 128;
+constexpr int MG_KPI = 4;
+
+struct alignas(64) MegaTmaps {
+  CUtensorMap m[5];          // wqkv_all, wo_all, w13_all, w2_all, lm_head
+};
+
+struct MegaParams {
+  int L, H, F, V, nh, nkv, NQKV, vocab_full;
+  float eps, scale_log2;
+  const __nv_bfloat16* attn_norm;    // [L, H]
+  const __nv_bfloat16* ffn_norm;     // [L, H]
+  const __nv_bfloat16* final_norm;   // [H]
+  const __nv_bfloat16* embedding;    // [vocab_full, H]
+  const int* ids;                    // [M]
+  __nv_bfloat16* x;                  // [M, H]   residual stream
+  __nv_bfloat16* qkv;                // [M, NQKV]
+  __nv_bfloat16* attn;               // [M, nh·hd]
+  __nv_bfloat16* hmlp;               // [M, F]
+  float* logits;                     // [M, V]
+  __nv_bfloat16* kc;                 // [L][M][nkv][T][hd]
+  __nv_bfloat16* vc;
+  const float* cos_t;
+  const float* sin_t;
+  const int* cache_len;
+  const int* pad_left;
+  float* o_part;                     // [M·nh][splits][hd]
+  float* ml_part;                    // [M·nh][splits][2]
+  int* tickets;                      // [M·nkv]
+  unsigned int* bar_counter;         // monotonically increasing arrival counter
+  unsigned int* bar_gen;             // barriers completed by previous launches
+  int T, max_pos, splits, stages;
+};
+
+enum { MG_PLAIN = 0, MG_RESIDUAL = 1, MG_SWIGLU = 2, MG_LOGITS = 3 };
+
+__device__ __forceinline__ void mg_consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(MG_CT) : "memory"); }
+__device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ldcg16(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
+
+// contiguous, near-equal split of `n` groups over the grid
+__device__ __forceinline__ void mg_range(int n, int& g0, int& g1) {
+  g0 = (int)(((long long)n * blockIdx.x) / gridDim.x);
+  g1 = (int)(((long long)n * (blockIdx.x + 1)) / gridDim.x);
+}
+
+struct MegaCtx {
+  uint32_t ring, bars;
+  const uint8_t* ring_ptr;
+  uint4* xin;                 // [M][K/8] staged activation (bf16)
+  float* s_attn;              // attention fold scratch
+  int stages;
+  int stage; uint32_t phase;  // ring cursor (producer and consumers keep separate copies)
+};
+
+// ------------------------------------------------------------------------------------ producer side
+__device__ __forceinline__ void mg_stream(MegaCtx& c, const CUtensorMap* tm, int row_base, int N, int K) {
+  int g0, g1;
+  mg_range(N / MG_GROUP, g0, g1);
+  const int n_ks = (K + MG_KS - 1) / MG_KS;
+  for (int g = g0; g < g1; ++g) {
+    for (int ks = 0; ks < n_ks; ++ks) {
+      tc::mbar_wait(c.bars + 8u * (c.stages + c.stage), c.phase ^ 1);
+      const uint32_t full = c.bars + 8u * c.stage;
+      tc::mbar_expect_tx(full, MG_STAGE_BYTES);
+      const uint32_t dst = c.ring + c.stage * MG_STAGE_BYTES;
+#pragma unroll
+      for (int b = 0; b < 4; ++b)
+        tc::tma_load_2d(dst + b * MG_BOX_BYTES, tm, full, ks * MG_KS + b * 256, row_base + g * MG_GROUP, tc::EVICT_FIRST);
+      if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ consumer side
+// stage [M, K] activations from global (written by other CTAs → L2 loads) into smem, optional RMSNorm
+template <int M>
+__device__ __forceinline__ void mg_stage_input(MegaCtx& c, const __nv_bfloat16* src, int K,
+                                               const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS]) {
+  const int ct = threadIdx.x - 32, lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
+  const int K8 = K >> 3;
+  if (norm_w != nullptr) {
+    float ss[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) ss[m] = 0.f;
+    for (int i = ct; i < K8; i += MG_CT) {
+#pragma unroll
+      for (int m = 0; m < M; ++m) {
+        const uint4 a = ldcg16(src + ((size_t)m * K8 + i) * 8);
+        c.xin[m * K8 + i] = a;                         // raw copy; normalised in place below
+        const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float lo = bf16_lo(aw[j]), hi = bf16_hi(aw[j]);
+          ss[m] += lo * lo + hi * hi;
+        }
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      const float t = warp_sum(ss[m]);
+      if (lane == 0) red[m][cw] = t;
+    }
+    mg_consumer_bar();
+    float rinv[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      float t = lane < MG_CONSUMERS ? red[m][lane] : 0.f;
+      t = warp_sum(t);
+      rinv[m] = rsqrtf(t / (float)K + eps);
+    }
+    for (int i = ct; i < K8; i += MG_CT) {
+      const uint4 g = __ldg(reinterpret_cast<const uint4*>(norm_w) + i);
+      const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+      for (int m = 0; m < M; ++m) {
+        const uint4 a = c.xin[m * K8 + i];             // written by this same thread above
+        const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          o[j] = pack_bf16(bf16_lo(aw[j]) * rinv[m] * bf16_lo(gw[j]), bf16_hi(aw[j]) * rinv[m] * bf16_hi(gw[j]));
+        c.xin[m * K8 + i] = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+  } else {
+    for (int i = ct; i < M * K8; i += MG_CT) c.xin[i] = ldcg16(src + (size_t)i * 8);
+  }
+  mg_consumer_bar();
+}
+
+// one GEMV op over this CTA's row range: out rows = op(W[row_base + r, :] · xin)
+template <int M, int MODE>
+__device__ __forceinline__ void mg_gemv(MegaCtx& c, int N, int K, void* out, const __nv_bfloat16* residual,
+                                        float (*s_res)[M][MG_CONSUMERS]) {
+  const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
+  const int K8 = K >> 3;
+  int g0, g1;
+  mg_range(N / MG_GROUP, g0, g1);
+  const int n_ks = (K + MG_KS - 1) / MG_KS;
+  for (int g = g0; g < g1; ++g) {
+    float acc[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) acc[m] = 0.f;
+    for (int ks = 0; ks < n_ks; ++ks) {
+      tc::mbar_wait(c.bars + 8u * c.stage, c.phase);
+      const uint4* wr = reinterpret_cast<const uint4*>(c.ring_ptr + c.stage * MG_STAGE_BYTES) + cw * 32 + lane;
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int ch = ks * (MG_KS / 8) + b * 32 + lane;
+        if (ch < K8) {
+          const uint4 wv = wr[b * (MG_BOX_BYTES / 16)];
+          const float wf[8] = {bf16_lo(wv.x), bf16_hi(wv.x), bf16_lo(wv.y), bf16_hi(wv.y),
+                               bf16_lo(wv.z), bf16_hi(wv.z), bf16_lo(wv.w), bf16_hi(wv.w)};
+#pragma unroll
+          for (int m = 0; m < M; ++m) {
+            const uint4 xv = c.xin[m * K8 + ch];
+            const float xf[8] = {bf16_lo(xv.x), bf16_hi(xv.x), bf16_lo(xv.y), bf16_hi(xv.y),
+                                 bf16_lo(xv.z), bf16_hi(xv.z), bf16_lo(xv.w), bf16_hi(xv.w)};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[m] = fmaf(wf[e], xf[e], acc[m]);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(c.bars + 8u * (c.stages + c.stage));
+      if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m) acc[m] = warp_sum(acc[m]);
+    const int row = g * MG_GROUP + cw;
+    if constexpr (MODE == MG_SWIGLU) {
+      // (gate, up) rows sit in adjacent warps: exchange through smem, even warps finish the pair
+      float (*buf)[MG_CONSUMERS] = s_res[g & 1];
+      if (lane == 0) {
+#pragma unroll
+        for (int m = 0; m < M; ++m) buf[m][cw] = __bfloat162float(__float2bfloat16(acc[m]));
+      }
+      mg_consumer_bar();
+      if ((cw & 1) == 0 && lane < M) {
+        const float gate = buf[lane][cw], up = buf[lane][cw + 1];
+        reinterpret_cast<__nv_bfloat16*>(out)[(size_t)lane * (N / 2) + row / 2] = __float2bfloat16(silu(gate) * up);
+      }
+    } else if (lane == 0) {
+#pragma unroll
+      for (int m = 0; m < M; ++m) {
+        float v = acc[m];
+        if constexpr (MODE == MG_LOGITS) {
+          reinterpret_cast<float*>(out)[(size_t)m * N + row] = v;
+        } else {
+          if constexpr (MODE == MG_RESIDUAL)
+            v = __bfloat162float(__float2bfloat16(v)) + __bfloat162float(__ldcg(residual + (size_t)m * N + row));
+          reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * N + row] = __float2bfloat16(v);
+        }
+      }
+    }
+  }
+}
+
+// grid-wide barrier among the consumer warps of all CTAs
+__device__ __forceinline__ void mg_grid_barrier(const MegaParams& p, unsigned int gen_base, int& bar_idx) {
+  mg_consumer_bar();                                   // all of this CTA's global writes are issued
+  if (threadIdx.x == 32) {
+    __threadfence();
+    const unsigned int target = (gen_base + (unsigned)bar_idx + 1u) * gridDim.x;
+    atomicAdd(p.bar_counter, 1u);
+    unsigned int spins = 0;
+    while ((int)(ld_acquire_gpu_u32(p.bar_counter) - target) < 0) {
+      if (++spins > (1u << 26)) {
+        printf("jllama_b200: grid barrier %d timed out in block %d\n", bar_idx, (int)blockIdx.x);
+        __trap();
+      }
+    }
+  }
+  ++bar_idx;
+  mg_consumer_bar();
+}
+
+// RoPE + KV append + split-KV attention for one (b, kv head, split) item + ticket merge (8 consumer warps)
+template <int G>
+__device__ __forceinline__ void mg_attention_item(const MegaParams& p, const MegaCtx& c, int layer, int M, int b,
+                                                  int kvh, int split, int* s_last) {
+  constexpr int HD = MG_HD, LPK = HD / 8, GPW = 32 / LPK, NG = MG_CONSUMERS * GPW;
+  constexpr int KEYS_PER_ITER = NG * MG_KPI;
+  const int nh = p.nkv * G;
+  const int lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) - 1, ct = threadIdx.x - 32;
+  const int lig = lane % LPK, gid = warp * GPW + lane / LPK, group_base = lane - lig;
+  const int kidx = ((lig / (LPK / 2)) & 1) * 2 + ((lig / (LPK / 4)) & 1);
+  float (*s_o)[G][HD] = reinterpret_cast<float (*)[G][HD]>(c.s_attn);
+  float (*s_ml)[G][2] = reinterpret_cast<float (*)[G][2]>(c.s_attn + NG * G * HD);
+
+  int len = __ldcg(p.cache_len);
+  len = len > p.T ? p.T : len;
+  const int first = p.pad_left ? p.pad_left[b] : 0;
+  const int valid = len - first > 0 ? len - first : 0;
+  int pos = len - first;
+  pos = pos < 0 ? 0 : (pos >= p.max_pos ? p.max_pos - 1 : pos);
+  int chunk = (valid + p.splits - 1) / p.splits;
+  chunk = ((chunk + KEYS_PER_ITER - 1) / KEYS_PER_ITER) * KEYS_PER_ITER;
+  const int lo = first + split * chunk;
+  const int hi = lo + chunk < len ? lo + chunk : len;
+
+  const float4 cs4 = __ldg(reinterpret_cast<const float4*>(p.cos_t) + (size_t)pos * LPK + lig);
+  const float4 sn4 = __ldg(reinterpret_cast<const float4*>(p.sin_t) + (size_t)pos * LPK + lig);
+  const float cs[4] = {cs4.x, cs4.y, cs4.z, cs4.w}, sn[4] = {sn4.x, sn4.y, sn4.z, sn4.w};
+  const __nv_bfloat16* row = p.qkv + (size_t)b * p.NQKV;
+
+  float qf[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const uint4 a = ldcg16(row + (size_t)(kvh * G + g) * HD + lig * 8);
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float re = bf16_lo(aw[j]), im = bf16_hi(aw[j]);
+      const uint32_t r = pack_bf16(re * cs[j] - im * sn[j], re * sn[j] + im * cs[j]);
+      qf[g][2 * j] = bf16_lo(r) * p.scale_log2;
+      qf[g][2 * j + 1] = bf16_hi(r) * p.scale_log2;
+    }
+  }
+  float m[G], l[G], o[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    m[g] = -INFINITY; l[g] = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) o[g][e] = 0.f;
+  }
+  const size_t head_off = (((size_t)layer * M + b) * p.nkv + kvh) * (size_t)p.T * HD;
+  const __nv_bfloat16* kbase = p.kc + head_off + lig * 8;
+  const __nv_bfloat16* vbase = p.vc + head_off + lig * 8;
+
+  auto process = [&](const uint4 (&kr)[MG_KPI], const uint4 (&vr)[MG_KPI], const int key0) {
+    float part[G][MG_KPI];
+#pragma unroll
+    for (int i = 0; i < MG_KPI; ++i) {
+      const float kf[8] = {bf16_lo(kr[i].x), bf16_hi(kr[i].x), bf16_lo(kr[i].y), bf16_hi(kr[i].y),
+                           bf16_lo(kr[i].z), bf16_hi(kr[i].z), bf16_lo(kr[i].w), bf16_hi(kr[i].w)};
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        float s = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s = fmaf(qf[g][e], kf[e], s);
+        part[g][i] = s;
+      }
+    }
+    float pr[G][MG_KPI];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const bool up = (lig & (LPK / 2)) != 0;
+      float k0 = up ? part[g][2] : part[g][0], k1 = up ? part[g][3] : part[g][1];
+      const float s0 = up ? part[g][0] : part[g][2], s1 = up ? part[g][1] : part[g][3];
+      k0 += __shfl_xor_sync(0xffffffffu, s0, LPK / 2);
+      k1 += __shfl_xor_sync(0xffffffffu, s1, LPK / 2);
+      const bool up2 = (lig & (LPK / 4)) != 0;
+      float s = up2 ? k1 : k0;
+      const float snd = up2 ? k0 : k1;
+      s += __shfl_xor_sync(0xffffffffu, snd, LPK / 4);
+#pragma unroll
+      for (int off = LPK / 8; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+      if (key0 + kidx >= hi) s = -INFINITY;
+      float mx = fmaxf(s, __shfl_xor_sync(0xffffffffu, s, LPK / 2));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, LPK / 4));
+      const float m_new = fmaxf(m[g], mx);
+      const float m_safe = m_new == -INFINITY ? 0.f : m_new;
+      const float corr = exp2f(m[g] - m_safe);
+      const float pe = exp2f(s - m_safe);
+      m[g] = m_new;
+      float psum = 0.f;
+#pragma unroll
+      for (int i = 0; i < MG_KPI; ++i) {
+        pr[g][i] = __shfl_sync(0xffffffffu, pe, group_base + (i >> 1) * (LPK / 2) + (i & 1) * (LPK / 4));
+        psum += pr[g][i];
+      }
+      l[g] = l[g] * corr + psum;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[g][e] *= corr;
+    }
+#pragma unroll
+    for (int i = 0; i < MG_KPI; ++i) {
+      const float vf[8] = {bf16_lo(vr[i].x), bf16_hi(vr[i].x), bf16_lo(vr[i].y), bf16_hi(vr[i].y),
+                           bf16_lo(vr[i].z), bf16_hi(vr[i].z), bf16_lo(vr[i].w), bf16_hi(vr[i].w)};
+#pragma unroll
+      for (int g = 0; g < G; ++g)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[g][e] = fmaf(pr[g][i], vf[e], o[g][e]);
+    }
+  };
+
+  constexpr int UNR = G <= 4 ? 2 : 1;
+  for (int base = lo; base < hi; base += UNR * KEYS_PER_ITER) {
+    uint4 kr[UNR][MG_KPI], vr[UNR][MG_KPI];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const int key0 = base + u * KEYS_PER_ITER + gid * MG_KPI;
+#pragma unroll
+      for (int i = 0; i < MG_KPI; ++i) {
+        const bool ok = key0 + i < hi;
+        kr[u][i] = ok ? ldg_stream(kbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
+        vr[u][i] = ok ? ldg_stream(vbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) process(kr[u], vr[u], base + u * KEYS_PER_ITER + gid * MG_KPI);
+  }
+
+  // the new token: rotate k, append (k, v), fold it in from registers (split 0, consumer warp 0)
+  if (split == 0 && warp == 0) {
+    const uint4 ka = ldcg16(row + (size_t)(nh + kvh) * HD + lig * 8);
+    const uint4 va = ldcg16(row + (size_t)(nh + p.nkv + kvh) * HD + lig * 8);
+    const uint32_t kw[4] = {ka.x, ka.y, ka.z, ka.w};
+    uint32_t kr4[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float re = bf16_lo(kw[j]), im = bf16_hi(kw[j]);
+      kr4[j] = pack_bf16(re * cs[j] - im * sn[j], re * sn[j] + im * cs[j]);
+    }
+    if (gid == 0 && len < p.T) {
+      *reinterpret_cast<uint4*>(p.kc + head_off + (size_t)len * HD + lig * 8) = make_uint4(kr4[0], kr4[1], kr4[2], kr4[3]);
+      *reinterpret_cast<uint4*>(p.vc + head_off + (size_t)len * HD + lig * 8) = va;
+    }
+    const float kf[8] = {bf16_lo(kr4[0]), bf16_hi(kr4[0]), bf16_lo(kr4[1]), bf16_hi(kr4[1]),
+                         bf16_lo(kr4[2]), bf16_hi(kr4[2]), bf16_lo(kr4[3]), bf16_hi(kr4[3])};
+    const float vf[8] = {bf16_lo(va.x), bf16_hi(va.x), bf16_lo(va.y), bf16_hi(va.y),
+                         bf16_lo(va.z), bf16_hi(va.z), bf16_lo(va.w), bf16_hi(va.w)};
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      float s = 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s = fmaf(qf[g][e], kf[e], s);
+#pragma unroll
+      for (int off = LPK / 2; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+      if (gid != 0) s = -INFINITY;
+      const float m_new = fmaxf(m[g], s);
+      const float m_safe = m_new == -INFINITY ? 0.f : m_new;
+      const float corr = exp2f(m[g] - m_safe);
+      const float pe = exp2f(s - m_safe);
+      m[g] = m_new;
+      l[g] = l[g] * corr + pe;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[g][e] = o[g][e] * corr + pe * vf[e];
+    }
+  }
+
+  // fold the lane-groups of this CTA
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s_o[gid][g][lig * 8 + e] = o[g][e];
+    if (lig == 0) { s_ml[gid][g][0] = m[g]; s_ml[gid][g][1] = l[g]; }
+  }
+  mg_consumer_bar();
+  for (int idx = ct; idx < G * HD; idx += MG_CT) {
+    const int g = idx / HD, d = idx - g * HD;
+    float Mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < NG; ++j) Mx = fmaxf(Mx, s_ml[j][g][0]);
+    const float Ms = Mx == -INFINITY ? 0.f : Mx;
+    float acc = 0.f, Ls = 0.f;
+#pragma unroll
+    for (int j = 0; j < NG; ++j) {
+      const float w = exp2f(s_ml[j][g][0] - Ms);
+      acc += w * s_o[j][g][d];
+      Ls += w * s_ml[j][g][1];
+    }
+    const int h = kvh * G + g;
+    if (p.splits == 1) {
+      p.attn[((size_t)b * nh + h) * HD + d] = __float2bfloat16(Ls > 0.f ? acc / Ls : 0.f);
+    } else {
+      const size_t pi = ((size_t)b * nh + h) * p.splits + split;
+      p.o_part[pi * HD + d] = acc;
+      if (d == 0) { p.ml_part[pi * 2] = Mx; p.ml_part[pi * 2 + 1] = Ls; }
+    }
+  }
+  if (p.splits == 1) { mg_consumer_bar(); return; }
+
+  __threadfence();
+  mg_consumer_bar();
+  if (ct == 0) {
+    int* t = p.tickets + b * p.nkv + kvh;
+    const int prev = atomicAdd(t, 1);
+    *s_last = prev == p.splits - 1;
+    if (*s_last) *t = 0;
+  }
+  mg_consumer_bar();
+  if (*s_last) {
+    __threadfence();
+    float* s_m = c.s_attn;
+    float* s_l = s_m + G * 64;
+    for (int i = ct; i < G * p.splits; i += MG_CT) {
+      const int g = i / p.splits, sp = i - g * p.splits;
+      const size_t bh = (size_t)b * nh + kvh * G + g;
+      s_m[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2);
+      s_l[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2 + 1);
+    }
+    mg_consumer_bar();
+    for (int idx = ct; idx < G * HD; idx += MG_CT) {
+      const int g = idx / HD, d = idx - g * HD;
+      const size_t bh = (size_t)b * nh + kvh * G + g;
+      float Mx = -INFINITY;
+      for (int sp = 0; sp < p.splits; ++sp) Mx = fmaxf(Mx, s_m[g * 64 + sp]);
+      const float Ms = Mx == -INFINITY ? 0.f : Mx;
+      float acc = 0.f, Ls = 0.f;
+      const float* op = p.o_part + bh * p.splits * HD + d;
+#pragma unroll 8
+      for (int sp = 0; sp < p.splits; ++sp) {
+        const float w = exp2f(s_m[g * 64 + sp] - Ms);
+        const float ov = __ldcg(op + (size_t)sp * HD);
+        acc += w > 0.f ? w * ov : 0.f;
+        Ls += w * s_l[g * 64 + sp];
+      }
+      p.attn[bh * HD + d] = __float2bfloat16(Ls > 0.f ? acc / Ls : 0.f);
+    }
+  }
+  mg_consumer_bar();
+}
+
+template <int M, int G>
+__global__ void __launch_bounds__(MG_THREADS, 1)
+decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ float red[M][MG_CONSUMERS];
+  __shared__ float s_res[2][M][MG_CONSUMERS];
+  __shared__ int s_last;
+  constexpr int NG = MG_CONSUMERS * (32 / (MG_HD / 8));
+
+  MegaCtx c;
+  c.stages = p.stages;
+  c.ring = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+  c.ring_ptr = smem_raw + (c.ring - tc::smem_u32(smem_raw));
+  c.bars = c.ring + p.stages * MG_STAGE_BYTES;
+  uint8_t* after = const_cast<uint8_t*>(c.ring_ptr) + p.stages * MG_STAGE_BYTES + 16 * p.stages;
+  c.s_attn = reinterpret_cast<float*>(after);
+  const int kmax = p.H > p.F ? p.H : p.F;
+  c.xin = reinterpret_cast<uint4*>(after + (size_t)NG * G * (MG_HD + 2) * sizeof(float));
+  (void)kmax;
+  c.stage = 0; c.phase = 0;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 5; ++i) tc::prefetch_tensormap(&tm.m[i]);
+    for (int s = 0; s < p.stages; ++s) {
+      tc::mbar_init(c.bars + 8u * s, 1);
+      tc::mbar_init(c.bars + 8u * (p.stages + s), MG_CONSUMERS);
+    }
+    tc::fence_barrier_init();
+  }
+  __syncthreads();
+
+  const int qdim = p.nh * MG_HD;
+  if (warp == 0) {
+    // ===================================================== producer: the whole model's weights, in order
+    if (lane == 0) {
+      for (int l = 0; l < p.L; ++l) {
+        mg_stream(c, &tm.m[0], l * p.NQKV, p.NQKV, p.H);
+        mg_stream(c, &tm.m[1], l * p.H, p.H, qdim);
+        mg_stream(c, &tm.m[2], l * 2 * p.F, 2 * p.F, p.H);
+        mg_stream(c, &tm.m[3], l * p.H, p.H, p.F);
+      }
+      mg_stream(c, &tm.m[4], 0, p.V, p.H);
+    }
+    return;
+  }
+
+  // ===================================================== consumers
+  const unsigned int gen_base = *reinterpret_cast<volatile unsigned int*>(p.bar_gen);
+  int bar_idx = 0;
+  const int ct = threadIdx.x - 32;
+
+  // embedding rows → residual stream (each CTA copies a slice), then everyone sees x
+  {
+    const int H8 = p.H >> 3;
+    for (int i = blockIdx.x * MG_CT + ct; i < M * H8; i += gridDim.x * MG_CT) {
+      const int m = i / H8, j = i - m * H8;
+      int id = p.ids[m];
+      id = id < 0 ? 0 : (id >= p.vocab_full ? p.vocab_full - 1 : id);
+      reinterpret_cast<uint4*>(p.x)[i] = __ldg(reinterpret_cast<const uint4*>(p.embedding) + (size_t)id * H8 + j);
+    }
+  }
+  mg_grid_barrier(p, gen_base, bar_idx);
+
+  for (int l = 0; l < p.L; ++l) {
+    // ---- fused qkv projection (RMSNorm in the prologue)
+    mg_stage_input<M>(c, p.x, p.H, p.attn_norm + (size_t)l * p.H, p.eps, red);
+    mg_gemv<M, MG_PLAIN>(c, p.NQKV, p.H, p.qkv, nullptr, s_res);
+    mg_grid_barrier(p, gen_base, bar_idx);
+    // ---- attention
+    {
+      const int items = M * p.nkv * p.splits;
+      for (int it = blockIdx.x; it < items; it += gridDim.x) {
+        const int split = it % p.splits, bk = it / p.splits;
+        mg_attention_item<G>(p, c, l, M, bk / p.nkv, bk % p.nkv, split, &s_last);
+      }
+    }
+    mg_grid_barrier(p, gen_base, bar_idx);
+    // ---- wo + residual
+    mg_stage_input<M>(c, p.attn, qdim, nullptr, 0.f, red);
+    mg_gemv<M, MG_RESIDUAL>(c, p.H, qdim, p.x, p.x, s_res);
+    mg_grid_barrier(p, gen_base, bar_idx);
+    // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
+    mg_stage_input<M>(c, p.x, p.H, p.ffn_norm + (size_t)l * p.H, p.eps, red);
+    mg_gemv<M, MG_SWIGLU>(c, 2 * p.F, p.H, p.hmlp, nullptr, s_res);
+    mg_grid_barrier(p, gen_base, bar_idx);
+    // ---- w2 + residual
+    mg_stage_input<M>(c, p.hmlp, p.F, nullptr, 0.f, red);
+    mg_gemv<M, MG_RESIDUAL>(c, p.H, p.F, p.x, p.x, s_res);
+    mg_grid_barrier(p, gen_base, bar_idx);
+  }
+  // ---- final norm + LM head
+  mg_stage_input<M>(c, p.x, p.H, p.final_norm, p.eps, red);
+  mg_gemv<M, MG_LOGITS>(c, p.V, p.H, p.logits, nullptr, s_res);
+  mg_grid_barrier(p, gen_base, bar_idx);
+  if (blockIdx.x == 0 && threadIdx.x == 32) *p.bar_gen = gen_base + (unsigned)bar_idx;
+}
+
+}  // namespace jl
+
+using namespace jl;
+
+extern "C" JL_API int jl_decode_mega_barriers(int L) { return 2 + 5 * L; }
+
+extern "C" JL_API size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, int num_sms) {
+  int splits = num_sms / (M * nkv);
+  if (splits < 1) splits = 1;
+  if (splits > 64) splits = 64;
+  const size_t parts = (size_t)M * nh * splits * (MG_HD + 2) * sizeof(float);
+  return parts + (size_t)M * nkv * sizeof(int) + 2 * sizeof(unsigned int) + 64;
+}
+
+// One decode step of the whole model for M <= 4 rows.  Weight pointers are the per-op stacks [L·N, K].
+extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
+                                     const void* lm_head, const void* attn_norm, const void* ffn_norm,
+                                     const void* final_norm, const void* embedding, const int* ids, void* x, void* qkv,
+                                     void* attn, void* hmlp, float* logits, void* k_cache, void* v_cache,
+                                     const float* cos_t, const float* sin_t, const int* cache_len, const int* pad_left,
+                                     void* scratch, int M, int L, int H, int F, int V, int vocab_full, int nh, int nkv,
+                                     int hd, int T, int max_pos, float eps, float scale, int num_sms, void* stream) {
+  JL_CHECK_ARG(M >= 1 && M <= 4, "jl_decode_mega: M=%d outside 1..4", M);
+  JL_CHECK_ARG(hd == MG_HD, "jl_decode_mega: head_dim=%d (only 128 is built)", hd);
+  JL_CHECK_ARG(nkv > 0 && nh % nkv == 0, "jl_decode_mega: nh=%d not a multiple of nkv=%d", nh, nkv);
+  const int G = nh / nkv;
+  JL_CHECK_ARG(G == 1 || G == 2 || G == 4 || G == 8, "jl_decode_mega: GQA group %d not in {1,2,4,8}", G);
+  const int NQKV = (nh + 2 * nkv) * hd;
+  JL_CHECK_ARG(H % 256 == 0 && F % 8 == 0 && V % 8 == 0 && NQKV % 8 == 0 && (2 * F) % 16 == 0,
+               "jl_decode_mega: H=%d must be a multiple of 256, F=%d and V=%d of 8", H, F, V);
+  if (num_sms <= 0) num_sms = 148;
+  MegaTmaps tm;
+  int rc;
+  if ((rc = make_tmap_2d_bf16_plain(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_2d_bf16_plain(&tm.m[1], wo_all, (uint64_t)L * H, nh * hd, nh * hd, 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_2d_bf16_plain(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_2d_bf16_plain(&tm.m[3], w2_all, (uint64_t)L * H, F, F, 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_2d_bf16_plain(&tm.m[4], lm_head, (uint64_t)V, H, H, 256, MG_GROUP))) return rc;
+
+  MegaParams p{};
+  p.L = L; p.H = H; p.F = F; p.V = V; p.nh = nh; p.nkv = nkv; p.NQKV = NQKV; p.vocab_full = vocab_full;
+  p.eps = eps; p.scale_log2 = scale * 1.4426950408889634f;
+  p.attn_norm = (const __nv_bfloat16*)attn_norm; p.ffn_norm = (const __nv_bfloat16*)ffn_norm;
+  p.final_norm = (const __nv_bfloat16*)final_norm; p.embedding = (const __nv_bfloat16*)embedding;
+  p.ids = ids; p.x = (__nv_bfloat16*)x; p.qkv = (__nv_bfloat16*)qkv; p.attn = (__nv_bfloat16*)attn;
+  p.hmlp = (__nv_bfloat16*)hmlp; p.logits = logits; p.kc = (__nv_bfloat16*)k_cache; p.vc = (__nv_bfloat16*)v_cache;
+  p.cos_t = cos_t; p.sin_t = sin_t; p.cache_len = cache_len; p.pad_left = pad_left;
+  int splits = num_sms / (M * nkv);
+  if (splits < 1) splits = 1;
+  if (splits > 64) splits = 64;
+  p.splits = splits;
+  const size_t part_floats = (size_t)M * nh * splits * MG_HD;
+  p.o_part = (float*)scratch;
+  p.ml_part = p.o_part + part_floats;
+  p.tickets = (int*)(p.ml_part + (size_t)M * nh * splits * 2);
+  uintptr_t bp = (reinterpret_cast<uintptr_t>(p.tickets + M * nkv) + 15) & ~(uintptr_t)15;
+  p.bar_counter = reinterpret_cast<unsigned int*>(bp);
+  p.bar_gen = p.bar_counter + 1;
+  p.T = T; p.max_pos = max_pos;
+
+  const int kmax = (H > F ? H : F) > nh * hd ? (H > F ? H : F) : nh * hd;
+  const size_t xin_bytes = (size_t)M * kmax * 2;
+  const size_t attn_bytes = (size_t)(MG_CONSUMERS * 2) * G * (MG_HD + 2) * sizeof(float);
+  const size_t fixed = 1024 + xin_bytes + attn_bytes + 64;
+  const size_t budget = 225 * 1024;
+  JL_CHECK_ARG(fixed + 4 * (MG_STAGE_BYTES + 16) <= budget, "jl_decode_mega: M=%d, F=%d leave no room for the weight ring", M, F);
+  int stages = (int)((budget - fixed) / (MG_STAGE_BYTES + 16));
+  if (stages > 12) stages = 12;
+  p.stages = stages;
+  const size_t smem = fixed + (size_t)stages * (MG_STAGE_BYTES + 16);
+
+  void (*kern)(const MegaTmaps, const MegaParams) = nullptr;
+#define JL_MG(M_, G_) if (M == M_ && G == G_) kern = decode_mega_kernel<M_, G_>;
+  JL_MG(1, 1) JL_MG(1, 2) JL_MG(1, 4) JL_MG(1, 8) JL_MG(2, 1) JL_MG(2, 2) JL_MG(2, 4) JL_MG(2, 8)
+  JL_MG(3, 1) JL_MG(3, 2) JL_MG(3, 4) JL_MG(3, 8) JL_MG(4, 1) JL_MG(4, 2) JL_MG(4, 4) JL_MG(4, 8)
+#undef JL_MG
+  JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_sms);
+  cfg.blockDim = dim3(MG_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident: the grid barrier cannot deadlock
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  count_launch();
+  JL_CUDA(cudaLaunchKernelEx(&cfg, kern, tm, p));
+  return JL_OK;
+}

@@ -89,6 +89,7 @@ class DecodeState:
 class B200Engine:
     def __init__(self, config: LLaMAConfig, embedding: torch.Tensor, layers: List[LayerWeights],
                  final_norm: torch.Tensor, lm_head: torch.Tensor, *, use_cuda_graph: bool = True,
+                 use_megakernel: bool = True,
                  tp: int = 1, rank: int = 0, comm: Any = None):
         """`layers` / `lm_head` hold this rank's tensor-parallel slice (Megatron layout of
         parallel/layout.py: wqkv/w13 cut on output rows, wo/w2 on the reduction dim, lm_head on vocab);
@@ -119,6 +120,27 @@ class B200Engine:
         self.cos, self.sin = cos.to(self.device), sin.to(self.device)
         self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
         self.warned_slow_prefill = False
+        self.use_megakernel = use_megakernel and self.tp == 1 and self.hd == 128 \
+            and config.hidden_size % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
+        self._stack_weights()
+
+    def _stack_weights(self) -> None:
+        """Store each op's weights of all layers contiguously ([L·N, K]); the per-layer tensors become views.
+        One TMA tensor map per op then describes the whole model (the persistent decode kernel streams
+        layer after layer through the same map)."""
+        def stack(name: str) -> torch.Tensor:
+            parts = [getattr(l, name) for l in self.layers]
+            big = torch.empty((len(parts) * parts[0].shape[0],) + tuple(parts[0].shape[1:]),
+                              dtype=parts[0].dtype, device=parts[0].device)
+            n = parts[0].shape[0]
+            for i, (l, t) in enumerate(zip(self.layers, parts)):
+                big[i * n:(i + 1) * n].copy_(t)
+                setattr(l, name, big[i * n:(i + 1) * n])       # drop the stand-alone copy
+            return big
+
+        self.wqkv_all, self.wo_all = stack("wqkv"), stack("wo")
+        self.w13_all, self.w2_all = stack("w13"), stack("w2")
+        self.attn_norm_all, self.ffn_norm_all = stack("attn_norm"), stack("ffn_norm")
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -272,7 +294,7 @@ class B200Engine:
     @torch.no_grad()
     def forward(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
                 position_ids: Optional[torch.Tensor] = None, cache: Optional[DeviceKVCache] = None,
-                with_head: bool = True, last_only: bool = False) -> ModelOutput:
+                with_head: bool = True, last_only: bool = False, gather_logits: bool = True) -> ModelOutput:
         B, S = input_ids.shape
         c = self.config
         own_cache = cache is None
@@ -300,14 +322,14 @@ class B200Engine:
             rows = S
         if with_head:
             logits = K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True)
-            if self.tp > 1:
+            if self.tp > 1 and gather_logits:
                 # API parity: `.logits` is the full vocabulary.  This gather is off the generate() path,
                 # which exchanges only top-k candidates (see _select_and_advance).
                 import torch.distributed as dist
                 parts = [torch.empty_like(logits) for _ in range(self.tp)]
                 dist.all_gather(parts, logits.contiguous(), group=self.comm.group)
                 logits = torch.cat(parts, dim=-1)
-            out.logits = logits.view(B, rows, c.vocab_size)
+            out.logits = logits.view(B, rows, -1)
             out.last_hidden_state = None
         else:
             out.last_hidden_state = K.rmsnorm(x, self.final_norm, c.rms_norm_eps).view(B, rows, c.hidden_size)
@@ -378,9 +400,26 @@ class B200Engine:
         c = self.config
         if self.comm is not None:
             self.comm.begin_sequence()
-        K.embed(st.ids, self.embedding, out=st.x)
-        x = self._layers(st.x, st.B, 1, cache, None, ws=st)
-        K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True, out=st.logits)
+        if self.use_megakernel and st.B <= 4:
+            # whole model in one persistent kernel: embedding → L layers → final norm → LM head
+            L = _lib.lib()
+            if getattr(st, "mega_scratch", None) is None:
+                nbytes = int(L.jl_decode_mega_scratch_bytes(st.B, self.nh, self.nkv, K.num_sms(self.device)))
+                st.mega_scratch = torch.zeros((nbytes + 3) // 4, dtype=torch.int32, device=self.device)
+            _lib.check(L.jl_decode_mega(
+                self.wqkv_all.data_ptr(), self.wo_all.data_ptr(), self.w13_all.data_ptr(), self.w2_all.data_ptr(),
+                self.lm_head.data_ptr(), self.attn_norm_all.data_ptr(), self.ffn_norm_all.data_ptr(),
+                self.final_norm.data_ptr(), self.embedding.data_ptr(), st.ids.data_ptr(), st.x.data_ptr(),
+                st.qkv.data_ptr(), st.attn.data_ptr(), st.mlp.data_ptr(), st.logits.data_ptr(),
+                cache.k.data_ptr(), cache.v.data_ptr(), self.cos.data_ptr(), self.sin.data_ptr(),
+                cache.len_dev.data_ptr(), cache.pad_left.data_ptr(), st.mega_scratch.data_ptr(), st.B,
+                len(self.layers), c.hidden_size, c.intermediate_size // self.tp, self.v_local, c.vocab_size,
+                self.nh, self.nkv, self.hd, cache.capacity, self.cos.shape[0], float(c.rms_norm_eps),
+                1.0 / (self.hd ** 0.5), K.num_sms(self.device), K._stream()), "jl_decode_mega")
+        else:
+            K.embed(st.ids, self.embedding, out=st.x)
+            x = self._layers(st.x, st.B, 1, cache, None, ws=st)
+            K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True, out=st.logits)
         self._select_and_advance(st, cache, sampling, eos, pad)
         if self.comm is not None:
             self.comm.end_sequence()
@@ -463,7 +502,7 @@ class B200Engine:
         st.cur_len.fill_(S)
         st.step.zero_()
         st.n_unfinished.fill_(B)
-        out = self.forward(input_ids, attention_mask=attention_mask, cache=cache, last_only=True)
+        out = self.forward(input_ids, attention_mask=attention_mask, cache=cache, last_only=True, gather_logits=False)
         st.logits.copy_(out.logits.view(B, -1))
         return cache
 

@@ -121,3 +121,31 @@ def test_public_generate_api_on_gpu():
     ids = torch.randint(3, cfg.vocab_size, (2, 7), generator=torch.Generator().manual_seed(6))
     out = model.generate(ids, params=tree_to(tree, device="cuda"), max_new_tokens=5, eos_token_id=-7)
     assert out.sequences.shape == (2, 12) and out.sequences.is_cuda
+
+
+@pytest.mark.parametrize("B", [1, 2, 4])
+def test_megakernel_step_matches_unfused_step(B):
+    """The persistent whole-model decode kernel against the per-op kernels, several consecutive steps."""
+    cfg = LLaMAConfig(vocab_size=1000, hidden_size=512, intermediate_size=1536, num_hidden_layers=3,
+                      num_attention_heads=4, num_key_value_heads=2, max_sequence_length=256, initializer_range=0.05)
+    tree = tree_to(ref.init_params(cfg, seed=2), dtype=torch.bfloat16, device="cuda")
+    engines = [B200Engine.from_tree(cfg, tree, use_cuda_graph=False, use_megakernel=flag) for flag in (True, False)]
+    assert engines[0].use_megakernel and not engines[1].use_megakernel
+    ids = torch.randint(3, cfg.vocab_size, (B, 37), generator=torch.Generator().manual_seed(7)).cuda()
+    mask = torch.ones(B, 37, dtype=torch.int32, device="cuda")
+    if B > 1:
+        mask[1, :6] = 0
+    outs = []
+    for eng in engines:
+        st = eng._decode_state(B, 64)
+        cache = eng.prepare(st, ids, mask, 0)
+        sampling = (False, 1.0, 0, 1.0, 0)
+        eng._select_and_advance_after_prefill(st, cache, sampling, -7, 0)
+        logits = []
+        for _ in range(5):
+            eng._decode_step(st, cache, sampling, -7, 0)
+            logits.append(st.logits.clone())
+        outs.append((torch.stack(logits), cache.k[:, :, :, :43].clone(), st.sequences.clone()))
+    assert rel(outs[0][0], outs[1][0]) < 2e-2
+    assert rel(outs[0][1], outs[1][1]) < 2e-2
+    assert int(engines[0]._decode_states[(B, 64)].mega_scratch[-8:].abs().sum()) >= 0    # scratch allocated
