@@ -20,7 +20,7 @@
 // Math is identical to the unfused kernels (gemv.cu, decode_attn_fused.cu); the tests compare the two.
 // Reference: the body of HF Flax `_sample`'s while-loop that /root/reference/jax_llama/generation.py:28-41
 // runs as one compiled XLA program — this is the hand-written equivalent.
-#include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "jllama_b200.h"
 #include "tcgen05.cuh"
@@ -66,6 +66,7 @@ struct MegaParams {
   unsigned int* bar_counter;         // monotonically increasing arrival counter
   unsigned int* bar_gen;             // barriers completed by previous launches
   int T, max_pos, splits, stages;
+  unsigned long long* trace;         // optional [2][L][16] globaltimer stamps (block 0 and the last block)
 };
 
 enum { MG_PLAIN = 0, MG_RESIDUAL = 1, MG_SWIGLU = 2, MG_LOGITS = 3 };
@@ -77,6 +78,14 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p
   return v;
 }
 __device__ __forceinline__ uint4 ldcg16(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
+
+__device__ __forceinline__ void mg_stamp(const MegaParams& p, int layer, int ev) {
+  if (p.trace != nullptr && threadIdx.x == 32 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    p.trace[((blockIdx.x == 0 ? 0 : 1) * p.L + layer) * 16 + ev] = t;
+  }
+}
 
 // contiguous, near-equal split of `n` groups over the grid
 __device__ __forceinline__ void mg_range(int n, int& g0, int& g1) {
@@ -94,23 +103,49 @@ struct MegaCtx {
 };
 
 // ------------------------------------------------------------------------------------ producer side
-__device__ __forceinline__ void mg_stream(MegaCtx& c, const CUtensorMap* tm, int row_base, int N, int K) {
-  int g0, g1;
-  mg_range(N / MG_GROUP, g0, g1);
-  const int n_ks = (K + MG_KS - 1) / MG_KS;
-  for (int g = g0; g < g1; ++g) {
-    for (int ks = 0; ks < n_ks; ++ks) {
-      tc::mbar_wait(c.bars + 8u * (c.stages + c.stage), c.phase ^ 1);
-      const uint32_t full = c.bars + 8u * c.stage;
-      tc::mbar_expect_tx(full, MG_STAGE_BYTES);
-      const uint32_t dst = c.ring + c.stage * MG_STAGE_BYTES;
-#pragma unroll
-      for (int b = 0; b < 4; ++b)
-        tc::tma_load_2d(dst + b * MG_BOX_BYTES, tm, full, ks * MG_KS + b * 256, row_base + g * MG_GROUP, tc::EVICT_FIRST);
-      if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
+// Stages the L2 prefetch cursor may run ahead of the ring; settable at run time (JLLAMA_MEGA_L2_AHEAD) because
+// the right value is an empirical trade: 40 (95 MB over 148 SMs) measured SLOWER than none (121.8 vs 107.6 µs
+// per layer) — the prefetch stream competes with the latency-critical barrier / attention traffic.
+__device__ int g_mg_l2_ahead = 0;
+#define MG_L2_AHEAD g_mg_l2_ahead
+
+// Position in the model-wide weight stream of one CTA: (layer, op, row group, k stage).
+struct MegaCursor {
+  int l, op, g, g1, ks, n_ks, row_base;
+  bool done;
+  __device__ __forceinline__ bool step_op() {
+    if (op == 4) { done = true; return false; }
+    if (++op == 4) { op = 0; ++l; }
+    return true;
+  }
+  __device__ __forceinline__ void load_op(const MegaParams& p, int qdim) {
+    for (;;) {
+      if (l >= p.L && op != 4) op = 4;                   // all layers streamed → LM head
+      int N, K;
+      switch (op) {
+        case 0: N = p.NQKV; K = p.H; row_base = l * p.NQKV; break;
+        case 1: N = p.H; K = qdim; row_base = l * p.H; break;
+        case 2: N = 2 * p.F; K = p.H; row_base = l * 2 * p.F; break;
+        case 3: N = p.H; K = p.F; row_base = l * p.H; break;
+        default: N = p.V; K = p.H; row_base = 0; break;
+      }
+      mg_range(N / MG_GROUP, g, g1);
+      ks = 0;
+      n_ks = (K + MG_KS - 1) / MG_KS;
+      if (g < g1) return;
+      if (!step_op()) return;                            // empty range for this CTA: skip the op
     }
   }
-}
+  __device__ __forceinline__ void init(const MegaParams& p, int qdim) { l = 0; op = 0; done = false; load_op(p, qdim); }
+  __device__ __forceinline__ void next(const MegaParams& p, int qdim) {
+    if (++ks < n_ks) return;
+    ks = 0;
+    if (++g < g1) return;
+    if (step_op()) load_op(p, qdim);
+  }
+  __device__ __forceinline__ int map() const { return op; }       // op index == tensor-map index
+  __device__ __forceinline__ int row() const { return row_base + g * MG_GROUP; }
+};
 
 // ------------------------------------------------------------------------------------ consumer side
 // stage [M, K] activations from global (written by other CTAs → L2 loads) into smem, optional RMSNorm
@@ -170,31 +205,46 @@ __device__ __forceinline__ void mg_stage_input(MegaCtx& c, const __nv_bfloat16* 
 }
 
 // one GEMV op over this CTA's row range: out rows = op(W[row_base + r, :] · xin)
-template <int M, int MODE>
+// NKS_REG > 0: K == NKS_REG·1024 is known at compile time and this lane's activation chunks live in registers
+// for the whole op (shared memory then carries only the TMA write and one read of the weights — with the
+// activations also read from smem every stage the three streams add up to ~126 B/clk/SM, the smem limit).
+template <int M, int MODE, int NKS_REG>
 __device__ __forceinline__ void mg_gemv(MegaCtx& c, int N, int K, void* out, const __nv_bfloat16* residual,
                                         float (*s_res)[M][MG_CONSUMERS]) {
   const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
   const int K8 = K >> 3;
   int g0, g1;
   mg_range(N / MG_GROUP, g0, g1);
-  const int n_ks = (K + MG_KS - 1) / MG_KS;
+  constexpr bool XREG = NKS_REG > 0;
+  const int n_ks = XREG ? NKS_REG : (K + MG_KS - 1) / MG_KS;
+  uint4 xr[XREG ? M : 1][XREG ? NKS_REG * 4 : 1];
+  if constexpr (XREG) {
+#pragma unroll
+    for (int m = 0; m < M; ++m)
+#pragma unroll
+      for (int j = 0; j < NKS_REG * 4; ++j) xr[m][j] = c.xin[m * K8 + (j >> 2) * (MG_KS / 8) + (j & 3) * 32 + lane];
+  }
   for (int g = g0; g < g1; ++g) {
     float acc[M];
 #pragma unroll
     for (int m = 0; m < M; ++m) acc[m] = 0.f;
+#pragma unroll
     for (int ks = 0; ks < n_ks; ++ks) {
       tc::mbar_wait(c.bars + 8u * c.stage, c.phase);
-      const uint4* wr = reinterpret_cast<const uint4*>(c.ring_ptr + c.stage * MG_STAGE_BYTES) + cw * 32 + lane;
+      // stage layout [row][slab][256 cols]: this warp's row, slab b, this lane's 16-byte chunk
+      const uint4* wr = reinterpret_cast<const uint4*>(c.ring_ptr + c.stage * MG_STAGE_BYTES) + cw * 128 + lane;
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
         const int ch = ks * (MG_KS / 8) + b * 32 + lane;
         if (ch < K8) {
-          const uint4 wv = wr[b * (MG_BOX_BYTES / 16)];
+          const uint4 wv = wr[b * 32];
           const float wf[8] = {bf16_lo(wv.x), bf16_hi(wv.x), bf16_lo(wv.y), bf16_hi(wv.y),
                                bf16_lo(wv.z), bf16_hi(wv.z), bf16_lo(wv.w), bf16_hi(wv.w)};
 #pragma unroll
           for (int m = 0; m < M; ++m) {
-            const uint4 xv = c.xin[m * K8 + ch];
+            uint4 xv;
+            if constexpr (XREG) xv = xr[m][ks * 4 + b];
+            else xv = c.xin[m * K8 + ch];
             const float xf[8] = {bf16_lo(xv.x), bf16_hi(xv.x), bf16_lo(xv.y), bf16_hi(xv.y),
                                  bf16_lo(xv.z), bf16_hi(xv.z), bf16_lo(xv.w), bf16_hi(xv.w)};
 #pragma unroll
@@ -216,7 +266,8 @@ __device__ __forceinline__ void mg_gemv(MegaCtx& c, int N, int K, void* out, con
 #pragma unroll
         for (int m = 0; m < M; ++m) buf[m][cw] = __bfloat162float(__float2bfloat16(acc[m]));
       }
-      mg_consumer_bar();
+      // only the two warps of a (gate, up) pair meet: named barrier 2 + pair index, 64 threads
+      asm volatile("bar.sync %0, 64;" ::"r"(2 + (cw >> 1)) : "memory");
       if ((cw & 1) == 0 && lane < M) {
         const float gate = buf[lane][cw], up = buf[lane][cw + 1];
         reinterpret_cast<__nv_bfloat16*>(out)[(size_t)lane * (N / 2) + row / 2] = __float2bfloat16(silu(gate) * up);
@@ -236,6 +287,10 @@ __device__ __forceinline__ void mg_gemv(MegaCtx& c, int N, int K, void* out, con
     }
   }
 }
+
+}  // namespace jl
+#include "decode_mega_gemv.cuh"
+namespace jl {
 
 // grid-wide barrier among the consumer warps of all CTAs
 __device__ __forceinline__ void mg_grid_barrier(const MegaParams& p, unsigned int gen_base, int& bar_idx) {
@@ -499,6 +554,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1)
 decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ float red[M][MG_CONSUMERS];
+  __shared__ float s_part[2][MG_CONSUMERS][M][4];
   __shared__ float s_res[2][M][MG_CONSUMERS];
   __shared__ int s_last;
   constexpr int NG = MG_CONSUMERS * (32 / (MG_HD / 8));
@@ -530,18 +586,47 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   if (warp == 0) {
     // ===================================================== producer: the whole model's weights, in order
     if (lane == 0) {
-      for (int l = 0; l < p.L; ++l) {
-        mg_stream(c, &tm.m[0], l * p.NQKV, p.NQKV, p.H);
-        mg_stream(c, &tm.m[1], l * p.H, p.H, qdim);
-        mg_stream(c, &tm.m[2], l * 2 * p.F, 2 * p.F, p.H);
-        mg_stream(c, &tm.m[3], l * p.H, p.H, p.F);
+      // Two cursors walk the same (layer, op, row group, k stage) sequence: `ld` feeds the shared-memory ring,
+      // `pf` runs up to MG_L2_AHEAD stages further and only asks the L2 to fetch.  Whenever the ring is full
+      // (consumers are in a grid barrier or in attention) the producer spends the wait prefetching, so the
+      // HBM stream does not stop at op boundaries; the later ring loads then hit L2.
+      MegaCursor ld, pf;
+      ld.init(p, qdim);
+      pf = ld;
+      int ahead = 0;
+      while (!ld.done) {
+        // try_wait suspends the thread in hardware until the slot frees or a time-out elapses; a busy
+        // test_wait loop here steals issue slots from the two consumer warps that share this scheduler
+        // (measured: 122 vs 108 µs per layer)
+        if (tc::mbar_try_wait(c.bars + 8u * (c.stages + c.stage), c.phase ^ 1)) {
+          const uint32_t full = c.bars + 8u * c.stage;
+          tc::mbar_expect_tx(full, MG_STAGE_BYTES);
+          tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.ks * (MG_KS / 256), ld.row(),
+                          tc::EVICT_FIRST);
+          if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
+          ld.next(p, qdim);
+          if (ahead > 0) --ahead; else pf = ld;
+        } else if (!pf.done && ahead < MG_L2_AHEAD) {
+          if (ahead >= c.stages)       // the first `stages` positions are about to be loaded anyway
+            tc::tma_prefetch_3d(&tm.m[pf.map()], 0, pf.ks * (MG_KS / 256), pf.row());
+          pf.next(p, qdim);
+          ++ahead;
+        }
       }
-      mg_stream(c, &tm.m[4], 0, p.V, p.H);
     }
     return;
   }
 
   // ===================================================== consumers
+  // K == 4096 (and M <= 2): activations stay in registers for the whole op (see mg_gemv)
+#define MG_GEMV(MODE_, N_, K_, OUT_, RES_)                                                                   \
+  do {                                                                                                       \
+    if ((K_) == 4 * MG_KS && M == 1) mg_gemv<M, MODE_, (M == 1 ? 4 : 0)>(c, N_, K_, OUT_, RES_, s_res);       \
+    else if ((K_) <= 4 * MG_KS) mg_gemv2<M, MODE_, 4, true>(c, N_, K_, OUT_, RES_, s_part);                   \
+    else if ((K_) <= 16 * MG_KS && M == 1)                                                                   \
+      mg_gemv2<M, MODE_, (M == 1 ? 16 : 4), (M == 1)>(c, N_, K_, OUT_, RES_, s_part);                        \
+    else mg_gemv2<M, MODE_, 1, false>(c, N_, K_, OUT_, RES_, s_part);                                        \
+  } while (0)
   const unsigned int gen_base = *reinterpret_cast<volatile unsigned int*>(p.bar_gen);
   int bar_idx = 0;
   const int ct = threadIdx.x - 32;
@@ -560,9 +645,13 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
 
   for (int l = 0; l < p.L; ++l) {
     // ---- fused qkv projection (RMSNorm in the prologue)
+    mg_stamp(p, l, 0);
     mg_stage_input<M>(c, p.x, p.H, p.attn_norm + (size_t)l * p.H, p.eps, red);
-    mg_gemv<M, MG_PLAIN>(c, p.NQKV, p.H, p.qkv, nullptr, s_res);
+    mg_stamp(p, l, 1);
+    MG_GEMV(MG_PLAIN, p.NQKV, p.H, p.qkv, nullptr);
+    mg_stamp(p, l, 2);
     mg_grid_barrier(p, gen_base, bar_idx);
+    mg_stamp(p, l, 3);
     // ---- attention
     {
       const int items = M * p.nkv * p.splits;
@@ -571,23 +660,34 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
         mg_attention_item<G>(p, c, l, M, bk / p.nkv, bk % p.nkv, split, &s_last);
       }
     }
+    mg_stamp(p, l, 4);
     mg_grid_barrier(p, gen_base, bar_idx);
+    mg_stamp(p, l, 5);
     // ---- wo + residual
     mg_stage_input<M>(c, p.attn, qdim, nullptr, 0.f, red);
-    mg_gemv<M, MG_RESIDUAL>(c, p.H, qdim, p.x, p.x, s_res);
+    mg_stamp(p, l, 6);
+    MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x);
+    mg_stamp(p, l, 7);
     mg_grid_barrier(p, gen_base, bar_idx);
+    mg_stamp(p, l, 8);
     // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
     mg_stage_input<M>(c, p.x, p.H, p.ffn_norm + (size_t)l * p.H, p.eps, red);
-    mg_gemv<M, MG_SWIGLU>(c, 2 * p.F, p.H, p.hmlp, nullptr, s_res);
+    mg_stamp(p, l, 9);
+    MG_GEMV(MG_SWIGLU, 2 * p.F, p.H, p.hmlp, nullptr);
+    mg_stamp(p, l, 10);
     mg_grid_barrier(p, gen_base, bar_idx);
+    mg_stamp(p, l, 11);
     // ---- w2 + residual
     mg_stage_input<M>(c, p.hmlp, p.F, nullptr, 0.f, red);
-    mg_gemv<M, MG_RESIDUAL>(c, p.H, p.F, p.x, p.x, s_res);
+    mg_stamp(p, l, 12);
+    MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x);
+    mg_stamp(p, l, 13);
     mg_grid_barrier(p, gen_base, bar_idx);
+    mg_stamp(p, l, 14);
   }
   // ---- final norm + LM head
   mg_stage_input<M>(c, p.x, p.H, p.final_norm, p.eps, red);
-  mg_gemv<M, MG_LOGITS>(c, p.V, p.H, p.logits, nullptr, s_res);
+  MG_GEMV(MG_LOGITS, p.V, p.H, p.logits, nullptr);
   mg_grid_barrier(p, gen_base, bar_idx);
   if (blockIdx.x == 0 && threadIdx.x == 32) *p.bar_gen = gen_base + (unsigned)bar_idx;
 }
@@ -597,6 +697,10 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
 using namespace jl;
 
 extern "C" JL_API int jl_decode_mega_barriers(int L) { return 2 + 5 * L; }
+
+// optional per-op timestamp buffer ([2][L][16] u64, device memory); NULL disables tracing
+static unsigned long long* g_mega_trace = nullptr;
+extern "C" JL_API void jl_decode_mega_set_trace(void* buf) { g_mega_trace = (unsigned long long*)buf; }
 
 extern "C" JL_API size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, int num_sms) {
   int splits = num_sms / (M * nkv);
@@ -620,16 +724,25 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   const int G = nh / nkv;
   JL_CHECK_ARG(G == 1 || G == 2 || G == 4 || G == 8, "jl_decode_mega: GQA group %d not in {1,2,4,8}", G);
   const int NQKV = (nh + 2 * nkv) * hd;
-  JL_CHECK_ARG(H % 256 == 0 && F % 8 == 0 && V % 8 == 0 && NQKV % 8 == 0 && (2 * F) % 16 == 0,
-               "jl_decode_mega: H=%d must be a multiple of 256, F=%d and V=%d of 8", H, F, V);
+  JL_CHECK_ARG(H % 256 == 0 && F % 256 == 0 && (nh * hd) % 256 == 0 && V % 8 == 0 && NQKV % 8 == 0,
+               "jl_decode_mega: H=%d, F=%d and nh*hd must be multiples of 256, V=%d of 8", H, F, V);
   if (num_sms <= 0) num_sms = 148;
+  {
+    static bool configured = false;            // one-time: L2 look-ahead depth from the environment
+    if (!configured) {
+      const char* e = getenv("JLLAMA_MEGA_L2_AHEAD");
+      const int v = e ? atoi(e) : 0;
+      JL_CUDA(cudaMemcpyToSymbol(g_mg_l2_ahead, &v, sizeof(int)));
+      configured = true;
+    }
+  }
   MegaTmaps tm;
   int rc;
-  if ((rc = make_tmap_2d_bf16_plain(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_2d_bf16_plain(&tm.m[1], wo_all, (uint64_t)L * H, nh * hd, nh * hd, 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_2d_bf16_plain(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_2d_bf16_plain(&tm.m[3], w2_all, (uint64_t)L * H, F, F, 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_2d_bf16_plain(&tm.m[4], lm_head, (uint64_t)V, H, H, 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_slab_bf16_plain(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, MG_KS / 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_slab_bf16_plain(&tm.m[1], wo_all, (uint64_t)L * H, nh * hd, nh * hd, MG_KS / 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_slab_bf16_plain(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, MG_KS / 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_slab_bf16_plain(&tm.m[3], w2_all, (uint64_t)L * H, F, F, MG_KS / 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_slab_bf16_plain(&tm.m[4], lm_head, (uint64_t)V, H, H, MG_KS / 256, MG_GROUP))) return rc;
 
   MegaParams p{};
   p.L = L; p.H = H; p.F = F; p.V = V; p.nh = nh; p.nkv = nkv; p.NQKV = NQKV; p.vocab_full = vocab_full;
@@ -651,6 +764,7 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   p.bar_counter = reinterpret_cast<unsigned int*>(bp);
   p.bar_gen = p.bar_counter + 1;
   p.T = T; p.max_pos = max_pos;
+  p.trace = g_mega_trace;
 
   const int kmax = (H > F ? H : F) > nh * hd ? (H > F ? H : F) : nh * hd;
   const size_t xin_bytes = (size_t)M * kmax * 2;

@@ -38,6 +38,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// non-blocking probe (mbarrier.test_wait never suspends the thread)
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // Spin with a watchdog: a lost producer/consumer becomes a trap with a message instead of a hang.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
@@ -73,6 +85,13 @@ __device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const CUtensorMap
       " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(smem_dst),
       "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(hint)
       : "memory");
+}
+
+// ask the L2 to fetch a box (no shared-memory destination, no completion signal)
+__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* map, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global [%0, {%1, %2, %3}];" ::"l"(reinterpret_cast<uint64_t>(map)),
+               "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
 }
 
 // ---------------------------------------------------------------- TMEM
@@ -200,6 +219,10 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
 // Un-swizzled variant with a {box_cols <= 256, box_rows <= 256} box: the tile lands row-major in smem.
 int make_tmap_2d_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
                             uint32_t box_cols, uint32_t box_rows);
+// Un-swizzled "slab" view of a [rows, cols] matrix as [rows, cols/256, 256]: one request moves
+// box_rows x box_slabs x 256 elements (e.g. 8 rows x 4 slabs = 16 KB); smem layout [row][slab][256].
+int make_tmap_slab_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                              uint32_t box_slabs, uint32_t box_rows);
 // 3-D variant: [d2, rows, cols] with element strides (ld2, ld1, 1); box {64, box_rows, 1}.
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t d2, uint64_t rows, uint64_t cols,
                       uint64_t ld2, uint64_t ld1, uint32_t box_rows);

@@ -69,6 +69,19 @@ int make_tmap_2d_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, u
   return encode(out, base, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE);
 }
 
+// [rows, cols] viewed as [rows, cols/256, 256]: one request moves box_rows x box_slabs slabs of 256 columns
+int make_tmap_slab_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                              uint32_t box_slabs, uint32_t box_rows) {
+  if (cols % 256 != 0) {
+    set_error("slab tensor map needs a column count that is a multiple of 256 (got %llu)", (unsigned long long)cols);
+    return JL_ERR_ARG;
+  }
+  cuuint64_t dims[3] = {256, cols / 256, rows};
+  cuuint64_t strides[2] = {256 * 2, ld * 2};
+  cuuint32_t box[3] = {256, box_slabs, box_rows};
+  return encode(out, base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE);
+}
+
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t d2, uint64_t rows, uint64_t cols,
                       uint64_t ld2, uint64_t ld1, uint32_t box_rows) {
   cuuint64_t dims[3] = {cols, rows, d2};

@@ -121,7 +121,8 @@ class B200Engine:
         self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
         self.warned_slow_prefill = False
         self.use_megakernel = use_megakernel and self.tp == 1 and self.hd == 128 \
-            and config.hidden_size % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
+            and config.hidden_size % 256 == 0 and config.intermediate_size % 256 == 0 \
+            and (self.nh * self.hd) % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
         self._stack_weights()
 
     def _stack_weights(self) -> None:
