@@ -38,7 +38,7 @@ constexpr int MG_HD = 128;
 constexpr int MG_KPI = 4;
 
 struct alignas(64) MegaTmaps {
-  CUtensorMap m[5];          // wqkv_all, wo_all, w13_all, w2_all, lm_head
+  CUtensorMap m[6];          // wqkv_all, wo_all, w13_all, w2_all (8-row boxes), lm_head, w2_all (4-row boxes)
 };
 
 struct MegaParams {
@@ -67,6 +67,7 @@ struct MegaParams {
   unsigned int* bar_gen;             // barriers completed by previous launches
   int T, max_pos, splits, stages;
   unsigned long long* trace;         // optional [2][L][16] globaltimer stamps (block 0 and the last block)
+  int gemv_mode;                     // 0: row-owner warps when K == 4096, column-owner otherwise; 1: always column-owner
 };
 
 enum { MG_PLAIN = 0, MG_RESIDUAL = 1, MG_SWIGLU = 2, MG_LOGITS = 3 };
@@ -83,7 +84,7 @@ __device__ __forceinline__ void mg_stamp(const MegaParams& p, int layer, int ev)
   if (p.trace != nullptr && threadIdx.x == 32 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    p.trace[((blockIdx.x == 0 ? 0 : 1) * p.L + layer) * 16 + ev] = t;
+    p.trace[((blockIdx.x == 0 ? 0 : 1) * p.L + layer) * 32 + ev] = t;
   }
 }
 
@@ -111,7 +112,7 @@ __device__ int g_mg_l2_ahead = 0;
 
 // Position in the model-wide weight stream of one CTA: (layer, op, row group, k stage).
 struct MegaCursor {
-  int l, op, g, g1, ks, n_ks, row_base;
+  int l, op, g, g1, ks, n_ks, row_base, rows;      // rows: weight rows per stage of this op (8, or 4 for w2)
   bool done;
   __device__ __forceinline__ bool step_op() {
     if (op == 4) { done = true; return false; }
@@ -126,10 +127,11 @@ struct MegaCursor {
         case 0: N = p.NQKV; K = p.H; row_base = l * p.NQKV; break;
         case 1: N = p.H; K = qdim; row_base = l * p.H; break;
         case 2: N = 2 * p.F; K = p.H; row_base = l * 2 * p.F; break;
-        case 3: N = p.H; K = p.F; row_base = l * p.H; break;
+        case 3: N = p.H; K = p.F; row_base = l * p.H; break;      // 4-row groups: see decode_mega_gemv.cuh
         default: N = p.V; K = p.H; row_base = 0; break;
       }
-      mg_range(N / MG_GROUP, g, g1);
+      rows = MG_GROUP;        // (4-row groups for w2 were tried: 8 KB stages double the per-stage overhead, 33 vs 23 µs)
+      mg_range(N / rows, g, g1);
       ks = 0;
       n_ks = (K + MG_KS - 1) / MG_KS;
       if (g < g1) return;
@@ -143,8 +145,9 @@ struct MegaCursor {
     if (++g < g1) return;
     if (step_op()) load_op(p, qdim);
   }
-  __device__ __forceinline__ int map() const { return op; }       // op index == tensor-map index
-  __device__ __forceinline__ int row() const { return row_base + g * MG_GROUP; }
+  __device__ __forceinline__ int map() const { return op; }
+  __device__ __forceinline__ uint32_t bytes() const { return (uint32_t)rows * (MG_KS * 2); }
+  __device__ __forceinline__ int row() const { return row_base + g * rows; }
 };
 
 // ------------------------------------------------------------------------------------ consumer side
@@ -335,6 +338,7 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
   const int lo = first + split * chunk;
   const int hi = lo + chunk < len ? lo + chunk : len;
 
+  mg_stamp(p, layer, 16);
   const float4 cs4 = __ldg(reinterpret_cast<const float4*>(p.cos_t) + (size_t)pos * LPK + lig);
   const float4 sn4 = __ldg(reinterpret_cast<const float4*>(p.sin_t) + (size_t)pos * LPK + lig);
   const float cs[4] = {cs4.x, cs4.y, cs4.z, cs4.w}, sn[4] = {sn4.x, sn4.y, sn4.z, sn4.w};
@@ -421,6 +425,7 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
     }
   };
 
+  mg_stamp(p, layer, 17);
   constexpr int UNR = G <= 4 ? 2 : 1;
   for (int base = lo; base < hi; base += UNR * KEYS_PER_ITER) {
     uint4 kr[UNR][MG_KPI], vr[UNR][MG_KPI];
@@ -438,6 +443,7 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
     for (int u = 0; u < UNR; ++u) process(kr[u], vr[u], base + u * KEYS_PER_ITER + gid * MG_KPI);
   }
 
+  mg_stamp(p, layer, 18);
   // the new token: rotate k, append (k, v), fold it in from registers (split 0, consumer warp 0)
   if (split == 0 && warp == 0) {
     const uint4 ka = ldcg16(row + (size_t)(nh + kvh) * HD + lig * 8);
@@ -476,6 +482,7 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
     }
   }
 
+  mg_stamp(p, layer, 19);
   // fold the lane-groups of this CTA
 #pragma unroll
   for (int g = 0; g < G; ++g) {
@@ -506,47 +513,36 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
       if (d == 0) { p.ml_part[pi * 2] = Mx; p.ml_part[pi * 2 + 1] = Ls; }
     }
   }
-  if (p.splits == 1) { mg_consumer_bar(); return; }
+  (void)s_last;
+  mg_stamp(p, layer, 20);
+  mg_consumer_bar();                 // s_attn is reused by this CTA's next item
+}
 
-  __threadfence();
-  mg_consumer_bar();
-  if (ct == 0) {
-    int* t = p.tickets + b * p.nkv + kvh;
-    const int prev = atomicAdd(t, 1);
-    *s_last = prev == p.splits - 1;
-    if (*s_last) *t = 0;
-  }
-  mg_consumer_bar();
-  if (*s_last) {
-    __threadfence();
-    float* s_m = c.s_attn;
-    float* s_l = s_m + G * 64;
-    for (int i = ct; i < G * p.splits; i += MG_CT) {
-      const int g = i / p.splits, sp = i - g * p.splits;
-      const size_t bh = (size_t)b * nh + kvh * G + g;
-      s_m[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2);
-      s_l[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2 + 1);
-    }
-    mg_consumer_bar();
-    for (int idx = ct; idx < G * HD; idx += MG_CT) {
-      const int g = idx / HD, d = idx - g * HD;
-      const size_t bh = (size_t)b * nh + kvh * G + g;
-      float Mx = -INFINITY;
-      for (int sp = 0; sp < p.splits; ++sp) Mx = fmaxf(Mx, s_m[g * 64 + sp]);
-      const float Ms = Mx == -INFINITY ? 0.f : Mx;
-      float acc = 0.f, Ls = 0.f;
-      const float* op = p.o_part + bh * p.splits * HD + d;
+// Merge of the split-KV partials, spread over the whole grid (one output element per thread): runs after a
+// grid barrier.  The earlier "last CTA of each kv head merges" ticket scheme put atomic + two dependent L2
+// round trips of a single CTA on the critical path of every layer (13 µs per attention phase).
+__device__ __forceinline__ void mg_attn_merge(const MegaParams& p, int M) {
+  const int ct = threadIdx.x - 32;
+  const int total = M * p.nh * MG_HD;
+  for (int idx = blockIdx.x * MG_CT + ct; idx < total; idx += gridDim.x * MG_CT) {
+    const int bh = idx / MG_HD, d = idx - bh * MG_HD;
+    const float2* ml = reinterpret_cast<const float2*>(p.ml_part) + (size_t)bh * p.splits;
+    const float* op = p.o_part + (size_t)bh * p.splits * MG_HD + d;
+    float Mx = -INFINITY;
 #pragma unroll 8
-      for (int sp = 0; sp < p.splits; ++sp) {
-        const float w = exp2f(s_m[g * 64 + sp] - Ms);
-        const float ov = __ldcg(op + (size_t)sp * HD);
-        acc += w > 0.f ? w * ov : 0.f;
-        Ls += w * s_l[g * 64 + sp];
-      }
-      p.attn[bh * HD + d] = __float2bfloat16(Ls > 0.f ? acc / Ls : 0.f);
+    for (int sp = 0; sp < p.splits; ++sp) Mx = fmaxf(Mx, __ldcg(ml + sp).x);
+    const float Ms = Mx == -INFINITY ? 0.f : Mx;
+    float acc = 0.f, Ls = 0.f;
+#pragma unroll 8
+    for (int sp = 0; sp < p.splits; ++sp) {
+      const float2 e = __ldcg(ml + sp);
+      const float w = exp2f(e.x - Ms);
+      const float ov = __ldcg(op + (size_t)sp * MG_HD);
+      acc += w > 0.f ? w * ov : 0.f;
+      Ls += w * e.y;
     }
+    p.attn[idx] = __float2bfloat16(Ls > 0.f ? acc / Ls : 0.f);
   }
-  mg_consumer_bar();
 }
 
 template <int M, int G>
@@ -573,7 +569,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 5; ++i) tc::prefetch_tensormap(&tm.m[i]);
+    for (int i = 0; i < 6; ++i) tc::prefetch_tensormap(&tm.m[i]);
     for (int s = 0; s < p.stages; ++s) {
       tc::mbar_init(c.bars + 8u * s, 1);
       tc::mbar_init(c.bars + 8u * (p.stages + s), MG_CONSUMERS);
@@ -600,7 +596,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
         // (measured: 122 vs 108 µs per layer)
         if (tc::mbar_try_wait(c.bars + 8u * (c.stages + c.stage), c.phase ^ 1)) {
           const uint32_t full = c.bars + 8u * c.stage;
-          tc::mbar_expect_tx(full, MG_STAGE_BYTES);
+          tc::mbar_expect_tx(full, ld.bytes());
           tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.ks * (MG_KS / 256), ld.row(),
                           tc::EVICT_FIRST);
           if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
@@ -619,13 +615,14 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
 
   // ===================================================== consumers
   // K == 4096 (and M <= 2): activations stay in registers for the whole op (see mg_gemv)
-#define MG_GEMV(MODE_, N_, K_, OUT_, RES_)                                                                   \
+#define MG_GEMV(MODE_, N_, K_, OUT_, RES_, ROWS_)                                                            \
   do {                                                                                                       \
-    if ((K_) == 4 * MG_KS && M == 1) mg_gemv<M, MODE_, (M == 1 ? 4 : 0)>(c, N_, K_, OUT_, RES_, s_res);       \
-    else if ((K_) <= 4 * MG_KS) mg_gemv2<M, MODE_, 4, true>(c, N_, K_, OUT_, RES_, s_part);                   \
+    if ((K_) == 4 * MG_KS && M == 1 && ROWS_ == 8 && p.gemv_mode == 0)                                       \
+      mg_gemv<M, MODE_, (M == 1 ? 4 : 0)>(c, N_, K_, OUT_, RES_, s_res);                                     \
+    else if ((K_) <= 4 * MG_KS) mg_gemv2<M, MODE_, 4, true, ROWS_>(c, N_, K_, OUT_, RES_, s_part);            \
     else if ((K_) <= 16 * MG_KS && M == 1)                                                                   \
-      mg_gemv2<M, MODE_, (M == 1 ? 16 : 4), (M == 1)>(c, N_, K_, OUT_, RES_, s_part);                        \
-    else mg_gemv2<M, MODE_, 1, false>(c, N_, K_, OUT_, RES_, s_part);                                        \
+      mg_gemv2<M, MODE_, (M == 1 ? 16 : 4), (M == 1), ROWS_>(c, N_, K_, OUT_, RES_, s_part);                 \
+    else mg_gemv2<M, MODE_, 1, false, ROWS_>(c, N_, K_, OUT_, RES_, s_part);                                 \
   } while (0)
   const unsigned int gen_base = *reinterpret_cast<volatile unsigned int*>(p.bar_gen);
   int bar_idx = 0;
@@ -648,7 +645,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     mg_stamp(p, l, 0);
     mg_stage_input<M>(c, p.x, p.H, p.attn_norm + (size_t)l * p.H, p.eps, red);
     mg_stamp(p, l, 1);
-    MG_GEMV(MG_PLAIN, p.NQKV, p.H, p.qkv, nullptr);
+    MG_GEMV(MG_PLAIN, p.NQKV, p.H, p.qkv, nullptr, 8);
     mg_stamp(p, l, 2);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 3);
@@ -662,32 +659,36 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     }
     mg_stamp(p, l, 4);
     mg_grid_barrier(p, gen_base, bar_idx);
+    if (p.splits > 1) {                      // grid-uniform: every CTA takes the same branch
+      mg_attn_merge(p, M);
+      mg_grid_barrier(p, gen_base, bar_idx);
+    }
     mg_stamp(p, l, 5);
     // ---- wo + residual
     mg_stage_input<M>(c, p.attn, qdim, nullptr, 0.f, red);
     mg_stamp(p, l, 6);
-    MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x);
+    MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x, 8);
     mg_stamp(p, l, 7);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 8);
     // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
     mg_stage_input<M>(c, p.x, p.H, p.ffn_norm + (size_t)l * p.H, p.eps, red);
     mg_stamp(p, l, 9);
-    MG_GEMV(MG_SWIGLU, 2 * p.F, p.H, p.hmlp, nullptr);
+    MG_GEMV(MG_SWIGLU, 2 * p.F, p.H, p.hmlp, nullptr, 8);
     mg_stamp(p, l, 10);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 11);
     // ---- w2 + residual
     mg_stage_input<M>(c, p.hmlp, p.F, nullptr, 0.f, red);
     mg_stamp(p, l, 12);
-    MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x);
+    MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x, 8);
     mg_stamp(p, l, 13);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 14);
   }
   // ---- final norm + LM head
   mg_stage_input<M>(c, p.x, p.H, p.final_norm, p.eps, red);
-  MG_GEMV(MG_LOGITS, p.V, p.H, p.logits, nullptr);
+  MG_GEMV(MG_LOGITS, p.V, p.H, p.logits, nullptr, 8);
   mg_grid_barrier(p, gen_base, bar_idx);
   if (blockIdx.x == 0 && threadIdx.x == 32) *p.bar_gen = gen_base + (unsigned)bar_idx;
 }
@@ -743,6 +744,7 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, MG_KS / 256, MG_GROUP))) return rc;
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[3], w2_all, (uint64_t)L * H, F, F, MG_KS / 256, MG_GROUP))) return rc;
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[4], lm_head, (uint64_t)V, H, H, MG_KS / 256, MG_GROUP))) return rc;
+  if ((rc = make_tmap_slab_bf16_plain(&tm.m[5], w2_all, (uint64_t)L * H, F, F, MG_KS / 256, 4))) return rc;
 
   MegaParams p{};
   p.L = L; p.H = H; p.F = F; p.V = V; p.nh = nh; p.nkv = nkv; p.NQKV = NQKV; p.vocab_full = vocab_full;
@@ -765,6 +767,10 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   p.bar_gen = p.bar_counter + 1;
   p.T = T; p.max_pos = max_pos;
   p.trace = g_mega_trace;
+  {
+    static const int mode = [] { const char* e = getenv("JLLAMA_MEGA_GEMV"); return e ? atoi(e) : 0; }();
+    p.gemv_mode = mode;
+  }
 
   const int kmax = (H > F ? H : F) > nh * hd ? (H > F ? H : F) : nh * hd;
   const size_t xin_bytes = (size_t)M * kmax * 2;

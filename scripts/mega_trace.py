@@ -11,28 +11,34 @@ from jax_llama_b200 import preset  # noqa: E402
 from jax_llama_b200.models.engine import B200Engine  # noqa: E402
 from jax_llama_b200.ops import _lib  # noqa: E402
 
-cfg = preset("llama3-8b")
+EV = 32
+cfg = preset(os.environ.get("MODEL", "llama3-8b"))
 eng = B200Engine.random_init(cfg, "cuda:0", use_cuda_graph=False)
 L = cfg.num_hidden_layers
-ids = torch.randint(0, cfg.vocab_size, (1, 2048), device="cuda")
-st = eng._decode_state(1, 2048 + 32)
+B = int(os.environ.get("BATCH", "1"))
+ids = torch.randint(0, cfg.vocab_size, (B, 2048), device="cuda")
+st = eng._decode_state(B, 2048 + 32)
 cache = eng.prepare(st, ids, None, 0)
 samp = (False, 1.0, 0, 1.0, 0)
 eng._select_and_advance_after_prefill(st, cache, samp, -1, 0)
 for _ in range(3):
     eng._decode_step(st, cache, samp, -1, 0)
-trace = torch.zeros(2 * L * 16, dtype=torch.int64, device="cuda")
+trace = torch.zeros(2 * L * EV, dtype=torch.int64, device="cuda")
 lib = _lib.lib()
 lib.jl_decode_mega_set_trace.argtypes = [C.c_void_p]
 lib.jl_decode_mega_set_trace(trace.data_ptr())
 eng._decode_step(st, cache, samp, -1, 0)
 torch.cuda.synchronize()
 lib.jl_decode_mega_set_trace(None)
-t = trace.view(2, L, 16).cpu().double()
-names = ["stage_qkv", "gemv_qkv", "bar", "attn", "bar", "stage_wo", "gemv_wo", "bar", "stage_w13", "gemv_w13", "bar",
-         "stage_w2", "gemv_w2", "bar"]
+t = trace.view(2, L, EV).cpu().double()
+names = ["stage_qkv", "gemv_qkv", "bar", "attn", "bar(+merge)", "stage_wo", "gemv_wo", "bar", "stage_w13", "gemv_w13",
+         "bar", "stage_w2", "gemv_w2", "bar"]
+lo, hi = 4, L - 4
 for blk in range(2):
-    d = (t[blk, 4:28, 1:15] - t[blk, 4:28, 0:14]) / 1e3          # µs, layers 4..27
+    d = (t[blk, lo:hi, 1:15] - t[blk, lo:hi, 0:14]) / 1e3          # µs
     print(f"block {'0' if blk == 0 else 'last'}: " + "  ".join(f"{n}={v:.1f}" for n, v in zip(names, d.mean(0).tolist())))
-    print(f"   layer total {((t[blk, 4:28, 14] - t[blk, 4:28, 0]) / 1e3).mean():.1f} us; layer-to-layer "
-          f"{((t[blk, 5:28, 0] - t[blk, 4:27, 0]) / 1e3).mean():.1f} us")
+    print(f"   layer total {((t[blk, lo:hi, 14] - t[blk, lo:hi, 0]) / 1e3).mean():.1f} us; layer-to-layer "
+          f"{((t[blk, lo + 1:hi, 0] - t[blk, lo:hi - 1, 0]) / 1e3).mean():.1f} us")
+a = (t[0, lo:hi, 16:21] - t[0, lo:hi, 3:4]) / 1e3
+print("block 0 attention internals (µs after the phase starts): " + "  ".join(
+    f"{n}={v:.1f}" for n, v in zip(["setup", "q+rope", "kv_loop", "new_tok", "fold+write"], a.mean(0).tolist())))
