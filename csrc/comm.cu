@@ -30,30 +30,6 @@ struct PeerTable {
   int* flags[MAX_TP];                // peer p's flag array base
 };
 
-__device__ __forceinline__ void st_release_sys(int* p, int v) {
-  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ int ld_acquire_sys(const int* p) {
-  int v;
-  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ float ld_relaxed_sys_f32(const float* p) {
-  float v;
-  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void wait_flag(const int* flag, int epoch, int rank, int peer, int what) {
-  unsigned spins = 0;
-  while (ld_acquire_sys(flag) < epoch) {
-    if (++spins > (1u << 27)) {
-      printf("jllama_b200: rank %d timed out waiting for peer %d (epoch %d, kind %d, block %d)\n", rank, peer,
-             epoch, what, (int)blockIdx.x);
-      __trap();
-    }
-  }
-}
-
 struct GemvArParams {
   const __nv_bfloat16* x;         // [M, K] local activation slice (K = K_total / tp)
   const __nv_bfloat16* w;         // [N, K] local weight slice

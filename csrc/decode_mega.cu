@@ -41,7 +41,17 @@ struct alignas(64) MegaTmaps {
   CUtensorMap m[6];          // wqkv_all, wo_all, w13_all, w2_all (8-row boxes), lm_head, w2_all (4-row boxes)
 };
 
+// Tensor-parallel all-reduce state (tp == 1: unused).  Same inbox / flag protocol as comm.cu.
+struct MegaAr {
+  float* inbox[8];                   // peer p's inbox, mapped into this process: [parity][src][M][H] fp32
+  int* flags[8];                     // peer p's flag array
+  const int* seq_ptr;                // device epoch counter (bumped once per step by the host-side sequence)
+  size_t parity_stride;              // floats between the two parity halves
+  int flag_offset, tp, rank;
+};
+
 struct MegaParams {
+  MegaAr ar;
   int L, H, F, V, nh, nkv, NQKV, vocab_full;
   float eps, scale_log2;
   const __nv_bfloat16* attn_norm;    // [L, H]
@@ -101,7 +111,17 @@ struct MegaCtx {
   float* s_attn;              // attention fold scratch
   int stages;
   int stage; uint32_t phase;  // ring cursor (producer and consumers keep separate copies)
+  const MegaAr* ar;           // tensor-parallel state; ar_parity selects the inbox half of the current all-reduce
+  int ar_parity;
 };
+
+// row-parallel epilogue under tensor parallelism: hand this rank's fp32 partial to every peer's inbox
+template <int M>
+__device__ __forceinline__ void mg_push_partial(const MegaCtx& c, int m, int row, int N, float v) {
+  const MegaAr& a = *c.ar;
+  const size_t off = (size_t)c.ar_parity * a.parity_stride + ((size_t)a.rank * M + m) * N + row;
+  for (int peer = 0; peer < a.tp; ++peer) a.inbox[peer][off] = v;
+}
 
 // ------------------------------------------------------------------------------------ producer side
 // Stages the L2 prefetch cursor may run ahead of the ring; settable at run time (JLLAMA_MEGA_L2_AHEAD) because
@@ -282,8 +302,10 @@ __device__ __forceinline__ void mg_gemv(MegaCtx& c, int N, int K, void* out, con
         if constexpr (MODE == MG_LOGITS) {
           reinterpret_cast<float*>(out)[(size_t)m * N + row] = v;
         } else {
-          if constexpr (MODE == MG_RESIDUAL)
+          if constexpr (MODE == MG_RESIDUAL) {
+            if (c.ar->tp > 1) { mg_push_partial<M>(c, m, row, N, v); continue; }      // reduced in mg_ar_finish
             v = __bfloat162float(__float2bfloat16(v)) + __bfloat162float(__ldcg(residual + (size_t)m * N + row));
+          }
           reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * N + row] = __float2bfloat16(v);
         }
       }
@@ -545,6 +567,33 @@ __device__ __forceinline__ void mg_attn_merge(const MegaParams& p, int M) {
   }
 }
 
+// Second half of the in-kernel one-shot all-reduce (tp > 1): publish this CTA's slice to every peer, wait for
+// the same-index CTA of every peer (all ranks cut rows identically), reduce in rank order (bit-identical on
+// all ranks), add the residual and store the new residual-stream rows.  The local grid barrier follows.
+template <int M>
+__device__ __forceinline__ void mg_ar_finish(const MegaParams& p, const MegaCtx& c, int epoch, int N) {
+  const MegaAr& a = p.ar;
+  const int ct = threadIdx.x - 32;
+  __threadfence_system();
+  mg_consumer_bar();
+  if (ct < a.tp) {
+    st_release_sys(a.flags[ct] + a.flag_offset + a.rank * gridDim.x + blockIdx.x, epoch);
+    wait_flag(a.flags[a.rank] + a.flag_offset + ct * gridDim.x + blockIdx.x, epoch, a.rank, ct, 2);
+  }
+  mg_consumer_bar();
+  int g0, g1;
+  mg_range(N / MG_GROUP, g0, g1);
+  const int nrows = (g1 - g0) * MG_GROUP;
+  const float* mine = a.inbox[a.rank] + (size_t)c.ar_parity * a.parity_stride;
+  for (int i = ct; i < nrows * M; i += MG_CT) {
+    const int m = i / nrows, row = g0 * MG_GROUP + (i - m * nrows);
+    float s = 0.f;
+    for (int src = 0; src < a.tp; ++src) s += ld_relaxed_sys_f32(mine + ((size_t)src * M + m) * N + row);
+    const float y = __bfloat162float(__float2bfloat16(s)) + __bfloat162float(__ldcg(p.x + (size_t)m * N + row));
+    p.x[(size_t)m * N + row] = __float2bfloat16(y);
+  }
+}
+
 template <int M, int G>
 __global__ void __launch_bounds__(MG_THREADS, 1)
 decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
@@ -566,6 +615,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   c.xin = reinterpret_cast<uint4*>(after + (size_t)NG * G * (MG_HD + 2) * sizeof(float));
   (void)kmax;
   c.stage = 0; c.phase = 0;
+  c.ar = &p.ar; c.ar_parity = 0;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -626,6 +676,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   } while (0)
   const unsigned int gen_base = *reinterpret_cast<volatile unsigned int*>(p.bar_gen);
   int bar_idx = 0;
+  const int ar_base = p.ar.tp > 1 ? __ldcg(p.ar.seq_ptr) : 0;      // epoch of collective j is ar_base + j + 1
   const int ct = threadIdx.x - 32;
 
   // embedding rows → residual stream (each CTA copies a slice), then everyone sees x
@@ -667,7 +718,9 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     // ---- wo + residual
     mg_stage_input<M>(c, p.attn, qdim, nullptr, 0.f, red);
     mg_stamp(p, l, 6);
+    c.ar_parity = (ar_base + 2 * l + 1) & 1;
     MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x, 8);
+    if (p.ar.tp > 1) mg_ar_finish<M>(p, c, ar_base + 2 * l + 1, p.H);
     mg_stamp(p, l, 7);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 8);
@@ -681,7 +734,9 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     // ---- w2 + residual
     mg_stage_input<M>(c, p.hmlp, p.F, nullptr, 0.f, red);
     mg_stamp(p, l, 12);
+    c.ar_parity = (ar_base + 2 * l + 2) & 1;
     MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x, 8);
+    if (p.ar.tp > 1) mg_ar_finish<M>(p, c, ar_base + 2 * l + 2, p.H);
     mg_stamp(p, l, 13);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 14);
@@ -718,7 +773,9 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
                                      void* attn, void* hmlp, float* logits, void* k_cache, void* v_cache,
                                      const float* cos_t, const float* sin_t, const int* cache_len, const int* pad_left,
                                      void* scratch, int M, int L, int H, int F, int V, int vocab_full, int nh, int nkv,
-                                     int hd, int T, int max_pos, float eps, float scale, int num_sms, void* stream) {
+                                     int hd, int T, int max_pos, float eps, float scale, int num_sms, int tp, int rank,
+                                     void* const* peer_inbox, void* const* peer_flags, size_t inbox_parity_stride_floats,
+                                     int flag_offset, const int* seq_ptr, void* stream) {
   JL_CHECK_ARG(M >= 1 && M <= 4, "jl_decode_mega: M=%d outside 1..4", M);
   JL_CHECK_ARG(hd == MG_HD, "jl_decode_mega: head_dim=%d (only 128 is built)", hd);
   JL_CHECK_ARG(nkv > 0 && nh % nkv == 0, "jl_decode_mega: nh=%d not a multiple of nkv=%d", nh, nkv);
@@ -766,6 +823,13 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   p.bar_counter = reinterpret_cast<unsigned int*>(bp);
   p.bar_gen = p.bar_counter + 1;
   p.T = T; p.max_pos = max_pos;
+  p.ar.tp = tp < 1 ? 1 : tp; p.ar.rank = rank; p.ar.seq_ptr = seq_ptr; p.ar.parity_stride = inbox_parity_stride_floats;
+  p.ar.flag_offset = flag_offset;
+  if (p.ar.tp > 1) {
+    JL_CHECK_ARG(p.ar.tp <= 8 && peer_inbox && peer_flags && seq_ptr, "jl_decode_mega: tensor-parallel launch needs peer tables");
+    JL_CHECK_ARG((size_t)p.ar.tp * M * H <= inbox_parity_stride_floats, "jl_decode_mega: inbox too small for the all-reduce");
+    for (int i = 0; i < p.ar.tp; ++i) { p.ar.inbox[i] = (float*)peer_inbox[i]; p.ar.flags[i] = (int*)peer_flags[i]; }
+  }
   p.trace = g_mega_trace;
   {
     static const int mode = [] { const char* e = getenv("JLLAMA_MEGA_GEMV"); return e ? atoi(e) : 0; }();

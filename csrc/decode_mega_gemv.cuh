@@ -123,9 +123,12 @@ __device__ __forceinline__ void mg_gemv2(MegaCtx& c, int N, int K, void* out, co
         reinterpret_cast<float*>(out)[(size_t)m * N + row] = v;
       } else {
         float y = v;
-        if constexpr (MODE == MG_RESIDUAL)
-          y = __bfloat162float(__float2bfloat16(v)) + __bfloat162float(__ldcg(residual + (size_t)m * N + row));
-        reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * N + row] = __float2bfloat16(y);
+        bool pushed = false;
+        if constexpr (MODE == MG_RESIDUAL) {
+          if (c.ar->tp > 1) { mg_push_partial<M>(c, m, row, N, v); pushed = true; }     // reduced in mg_ar_finish
+          else y = __bfloat162float(__float2bfloat16(v)) + __bfloat162float(__ldcg(residual + (size_t)m * N + row));
+        }
+        if (!pushed) reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * N + row] = __float2bfloat16(y);
       }
     }
   }

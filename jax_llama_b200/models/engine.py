@@ -120,10 +120,19 @@ class B200Engine:
         self.cos, self.sin = cos.to(self.device), sin.to(self.device)
         self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
         self.warned_slow_prefill = False
-        self.use_megakernel = use_megakernel and self.tp == 1 and self.hd == 128 \
-            and config.hidden_size % 256 == 0 and config.intermediate_size % 256 == 0 \
+        self.use_megakernel = use_megakernel and self.hd == 128 \
+            and config.hidden_size % 256 == 0 and (config.intermediate_size // self.tp) % 256 == 0 \
             and (self.nh * self.hd) % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
         self._stack_weights()
+
+    def _mega_tp_args(self) -> Tuple:
+        """(tp, rank, peer inbox table, peer flag table, parity stride in floats, flag offset, epoch counter)."""
+        if self.tp == 1:
+            return (1, 0, None, None, 0, 0, None)
+        cm = self.comm
+        grid = K.num_sms(self.device)
+        off = cm.flag_block(("mega", grid), 8 * grid)
+        return (self.tp, self.rank, cm.inbox_ptrs, cm.flag_ptrs, cm.parity_bytes // 4, off, cm.seq.data_ptr())
 
     def _stack_weights(self) -> None:
         """Store each op's weights of all layers contiguously ([L·N, K]); the per-layer tensors become views.
@@ -416,7 +425,9 @@ class B200Engine:
                 cache.len_dev.data_ptr(), cache.pad_left.data_ptr(), st.mega_scratch.data_ptr(), st.B,
                 len(self.layers), c.hidden_size, c.intermediate_size // self.tp, self.v_local, c.vocab_size,
                 self.nh, self.nkv, self.hd, cache.capacity, self.cos.shape[0], float(c.rms_norm_eps),
-                1.0 / (self.hd ** 0.5), K.num_sms(self.device), K._stream()), "jl_decode_mega")
+                1.0 / (self.hd ** 0.5), K.num_sms(self.device), *self._mega_tp_args(), K._stream()), "jl_decode_mega")
+            if self.tp > 1:
+                self.comm.call_index += 2 * len(self.layers)      # the kernel ran 2 all-reduces per layer
         else:
             K.embed(st.ids, self.embedding, out=st.x)
             x = self._layers(st.x, st.B, 1, cache, None, ws=st)

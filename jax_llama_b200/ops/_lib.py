@@ -35,7 +35,7 @@ _SIGNATURES = {
     "jl_decode_attn_fused": (i32, [vp, vp, vp, fp, fp, ip, ip, vp, vp, i32, i32, i32, i32, i32, i32, f32, i32, vp]),
     "jl_decode_mega_scratch_bytes": (sz, [i32, i32, i32, i32]),
     "jl_decode_mega": (i32, [vp] * 9 + [ip] + [vp] * 4 + [fp, vp, vp, fp, fp, ip, ip, vp] + [i32] * 11 +
-                       [f32, f32, i32, vp]),
+                       [f32, f32, i32, i32, i32, vp, vp, sz, i32, ip, vp]),
     "jl_argmax": (i32, [fp, i32, i32, i32, i32, fp, ip, vp]),
     "jl_topk": (i32, [fp, i32, i32, i32, i32, i32, fp, ip, vp]),
     "jl_sample": (i32, [fp, ip, i32, i32, sz, i32, i32, f32, f32, u64, ip, ip, vp]),
