@@ -97,6 +97,11 @@ class PeerComm:
                 inbox[r], flags[r] = self._open(hi), self._open(hf)
         self.inbox_ptrs = (C.c_void_p * MAX_TP)(*inbox)
         self.flag_ptrs = (C.c_void_p * MAX_TP)(*flags)
+        # the small all-gather gets the top 64 KB of each parity half to itself: the all-reduce region is read
+        # with tag matching (decode_mega.cu) and must never see unrelated payload bytes
+        self.gather_region = 64 << 10
+        self.gather_ptrs = (C.c_void_p * MAX_TP)(*[(p + self.parity_bytes - self.gather_region) if p else 0
+                                                   for p in inbox])
         self.seq = torch.zeros(1, dtype=torch.int32, device=device)     # device epoch counter
         self.call_index = 0                                               # collectives since the last bump
         self._flag_blocks: Dict[Tuple, int] = {}
@@ -175,9 +180,11 @@ class PeerComm:
         if nbytes % 16:
             raise ValueError("allgather_small needs a multiple of 16 bytes")
         L = _L()
+        if self.tp * nbytes > self.gather_region:
+            raise ValueError(f"allgather_small payload {nbytes} B x {self.tp} exceeds the {self.gather_region} B region")
         off = self.flag_block(("ag",), MAX_TP)
         _lib.check(L.jl_allgather_small(src.data_ptr(), out.data_ptr(), nbytes, nbytes, self.tp, self.rank,
-                                        self.inbox_ptrs, self.flag_ptrs, self.parity_bytes, off,
+                                        self.gather_ptrs, self.flag_ptrs, self.parity_bytes, off,
                                         self.seq.data_ptr(), self.call_index, K._stream()), "jl_allgather_small")
         self.call_index += 1
         return out

@@ -11,9 +11,14 @@ from jax_llama_b200 import preset  # noqa: E402
 from jax_llama_b200.models.engine import B200Engine  # noqa: E402
 from jax_llama_b200.ops import _lib  # noqa: E402
 
+from jax_llama_b200.parallel.comm import init_distributed  # noqa: E402
+
 EV = 32
+rank, world, local = init_distributed()
+torch.cuda.set_device(local)
 cfg = preset(os.environ.get("MODEL", "llama3-8b"))
-eng = B200Engine.random_init(cfg, "cuda:0", use_cuda_graph=False)
+kw = dict(tp=world, rank=rank) if world > 1 else {}
+eng = B200Engine.random_init(cfg, f"cuda:{local}", use_cuda_graph=False, **kw)
 L = cfg.num_hidden_layers
 B = int(os.environ.get("BATCH", "1"))
 ids = torch.randint(0, cfg.vocab_size, (B, 2048), device="cuda")
@@ -31,6 +36,8 @@ eng._decode_step(st, cache, samp, -1, 0)
 torch.cuda.synchronize()
 lib.jl_decode_mega_set_trace(None)
 t = trace.view(2, L, EV).cpu().double()
+if rank != 0:
+    sys.exit(0)
 names = ["stage_qkv", "gemv_qkv", "bar", "attn", "bar(+merge)", "stage_wo", "gemv_wo", "bar", "stage_w13", "gemv_w13",
          "bar", "stage_w2", "gemv_w2", "bar"]
 lo, hi = 4, L - 4
