@@ -344,9 +344,25 @@ __device__ __forceinline__ void mg_grid_barrier(const MegaParams& p, unsigned in
 }
 
 // RoPE + KV append + split-KV attention for one (b, kv head, split) item + ticket merge (8 consumer warps)
+struct MgPos { int len, first; float cs[4], sn[4]; };      // per-step constants of one batch row (this lane's pairs)
+
+__device__ __forceinline__ MgPos mg_pos(const MegaParams& p, int b, int lig) {
+  MgPos r;
+  int len = __ldcg(p.cache_len);
+  r.len = len > p.T ? p.T : len;
+  r.first = p.pad_left ? p.pad_left[b] : 0;
+  int pos = r.len - r.first;
+  pos = pos < 0 ? 0 : (pos >= p.max_pos ? p.max_pos - 1 : pos);
+  const float4 cs4 = __ldg(reinterpret_cast<const float4*>(p.cos_t) + (size_t)pos * (MG_HD / 8) + lig);
+  const float4 sn4 = __ldg(reinterpret_cast<const float4*>(p.sin_t) + (size_t)pos * (MG_HD / 8) + lig);
+  r.cs[0] = cs4.x; r.cs[1] = cs4.y; r.cs[2] = cs4.z; r.cs[3] = cs4.w;
+  r.sn[0] = sn4.x; r.sn[1] = sn4.y; r.sn[2] = sn4.z; r.sn[3] = sn4.w;
+  return r;
+}
+
 template <int G>
 __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const MegaCtx& c, int layer, int M, int b,
-                                                  int kvh, int split, int* s_last) {
+                                                  int kvh, int split, int* s_last, const MgPos& pp) {
   constexpr int HD = MG_HD, LPK = HD / 8, GPW = 32 / LPK, NG = MG_CONSUMERS * GPW;
   constexpr int KEYS_PER_ITER = NG * MG_KPI;
   const int nh = p.nkv * G;
@@ -356,22 +372,23 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
   float (*s_o)[G][HD] = reinterpret_cast<float (*)[G][HD]>(c.s_attn);
   float (*s_ml)[G][2] = reinterpret_cast<float (*)[G][2]>(c.s_attn + NG * G * HD);
 
-  int len = __ldcg(p.cache_len);
-  len = len > p.T ? p.T : len;
-  const int first = p.pad_left ? p.pad_left[b] : 0;
+  const int len = pp.len, first = pp.first;
   const int valid = len - first > 0 ? len - first : 0;
-  int pos = len - first;
-  pos = pos < 0 ? 0 : (pos >= p.max_pos ? p.max_pos - 1 : pos);
   int chunk = (valid + p.splits - 1) / p.splits;
   chunk = ((chunk + KEYS_PER_ITER - 1) / KEYS_PER_ITER) * KEYS_PER_ITER;
   const int lo = first + split * chunk;
   const int hi = lo + chunk < len ? lo + chunk : len;
 
   mg_stamp(p, layer, 16);
-  const float4 cs4 = __ldg(reinterpret_cast<const float4*>(p.cos_t) + (size_t)pos * LPK + lig);
-  const float4 sn4 = __ldg(reinterpret_cast<const float4*>(p.sin_t) + (size_t)pos * LPK + lig);
-  const float cs[4] = {cs4.x, cs4.y, cs4.z, cs4.w}, sn[4] = {sn4.x, sn4.y, sn4.z, sn4.w};
+  const float cs[4] = {pp.cs[0], pp.cs[1], pp.cs[2], pp.cs[3]}, sn[4] = {pp.sn[0], pp.sn[1], pp.sn[2], pp.sn[3]};
   const __nv_bfloat16* row = p.qkv + (size_t)b * p.NQKV;
+  // the new token's k, v are fetched together with q (consumed after the KV loop by split 0 / warp 0)
+  const bool owns_new = split == 0 && warp == 0;
+  uint4 ka = make_uint4(0, 0, 0, 0), va = ka;
+  if (owns_new) {
+    ka = ldcg16(row + (size_t)(nh + kvh) * HD + lig * 8);
+    va = ldcg16(row + (size_t)(nh + p.nkv + kvh) * HD + lig * 8);
+  }
 
   float qf[G][8];
 #pragma unroll
@@ -474,9 +491,7 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
 
   mg_stamp(p, layer, 18);
   // the new token: rotate k, append (k, v), fold it in from registers (split 0, consumer warp 0)
-  if (split == 0 && warp == 0) {
-    const uint4 ka = ldcg16(row + (size_t)(nh + kvh) * HD + lig * 8);
-    const uint4 va = ldcg16(row + (size_t)(nh + p.nkv + kvh) * HD + lig * 8);
+  if (owns_new) {
     const uint32_t kw[4] = {ka.x, ka.y, ka.z, ka.w};
     uint32_t kr4[4];
 #pragma unroll
@@ -557,18 +572,39 @@ __device__ __forceinline__ void mg_attn_merge(const MegaParams& p, int M) {
     const int bh = idx / MG_HD, d = idx - bh * MG_HD;
     const float2* ml = reinterpret_cast<const float2*>(p.ml_part) + (size_t)bh * p.splits;
     const float* op = p.o_part + (size_t)bh * p.splits * MG_HD + d;
-    float Mx = -INFINITY;
-#pragma unroll 8
-    for (int sp = 0; sp < p.splits; ++sp) Mx = fmaxf(Mx, __ldcg(ml + sp).x);
-    const float Ms = Mx == -INFINITY ? 0.f : Mx;
     float acc = 0.f, Ls = 0.f;
+    if (p.splits <= 32) {
+      // issue every load of this output up front: one L2 round trip instead of two dependent ones
+      float2 e[32];
+      float ov[32];
+#pragma unroll
+      for (int sp = 0; sp < 32; ++sp) {
+        if (sp < p.splits) { e[sp] = __ldcg(ml + sp); ov[sp] = __ldcg(op + (size_t)sp * MG_HD); }
+        else { e[sp] = make_float2(-INFINITY, 0.f); ov[sp] = 0.f; }
+      }
+      float Mx = -INFINITY;
+#pragma unroll
+      for (int sp = 0; sp < 32; ++sp) Mx = fmaxf(Mx, e[sp].x);
+      const float Ms = Mx == -INFINITY ? 0.f : Mx;
+#pragma unroll
+      for (int sp = 0; sp < 32; ++sp) {
+        const float w = exp2f(e[sp].x - Ms);
+        acc += w > 0.f ? w * ov[sp] : 0.f;
+        Ls += w * e[sp].y;
+      }
+    } else {
+      float Mx = -INFINITY;
 #pragma unroll 8
-    for (int sp = 0; sp < p.splits; ++sp) {
-      const float2 e = __ldcg(ml + sp);
-      const float w = exp2f(e.x - Ms);
-      const float ov = __ldcg(op + (size_t)sp * MG_HD);
-      acc += w > 0.f ? w * ov : 0.f;
-      Ls += w * e.y;
+      for (int sp = 0; sp < p.splits; ++sp) Mx = fmaxf(Mx, __ldcg(ml + sp).x);
+      const float Ms = Mx == -INFINITY ? 0.f : Mx;
+#pragma unroll 8
+      for (int sp = 0; sp < p.splits; ++sp) {
+        const float2 e = __ldcg(ml + sp);
+        const float w = exp2f(e.x - Ms);
+        const float ov = __ldcg(op + (size_t)sp * MG_HD);
+        acc += w > 0.f ? w * ov : 0.f;
+        Ls += w * e.y;
+      }
     }
     p.attn[idx] = __float2bfloat16(Ls > 0.f ? acc / Ls : 0.f);
   }
@@ -690,6 +726,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   } while (0)
   const unsigned int gen_base = *reinterpret_cast<volatile unsigned int*>(p.bar_gen);
   int bar_idx = 0;
+  const MgPos pos0 = mg_pos(p, 0, lane % (MG_HD / 8));      // batch row 0: constant for the whole step
   const int ar_base = p.ar.tp > 1 ? __ldcg(p.ar.seq_ptr) : 0;      // epoch of collective j is ar_base + j + 1
   const int ct = threadIdx.x - 32;
 
@@ -719,7 +756,8 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
       const int items = M * p.nkv * p.splits;
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
         const int split = it % p.splits, bk = it / p.splits;
-        mg_attention_item<G>(p, c, l, M, bk / p.nkv, bk % p.nkv, split, &s_last);
+        const int bb = bk / p.nkv;
+        mg_attention_item<G>(p, c, l, M, bb, bk % p.nkv, split, &s_last, M == 1 ? pos0 : mg_pos(p, bb, lane % (MG_HD / 8)));
       }
     }
     mg_stamp(p, l, 4);
