@@ -111,6 +111,7 @@ def main() -> None:
     ap.add_argument("--prompt-len", type=int, default=2048)
     ap.add_argument("--prefill-reps", type=int, default=3)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-baseline", action="store_true", help="skip the same-box PyTorch (cuBLAS + SDPA + NCCL) arm")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
@@ -220,6 +221,35 @@ def main() -> None:
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
 
+    # ---------------------------------------------------------------- same-box library yardstick
+    baseline = None
+    if not args.no_baseline:
+        try:
+            from jax_llama_b200.models.baseline import TorchBaseline
+            tb = TorchBaseline(eng, B, max_len)
+            barrier()
+            b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            b0.record()
+            tb.prefill(ids_dev)
+            b1.record()
+            torch.cuda.synchronize()
+            base_prefill_ms = max_over_ranks(b0.elapsed_time(b1))
+            for _ in range(args.warmup):
+                tb.decode_step()
+            barrier()
+            b0.record()
+            for _ in range(args.steps):
+                tb.decode_step()
+            b1.record()
+            barrier()
+            base_ms = max_over_ranks(b0.elapsed_time(b1)) / args.steps
+            baseline = {"impl": "torch F.linear (cuBLAS) + SDPA + NCCL, CUDA-graphed, same weights",
+                        "decode_tokens_per_sec": round(B / (base_ms / 1e3), 2), "ms_per_step": round(base_ms, 4),
+                        "prefill_tokens_per_sec_first_call": round(B * P / (base_prefill_ms / 1e3), 1)}
+            del tb
+        except Exception as e:  # noqa: BLE001  (the yardstick must never take the product number down with it)
+            baseline = {"error": f"{type(e).__name__}: {str(e)[:160]}"}
+
     if rank == 0:
         value = B * args.steps / (ms_total / 1e3)
         weight_bytes = sum(t.numel() * 2 for l in eng.layers for t in (l.wqkv, l.wo, l.w13, l.w2)) + eng.lm_head.numel() * 2
@@ -247,6 +277,9 @@ def main() -> None:
                     "h2d_bytes_per_step": stream2.h2d_bytes, "d2h_bytes_per_step": stream2.d2h_bytes,
                     "api": "LLaMA.stream(...).step(feed)"},
             "gpu_launches": int(gpu_launches), "clocks": clocks,
+            "same_box_library_baseline": baseline,
+            "speedup_vs_library_baseline": (round(baseline["ms_per_step"] / ms_per_step, 3)
+                                            if baseline and "ms_per_step" in baseline else None),
         }
         print(json.dumps(line))
     if world > 1:
