@@ -266,3 +266,8 @@ extern "C" JL_API int jl_comm_bump(int* seq_ptr, int n, void* stream) {
   JL_CUDA(launch_pdl(bump_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, seq_ptr, n));
   return JL_OK;
 }
+
+extern "C" JL_API int jl_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream) {
+  JL_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return JL_OK;
+}

@@ -89,6 +89,12 @@ __device__ __forceinline__ uint4 ldg_cached(const void* p) {
   return *reinterpret_cast<const uint4*>(p);
 }
 
+// device-scope acquire load (grid barriers, in-kernel ready counters)
+__device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 // ---- system-scope flag protocol used by the NVLink peer-memory collectives (comm.cu, decode_mega.cu)
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
   asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

@@ -83,11 +83,6 @@ struct MegaParams {
 enum { MG_PLAIN = 0, MG_RESIDUAL = 1, MG_SWIGLU = 2, MG_LOGITS = 3 };
 
 __device__ __forceinline__ void mg_consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(MG_CT) : "memory"); }
-__device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 __device__ __forceinline__ uint4 ldcg16(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
 
 __device__ __forceinline__ void mg_stamp(const MegaParams& p, int layer, int ev) {

@@ -34,13 +34,29 @@ struct GemmParams {
   int a_blocks, b_blocks;   // tile counts
   int stages;
   uint64_t hint_a, hint_b;
+  // ---- tensor-parallel, sequence-parallel prefill (COMM != 0) ------------------------------------------
+  // COMM_SCATTER (GEMM → reduce-scatter): the D tile of token rows [m0, m0+128) is stored, as this rank's bf16
+  // partial, straight into the row owner's receive buffer over NVLink: owner = m0 / mloc,
+  // dst = scatter_out[owner] + ((rank·mloc + row − owner·mloc)·ldo + col).
+  void* scatter_out[8];
+  // COMM_GATHER (all-gather → GEMM): warp 3 of every CTA copies a slice of the peers' activation shards
+  // (gather_src[r]: [mloc, K] on rank r, peer-mapped) into the local A buffer gather_dst [tp·mloc, K] and bumps
+  // a per-row-block counter; the TMA producer only loads an A tile once its row block is complete.
+  const void* gather_src[8];
+  void* gather_dst;
+  const int* ready_flags;            // local flag array: ready_flags[r] >= ready_epoch ⇔ rank r's shard is final
+  unsigned int* gather_counters;     // [a_blocks], monotonically increasing
+  unsigned int gather_target;        // value counters reach when this call's copies of a row block are done
+  int ready_epoch, tp, rank, mloc, gather_parts;
 };
+
+enum { COMM_NONE = 0, COMM_GATHER = 1, COMM_SCATTER = 2 };
 
 __host__ __device__ constexpr int tmem_cols_for(int bn) {
   return 2 * bn <= 32 ? 32 : (2 * bn <= 64 ? 64 : (2 * bn <= 128 ? 128 : (2 * bn <= 256 ? 256 : 512)));
 }
 
-template <int BN, int EPI, bool SWAP, bool OUT_F32>
+template <int BN, int EPI, bool SWAP, bool OUT_F32, int COMM = COMM_NONE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const GemmParams p) {
@@ -89,7 +105,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int a_blk = t % p.a_blocks, b_blk = t / p.a_blocks;
+        const int b_blk = t / p.a_blocks;
+        int a_blk = t % p.a_blocks;
+        if constexpr (COMM == COMM_GATHER) {
+          // local rows first: remote row blocks arrive over NVLink while these tiles compute
+          a_blk = (a_blk + p.rank * (p.mloc / GEMM_BM)) % p.a_blocks;
+          unsigned spins = 0;
+          while ((int)(ld_acquire_gpu_u32(p.gather_counters + a_blk) - p.gather_target) < 0) {
+            if (++spins > (1u << 26)) { printf("jllama_b200: gather of row block %d never completed\n", a_blk); __trap(); }
+          }
+          asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores → TMA (async proxy) reads
+        }
         for (int kb = 0; kb < num_kb; ++kb) {
           tc::mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
@@ -123,12 +149,44 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         tc::mma_commit(tfull_bar(as));                      // accumulator complete → epilogue
       }
     }
+  } else if (warp == 3) {
+    if constexpr (COMM == COMM_GATHER) {
+      // ===================================================== all-gather: peers' shards → local A buffer
+      const int K16 = p.K / 8;                                   // 16-byte chunks per row
+      const int per_rb = GEMM_BM * K16;                          // chunks per 128-row block
+      const int per_part = (per_rb + p.gather_parts - 1) / p.gather_parts;
+      const int n_items = p.a_blocks * p.gather_parts;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int rb = item / p.gather_parts, part = item - rb * p.gather_parts;
+        const int src = (rb * GEMM_BM) / p.mloc;
+        if (lane == 0) wait_flag(p.ready_flags + src, p.ready_epoch, p.rank, src, 3);
+        __syncwarp();
+        const uint4* sp = reinterpret_cast<const uint4*>(p.gather_src[src]) + (size_t)(rb * GEMM_BM - src * p.mloc) * K16;
+        uint4* dp = reinterpret_cast<uint4*>(p.gather_dst) + (size_t)rb * per_rb;
+        const int lo = part * per_part, hi = min(lo + per_part, per_rb);
+        for (int i = lo + lane; i < hi; i += 32 * 8) {
+          uint4 v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (i + j * 32 < hi)
+              asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "l"(sp + i + j * 32) : "memory");
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (i + j * 32 < hi) dp[i + j * 32] = v[j];
+        }
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) atomicAdd(p.gather_counters + rb, 1u);
+      }
+    }
   } else if (warp >= 4) {
     // ===================================================== epilogue: TMEM → registers → global
     const int quarter = warp & 3;                           // TMEM lanes [32·quarter, 32·quarter+32)
     int it = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
-      const int a_blk = t % p.a_blocks, b_blk = t / p.a_blocks;
+      const int b_blk = t / p.a_blocks;
+      int a_blk = t % p.a_blocks;
+      if constexpr (COMM == COMM_GATHER) a_blk = (a_blk + p.rank * (p.mloc / GEMM_BM)) % p.a_blocks;
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
       tc::mbar_wait(tfull_bar(as), aphase);
       tc::fence_after_sync();
@@ -176,6 +234,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
               }
             } else {
               __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)ra * p.ldo + cb0;
+              if constexpr (COMM == COMM_SCATTER) {
+                const int owner = ra / p.mloc;
+                o = reinterpret_cast<__nv_bfloat16*>(p.scatter_out[owner]) +
+                    ((size_t)p.rank * p.mloc + (ra - owner * p.mloc)) * p.ldo + cb0;
+              }
               const bool full = cb0 + CH <= p.Rb;
               uint32_t w[CH / 2];
               if constexpr (EPI == EPI_RESIDUAL) {
@@ -243,12 +306,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     }
   }
 
+  if constexpr (COMM == COMM_SCATTER) __threadfence_system();     // partial tiles must be visible to their owners
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 2) tc::tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
-template <int BN, int EPI, bool SWAP, bool OUT_F32>
+template <int BN, int EPI, bool SWAP, bool OUT_F32, int COMM = COMM_NONE>
 static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int Ra, int Rb, int K, int num_sms,
                        cudaStream_t stream) {
   GemmParams p = p0;
@@ -268,7 +332,7 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
   p.a_blocks = (Ra + GEMM_BM - 1) / GEMM_BM;
   p.b_blocks = (Rb + BN - 1) / BN;
   const size_t smem = (size_t)stages * STAGE_BYTES + 8 * (2 * stages + 4) + 16 + 1024;
-  auto kern = gemm_kernel<BN, EPI, SWAP, OUT_F32>;
+  auto kern = gemm_kernel<BN, EPI, SWAP, OUT_F32, COMM>;
   JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = p.a_blocks * p.b_blocks;
   if (grid > num_sms) grid = num_sms;
@@ -320,4 +384,57 @@ extern "C" JL_API int jl_gemm(const void* x, const void* w, const void* residual
   if (mode == EPI_PLAIN) return dispatch_gemm<EPI_PLAIN, false>(x, w, p, M, N, K, num_sms, s);
   if (mode == EPI_RESIDUAL) return dispatch_gemm<EPI_RESIDUAL, false>(x, w, p, M, N, K, num_sms, s);
   return dispatch_gemm<EPI_SWIGLU, false>(x, w, p, M, N, K, num_sms, s);
+}
+
+
+// ------------------------------------------------------------------------------------ sequence-parallel prefill
+// all-gather → GEMM: y[M, N] = gather(peer shards)[M, K] · W[N, K]^T, M = tp·mloc.  The gather runs INSIDE the
+// GEMM kernel (warp 3 of every CTA pulls peers' rows over NVLink into `a_full` while tiles of the local rows
+// already compute).  `counters` ([M/128] u32) is zeroed on the stream before the launch.
+extern "C" JL_API int jl_ag_gemm(void* const* peer_shards, void* a_full, const void* w, void* out, int M, int N, int K,
+                                 int mode, int tp, int rank, const int* ready_flags, int ready_epoch, void* counters,
+                                 int num_sms, void* stream) {
+  JL_CHECK_ARG(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "jl_ag_gemm: bad tp/rank %d/%d", tp, rank);
+  JL_CHECK_ARG(M % (tp * GEMM_BM) == 0, "jl_ag_gemm: M=%d must be a multiple of tp*128", M);
+  JL_CHECK_ARG(M > 128 && K % 8 == 0 && N % 16 == 0, "jl_ag_gemm: needs M > 128, K %% 8 == 0, N %% 16 == 0");
+  JL_CHECK_ARG(mode == EPI_PLAIN || mode == EPI_SWIGLU, "jl_ag_gemm: mode must be plain or SwiGLU");
+  if (num_sms <= 0) num_sms = 148;
+  GemmParams p{};
+  p.out = out; p.K = K; p.ldo = mode == EPI_SWIGLU ? N / 2 : N;
+  p.Ra = M; p.Rb = N; p.hint_a = tc::EVICT_LAST; p.hint_b = tc::EVICT_NORMAL;
+  p.tp = tp; p.rank = rank; p.mloc = M / tp;
+  for (int i = 0; i < tp; ++i) p.gather_src[i] = peer_shards[i];
+  p.gather_dst = a_full; p.ready_flags = ready_flags; p.ready_epoch = ready_epoch;
+  p.gather_counters = (unsigned int*)counters;
+  const int a_blocks = M / GEMM_BM;
+  int parts = num_sms / a_blocks;
+  if (parts < 1) parts = 1;
+  p.gather_parts = parts; p.gather_target = (unsigned)parts;
+  auto s = (cudaStream_t)stream;
+  JL_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned int) * a_blocks, s));
+  if (mode == EPI_SWIGLU) {
+    if (N >= 256) return launch_gemm<256, EPI_SWIGLU, false, false, COMM_GATHER>(a_full, w, p, M, N, K, num_sms, s);
+    return launch_gemm<128, EPI_SWIGLU, false, false, COMM_GATHER>(a_full, w, p, M, N, K, num_sms, s);
+  }
+  if (N >= 256) return launch_gemm<256, EPI_PLAIN, false, false, COMM_GATHER>(a_full, w, p, M, N, K, num_sms, s);
+  return launch_gemm<128, EPI_PLAIN, false, false, COMM_GATHER>(a_full, w, p, M, N, K, num_sms, s);
+}
+
+// GEMM → reduce-scatter: this rank's partial x[M, K_local] · W[N, K_local]^T leaves the epilogue tile by tile
+// straight into the row owner's receive buffer peer_rs_buf[owner] ([tp][mloc][N] bf16 on that rank); the sum
+// over ranks, the residual add and the next RMSNorm happen in jl_rs_reduce on the owner.
+extern "C" JL_API int jl_gemm_rs(const void* x, const void* w, void* const* peer_rs_buf, int M, int N, int K, int tp,
+                                 int rank, int num_sms, void* stream) {
+  JL_CHECK_ARG(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "jl_gemm_rs: bad tp/rank %d/%d", tp, rank);
+  JL_CHECK_ARG(M % (tp * GEMM_BM) == 0, "jl_gemm_rs: M=%d must be a multiple of tp*128", M);
+  JL_CHECK_ARG(M > 128 && K % 8 == 0 && N % 32 == 0, "jl_gemm_rs: needs M > 128, K %% 8 == 0, N %% 32 == 0");
+  if (num_sms <= 0) num_sms = 148;
+  GemmParams p{};
+  p.out = nullptr; p.K = K; p.ldo = N;
+  p.Ra = M; p.Rb = N; p.hint_a = tc::EVICT_LAST; p.hint_b = tc::EVICT_NORMAL;
+  p.tp = tp; p.rank = rank; p.mloc = M / tp;
+  for (int i = 0; i < tp; ++i) p.scatter_out[i] = peer_rs_buf[i];
+  auto s = (cudaStream_t)stream;
+  if (N >= 256) return launch_gemm<256, EPI_PLAIN, false, false, COMM_SCATTER>(x, w, p, M, N, K, num_sms, s);
+  return launch_gemm<128, EPI_PLAIN, false, false, COMM_SCATTER>(x, w, p, M, N, K, num_sms, s);
 }

@@ -18,6 +18,7 @@ Model math: /root/reference/jax_llama/model.py:201-300 (attention), :337-340 (ML
 from __future__ import annotations
 
 import logging
+import os
 from dataclasses import dataclass, field
 from typing import Any, Dict, List, Optional, Tuple
 
@@ -277,6 +278,47 @@ class B200Engine:
             x = self._row_parallel(h, l.w2, x)
         return x
 
+    def _prefill_sp(self, input_ids: torch.Tensor, cache: DeviceKVCache, B: int, S: int) -> torch.Tensor:
+        """Megatron-style sequence-parallel prefill (a capability the reference does not have).
+
+        The residual stream lives sharded by token rows ([M/tp, H] per rank).  Column-parallel GEMMs
+        (wqkv, w1·w3) gather the normalised shards of all ranks inside the kernel; row-parallel GEMMs (wo, w2)
+        scatter their partial output tiles to the row owners from the epilogue; the owner sums, adds the
+        residual and normalises for the next GEMM (`SPState.rs_reduce`).  Returns this rank's vocabulary slice
+        of the last-position logits, [B, V/tp] fp32."""
+        c = self.config
+        eps = c.rms_norm_eps
+        nh, nkv, hd = self.nh, self.nkv, self.hd
+        M = B * S
+        sp = self.comm.sp_state(M, c.hidden_size, c.hidden_size)
+        mloc, r = sp.mloc, self.rank
+        start = cache.index
+        ids = input_ids.reshape(-1)
+        x = K.embed(ids[r * mloc:(r + 1) * mloc], self.embedding)                 # this rank's rows of the stream
+        sp.rs_reduce(x, self.layers[0].attn_norm, eps, n_src=0)                  # starts the chain: norm + publish
+        for i, l in enumerate(self.layers):
+            kc, vc = cache.k[i], cache.v[i]
+            qkv = sp.ag_gemm(l.wqkv, K.PLAIN)                                    # [M, (nh+2nkv)·hd] local heads, all tokens
+            q_rot = torch.empty((M, nh * hd), dtype=qkv.dtype, device=qkv.device)
+            K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
+                            pad_left=cache.pad_left, q_out=q_rot)
+            attn = self._prefill_attn(q_rot.view(B, S, nh, hd), kc, vc, start, S, cache).view(M, nh * hd)
+            sp.gemm_rs(attn, l.wo)
+            sp.rs_reduce(x, l.ffn_norm, eps, n_src=self.tp)
+            h = sp.ag_gemm(l.w13, K.SWIGLU)
+            sp.gemm_rs(h, l.w2)
+            nxt = self.layers[i + 1].attn_norm if i + 1 < len(self.layers) else self.final_norm
+            sp.rs_reduce(x, nxt, eps, n_src=self.tp)
+        # last position of every batch row, already final-normed, lives on the rank that owns that row
+        import torch.distributed as dist
+        last = torch.arange(B, device=self.device) * S + (S - 1)
+        mine = (last // mloc) == r
+        xl = torch.zeros((B, c.hidden_size), dtype=torch.bfloat16, device=self.device)
+        if bool(mine.any()):
+            xl[mine] = sp.read_rows(last[mine])
+        dist.all_reduce(xl, group=self.comm.group)                                # B rows: off the hot path
+        return K.linear(xl, self.lm_head, out_f32=True)
+
     def _row_parallel(self, a: torch.Tensor, w: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
         """x += a · wᵀ summed over tensor-parallel ranks (the reference's GSPMD all-reduce after wo / w2)."""
         if self.tp == 1:
@@ -317,6 +359,19 @@ class B200Engine:
         positions = None
         if position_ids is not None:
             positions = position_ids.to(torch.int32).reshape(-1).contiguous()
+        if (self.tp > 1 and S > 1 and last_only and with_head and positions is None and self.hd == 128
+                and (B * S) % (128 * self.tp) == 0 and not os.environ.get("JLLAMA_NO_SP")):
+            # sequence-parallel prefill: all-gather→GEMM and GEMM→reduce-scatter fused over NVLink peer memory
+            logits = self._prefill_sp(input_ids, cache, B, S)
+            cache.set_index(cache.index + S)
+            out = ModelOutput(past_key_values=None if own_cache else cache)
+            if gather_logits:
+                import torch.distributed as dist
+                parts = [torch.empty_like(logits) for _ in range(self.tp)]
+                dist.all_gather(parts, logits.contiguous(), group=self.comm.group)
+                logits = torch.cat(parts, dim=-1)
+            out.logits = logits.view(B, 1, -1)
+            return out
         if self.comm is not None:
             self.comm.begin_sequence()
         x = K.embed(input_ids.reshape(-1), self.embedding)

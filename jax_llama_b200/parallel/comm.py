@@ -16,7 +16,7 @@ from __future__ import annotations
 import ctypes as C
 import logging
 import os
-from typing import Dict, Optional, Tuple
+from typing import Any, Dict, Optional, Tuple
 
 import torch
 import torch.distributed as dist
@@ -39,6 +39,14 @@ _EXTRA_SIGNATURES = {
     "jl_allgather_small": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "jl_comm_bump": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "jl_memcpy_d2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "jl_ag_gemm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                             C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    "jl_gemm_rs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                             C.c_void_p]),
+    "jl_rs_reduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                               C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
+                               C.c_void_p]),
 }
 
 
@@ -189,8 +197,103 @@ class PeerComm:
         self.call_index += 1
         return out
 
+    # ------------------------------------------------------------------ sequence-parallel prefill
+    def symmetric_alloc(self, nbytes: int) -> Tuple[int, Any]:
+        """cudaMalloc + IPC exchange: (local pointer, ctypes table of every rank's pointer to its copy)."""
+        nbytes = (nbytes + 255) // 256 * 256
+        local, handle = self._alloc(nbytes)
+        if self.tp > 1:
+            gathered: list = [None] * self.tp
+            dist.all_gather_object(gathered, (self.rank, handle), group=self.group)
+        else:
+            gathered = [(self.rank, handle)]
+        ptrs = [0] * MAX_TP
+        for r, h in gathered:
+            ptrs[r] = local if r == self.rank else self._open(h)
+        self._symmetric = getattr(self, "_symmetric", []) + [local]
+        if self.tp > 1:
+            dist.barrier(group=self.group)
+        return local, (C.c_void_p * MAX_TP)(*ptrs)
+
+    def sp_state(self, M: int, H: int, kmax: int) -> "SPState":
+        key = (M, H, kmax)
+        states = self.__dict__.setdefault("_sp_states", {})
+        if key not in states:
+            states[key] = SPState(self, M, H, kmax)
+        return states[key]
+
     # ------------------------------------------------------------------ NCCL baseline (measured, not the product)
     def allreduce_nccl(self, t: torch.Tensor) -> torch.Tensor:
         if self.tp > 1:
             dist.all_reduce(t, group=self.group)
         return t
+
+
+class SPState:
+    """Buffers and epochs of the sequence-parallel prefill chain for one (tokens, hidden) shape.
+
+    rs_buf  [tp][mloc][H] bf16   receive buffer for the partial tiles peers scatter out of their GEMM epilogues
+    xn[2]   [mloc][H] bf16       this rank's normalised shard, read by peers' in-kernel all-gather (double-buffered)
+    a_full  [M][kmax] bf16       local destination of the gather
+    """
+
+    def __init__(self, comm: PeerComm, M: int, H: int, kmax: int):
+        tp = comm.tp
+        if M % (tp * 128):
+            raise ValueError(f"sequence-parallel prefill needs a token count that is a multiple of {tp * 128}, got {M}")
+        self.comm, self.M, self.H, self.mloc = comm, M, H, M // tp
+        dev = comm.device
+        self.rs_local, self.rs_ptrs = comm.symmetric_alloc(tp * self.mloc * H * 2)
+        xn0, self.xn_ptrs0 = comm.symmetric_alloc(self.mloc * H * 2)
+        xn1, self.xn_ptrs1 = comm.symmetric_alloc(self.mloc * H * 2)
+        self.xn_local = (xn0, xn1)
+        self.xn_ptrs = (self.xn_ptrs0, self.xn_ptrs1)
+        self.a_full = torch.empty((M, kmax), dtype=torch.bfloat16, device=dev)
+        self.counters = torch.zeros(M // 128, dtype=torch.int32, device=dev)
+        self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.gemm_off = comm.flag_block(("sp_gemm",), MAX_TP)
+        self.ready_off = comm.flag_block(("sp_ready",), MAX_TP)
+        self.parity = 0
+        # epochs persist across forwards (flags are never reset)
+        comm.__dict__.setdefault("_sp_epochs", {"gemm": 0, "ready": 0})
+        self.ep = comm._sp_epochs
+
+    def rs_reduce(self, x_shard: torch.Tensor, norm_w: torch.Tensor, eps: float, n_src: int) -> None:
+        """x_shard += Σ partials (n_src = tp) or nothing (n_src = 0); RMSNorm → next parity's shard; publish."""
+        cm = self.comm
+        self.parity ^= 1
+        self.ep["ready"] += 1
+        if n_src:
+            self.ep["gemm"] += 1
+        _lib.check(_L().jl_rs_reduce(x_shard.data_ptr(), self.rs_local, norm_w.data_ptr(), self.xn_local[self.parity],
+                                     self.mloc, self.H, n_src, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off, self.ready_off,
+                                     self.ep["gemm"], self.ep["ready"], self.ticket.data_ptr(), float(eps), K._stream()),
+                   "jl_rs_reduce")
+
+    def ag_gemm(self, w: torch.Tensor, mode: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """y = all_gather(normalised shards) · wᵀ; the gather happens inside the GEMM kernel."""
+        cm = self.comm
+        n, k = w.shape
+        odim = n // 2 if mode == K.SWIGLU else n
+        if out is None:
+            out = torch.empty((self.M, odim), dtype=torch.bfloat16, device=cm.device)
+        a_full = self.a_full if k == self.a_full.shape[1] else self.a_full.view(-1)[:self.M * k].view(self.M, k)
+        flags_local = cm._own_flags + 4 * self.ready_off
+        _lib.check(_L().jl_ag_gemm(self.xn_ptrs[self.parity], a_full.data_ptr(), w.data_ptr(), out.data_ptr(), self.M, n,
+                                   k, mode, cm.tp, cm.rank, flags_local, self.ep["ready"], self.counters.data_ptr(),
+                                   K.num_sms(cm.device), K._stream()), "jl_ag_gemm")
+        return out
+
+    def gemm_rs(self, a: torch.Tensor, w: torch.Tensor) -> None:
+        """Partial a · wᵀ scattered tile by tile into the row owners' receive buffers."""
+        cm = self.comm
+        n, k = w.shape
+        _lib.check(_L().jl_gemm_rs(a.data_ptr(), w.data_ptr(), self.rs_ptrs, self.M, n, k, cm.tp, cm.rank,
+                                   K.num_sms(cm.device), K._stream()), "jl_gemm_rs")
+
+    def read_rows(self, rows: torch.Tensor) -> torch.Tensor:
+        """Rows (global token indices owned by this rank) of the current normalised shard as a torch tensor."""
+        out = torch.empty((self.mloc, self.H), dtype=torch.bfloat16, device=self.comm.device)
+        _lib.check(_L().jl_memcpy_d2d(out.data_ptr(), self.xn_local[self.parity], out.numel() * 2, K._stream()),
+                   "jl_memcpy_d2d")
+        return out[rows - self.comm.rank * self.mloc]

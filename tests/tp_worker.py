@@ -86,6 +86,20 @@ def main():
     ga = [torch.empty_like(a) for _ in range(world)]
     dist.all_gather(ga, a)
     assert all(torch.equal(ga[0], t) for t in ga)
+    # ---- 3. sequence-parallel prefill (all-gather→GEMM, GEMM→reduce-scatter fused over peer memory)
+    S = 64 * world if world > 2 else 128
+    ids_sp = torch.randint(3, cfg.vocab_size, (2, S), generator=torch.Generator().manual_seed(9))
+    assert (2 * S) % (128 * world) == 0
+    want_sp = ref.forward(full32, cfg, ids_sp).logits[:, -1]
+    for _ in range(2):                                  # twice: epochs, parities and counters must re-arm
+        cache = eng.new_cache(2, S + 8)
+        got_sp = eng.forward(ids_sp.to(dev), cache=cache, last_only=True).logits[:, 0]
+        assert got_sp.shape == want_sp.shape and rel(got_sp, want_sp) < 3e-2, rel(got_sp, want_sp)
+    os.environ["JLLAMA_NO_SP"] = "1"                    # same prefill through the NCCL-all-reduce path
+    cache2 = eng.new_cache(2, S + 8)
+    got_nccl = eng.forward(ids_sp.to(dev), cache=cache2, last_only=True).logits[:, 0]
+    del os.environ["JLLAMA_NO_SP"]
+    assert rel(got_sp, got_nccl) < 3e-2 and rel(cache.k, cache2.k) < 2e-2
     dist.barrier()
     if rank == 0:
         print(f"TP_WORKER_OK world={world}")
