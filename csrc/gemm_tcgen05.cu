@@ -59,7 +59,7 @@ __host__ __device__ constexpr int tmem_cols_for(int bn) {
 template <int BN, int EPI, bool SWAP, bool OUT_F32, int COMM = COMM_NONE>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-            const GemmParams p) {
+            const __grid_constant__ CUtensorMap tmap_a_local, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2;
   constexpr uint32_t B_BYTES = BN * GEMM_BK * 2;
@@ -107,12 +107,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         const int b_blk = t / p.a_blocks;
         int a_blk = t % p.a_blocks;
+        bool a_is_local = false;
         if constexpr (COMM == COMM_GATHER) {
           // local rows first: remote row blocks arrive over NVLink while these tiles compute
           a_blk = (a_blk + p.rank * (p.mloc / GEMM_BM)) % p.a_blocks;
-          unsigned spins = 0;
-          while ((int)(ld_acquire_gpu_u32(p.gather_counters + a_blk) - p.gather_target) < 0) {
-            if (++spins > (1u << 26)) { printf("jllama_b200: gather of row block %d never completed\n", a_blk); __trap(); }
+          a_is_local = (a_blk * GEMM_BM) / p.mloc == p.rank;
+          if (a_is_local) {
+            // this rank's own rows are read in place from its shard (no copy); it must be final
+            wait_flag(p.ready_flags + p.rank, p.ready_epoch, p.rank, p.rank, 5);
+          } else {
+            unsigned spins = 0;
+            while ((int)(ld_acquire_gpu_u32(p.gather_counters + a_blk) - p.gather_target) < 0) {
+              if (++spins > (1u << 26)) { printf("jllama_b200: gather of row block %d never completed\n", a_blk); __trap(); }
+            }
           }
           asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores → TMA (async proxy) reads
         }
@@ -120,7 +127,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           tc::mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
           tc::mbar_expect_tx(full_bar(stage), A_BYTES + B_BYTES);
-          tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM, p.hint_a);
+          if (a_is_local) tc::tma_load_2d(sa, &tmap_a_local, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM - p.rank * p.mloc, p.hint_a);
+          else tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM, p.hint_a);
           tc::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * GEMM_BK, b_blk * BN, p.hint_b);
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
@@ -155,23 +163,26 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const int K16 = p.K / 8;                                   // 16-byte chunks per row
       const int per_rb = GEMM_BM * K16;                          // chunks per 128-row block
       const int per_part = (per_rb + p.gather_parts - 1) / p.gather_parts;
-      const int n_items = p.a_blocks * p.gather_parts;
+      const int local_blocks = p.mloc / GEMM_BM;
+      const int n_items = (p.a_blocks - local_blocks) * p.gather_parts;          // remote row blocks only
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int rb = item / p.gather_parts, part = item - rb * p.gather_parts;
+        const int part = item % p.gather_parts;
+        // k-th remote row block in the order the tiles will want them (the blocks after this rank's own)
+        const int rb = (p.rank * local_blocks + local_blocks + item / p.gather_parts) % p.a_blocks;
         const int src = (rb * GEMM_BM) / p.mloc;
         if (lane == 0) wait_flag(p.ready_flags + src, p.ready_epoch, p.rank, src, 3);
         __syncwarp();
         const uint4* sp = reinterpret_cast<const uint4*>(p.gather_src[src]) + (size_t)(rb * GEMM_BM - src * p.mloc) * K16;
         uint4* dp = reinterpret_cast<uint4*>(p.gather_dst) + (size_t)rb * per_rb;
         const int lo = part * per_part, hi = min(lo + per_part, per_rb);
-        for (int i = lo + lane; i < hi; i += 32 * 8) {
-          uint4 v[8];
+        for (int i = lo + lane; i < hi; i += 32 * 16) {
+          uint4 v[16];
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
+          for (int j = 0; j < 16; ++j)
             if (i + j * 32 < hi)
               asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "l"(sp + i + j * 32) : "memory");
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
+          for (int j = 0; j < 16; ++j)
             if (i + j * 32 < hi) dp[i + j * 32] = v[j];
         }
         __threadfence();
@@ -336,7 +347,12 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
   JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = p.a_blocks * p.b_blocks;
   if (grid > num_sms) grid = num_sms;
-  JL_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), smem, stream, ta, tb, p));
+  CUtensorMap tl = ta;                          // local-shard map (COMM_GATHER only; otherwise a copy of A's)
+  if constexpr (COMM == COMM_GATHER) {
+    rc = make_tmap_2d_bf16(&tl, p.gather_src[p.rank], p.mloc, K, K, GEMM_BM);
+    if (rc) return rc;
+  }
+  JL_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), smem, stream, ta, tb, tl, p));
   return JL_OK;
 }
 
@@ -407,7 +423,8 @@ extern "C" JL_API int jl_ag_gemm(void* const* peer_shards, void* a_full, const v
   p.gather_dst = a_full; p.ready_flags = ready_flags; p.ready_epoch = ready_epoch;
   p.gather_counters = (unsigned int*)counters;
   const int a_blocks = M / GEMM_BM;
-  int parts = num_sms / a_blocks;
+  const int remote_blocks = a_blocks - a_blocks / tp;
+  int parts = remote_blocks > 0 ? num_sms / remote_blocks : 1;
   if (parts < 1) parts = 1;
   p.gather_parts = parts; p.gather_target = (unsigned)parts;
   auto s = (cudaStream_t)stream;
