@@ -118,6 +118,73 @@ int jl_decode_advance(const int* tok, int* next_ids, int* finished, int* sequenc
                       int eos, int pad, int* cur_len, int* cache_len, int* step, int* n_unfinished,
                       void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Whole-model decode step (model.py:743-790 at S=1, i.e. everything FlaxLLaMAForCausalLMModule.__call__ does
+ * for one new token) in ONE persistent cooperative kernel for M <= 4 rows: embedding, L x (RMSNorm+wqkv, RoPE,
+ * cache append, GQA attention, wo+residual, RMSNorm+w13+SwiGLU, w2+residual), final norm and LM head.
+ * Weights are the per-op stacks [L*N, K]; x/qkv/attn/hmlp are bf16 activations the kernel uses between
+ * phases; logits fp32 [M, V] (V = this rank's vocab shard, vocab_full the whole vocabulary); scratch must hold
+ * jl_decode_mega_scratch_bytes() bytes and be ZERO when first used.  Needs a cooperative launch of one CTA
+ * per SM (num_sms CTAs must be co-resident).  With tp > 1 the wo / w2 outputs are all-reduced inside the kernel
+ * over the peer inboxes (tagged 8-byte packets; partition.py:67,70 is what GSPMD all-reduced there) and the
+ * caller advances the epoch counter behind seq_ptr by 2*L per step (jl_comm_bump; see parallel/comm.py). */
+int jl_decode_mega_barriers(int L);
+size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, int num_sms);
+void jl_decode_mega_set_trace(void* buf /* device u64 [2][L][16] %globaltimer stamps, NULL = off */);
+int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
+                   const void* lm_head, const void* attn_norm, const void* ffn_norm, const void* final_norm,
+                   const void* embedding, const int* ids, void* x, void* qkv, void* attn, void* hmlp,
+                   float* logits, void* k_cache, void* v_cache, const float* cos_t, const float* sin_t,
+                   const int* cache_len, const int* pad_left, void* scratch, int M, int L, int H, int F, int V,
+                   int vocab_full, int nh, int nkv, int hd, int T, int max_pos, float eps, float scale,
+                   int num_sms, int tp, int rank, void* const* peer_inbox, void* const* peer_flags,
+                   size_t inbox_parity_stride_floats, int flag_offset, const int* seq_ptr, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Tensor parallelism over NVLink peer memory (partition.py:62-78 names the sharding; XLA/GSPMD inserted NCCL
+ * collectives, here they run inside the compute kernels).  Peer buffers are cudaMalloc'd + exported with
+ * CUDA IPC; `peer_*` arguments are host arrays of tp device pointers (index = rank, own entry local). */
+int jl_ipc_alloc(size_t bytes, void** ptr, void* handle64 /* out: 64-byte IPC handle */);
+int jl_ipc_open(const void* handle64, void** ptr);
+int jl_ipc_close(void* ptr);
+int jl_ipc_free(void* ptr);
+
+/* Row-parallel linear at decode (wo, w2; M <= 8): local GEMV over this rank's K shard, partial sums pushed to
+ * every peer's inbox, one-shot all-reduce in rank order (bitwise identical on all ranks) + residual, in one
+ * launch.  The epoch that tags the flags is *seq_ptr + call_index (device counter advanced with jl_comm_bump,
+ * so the same CUDA graph replays with fresh epochs).  peer_flags must hold jl_gemv_allreduce_flags(N) ints at
+ * flag_offset. */
+int jl_gemv_allreduce_flags(int N);
+int jl_gemv_allreduce(const void* x, const void* w, const void* residual, void* out, int M, int N, int K, int tp,
+                      int rank, void* const* peer_inbox, void* const* peer_flags,
+                      size_t inbox_parity_stride_floats, int flag_offset, const int* seq_ptr, int call_index,
+                      int num_sms, void* stream);
+/* All-gather of a small record (<= slot_bytes, multiples of 16) from every rank: push to every inbox + flag.
+ * Used for the cross-rank sampler (per-rank top-k candidates of the vocab-sharded logits). */
+int jl_allgather_small(const void* src, void* out, int n_bytes, int slot_bytes, int tp, int rank,
+                       void* const* peer_inbox, void* const* peer_flags, size_t parity_stride_bytes,
+                       int flag_offset, const int* seq_ptr, int call_index, void* stream);
+int jl_comm_bump(int* seq_ptr, int n, void* stream);
+int jl_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream);
+
+/* Sequence-parallel prefill (M % (128*tp) == 0).  The residual stream is sharded by rows; per layer:
+ *   jl_ag_gemm  — column-parallel GEMM (wqkv, w13) whose A operand is the all-gather of every rank's
+ *                 normalised row shard: remote row blocks are copied over NVLink by a gather warp inside the
+ *                 kernel while the MMA warps work on blocks that already arrived; local rows are read in place.
+ *   jl_gemm_rs  — row-parallel GEMM (wo, w2) whose epilogue writes each bf16 output tile straight into the
+ *                 row owner's receive buffer (reduce-scatter by remote stores).
+ *   jl_rs_reduce— owner side: wait for all partial tiles, fp32 sum in rank order + residual, RMSNorm for the
+ *                 next jl_ag_gemm, publish "shard ready".
+ * Replaces the whole-activation all-reduce GSPMD placed after wo / w2 (partition.py:67,70). */
+int jl_ag_gemm(void* const* peer_shards, void* a_full, const void* w, void* out, int M, int N, int K, int mode,
+               int tp, int rank, const int* ready_flags, int ready_epoch, void* counters, int num_sms,
+               void* stream);
+int jl_gemm_rs(const void* x, const void* w, void* const* peer_rs_buf, int M, int N, int K, int tp, int rank,
+               int num_sms, void* stream);
+int jl_rs_reduce(void* x, const void* partials, const void* norm_w, void* xn, int mloc, int H, int n_src, int tp,
+                 int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off, int gemm_epoch,
+                 int ready_epoch, int* ticket, float eps, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
