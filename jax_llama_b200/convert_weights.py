@@ -238,3 +238,37 @@ def write_meta_checkpoint(tree: Tree, config: LLaMAConfig, out_dir: str, mp: int
         params["ffn_dim_multiplier"] = ffn_dim_multiplier
     with open(out / "params.json", "w") as f:
         json.dump(params, f)
+
+
+def main(argv: Optional[Sequence[str]] = None) -> int:
+    """``python -m jax_llama_b200.convert_weights --ckpt_dir D --out_dir O [--tp N]`` — the command the
+    reference's convert.sh calls but never shipped (/root/reference/convert.sh:10): Meta shards → the sharded
+    safetensors cache of `checkpoint.py`, one rank slice at a time."""
+    import argparse
+
+    from .checkpoint import save_sharded_from_meta
+
+    ap = argparse.ArgumentParser(description=main.__doc__)
+    ap.add_argument("--ckpt_dir", required=True)
+    ap.add_argument("--out_dir", required=True)
+    ap.add_argument("--tokenizer_path", default=None, help="sets vocab_size / bos / eos ids in config.json")
+    ap.add_argument("--is_llama3", type=lambda s: str(s).lower() in ("1", "true", "yes"), default=False)
+    ap.add_argument("--tp", type=int, default=1, help="number of tensor-parallel rank files to write")
+    ap.add_argument("--max_seq_len", type=int, default=2048)
+    ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float16", "float32"])
+    ap.add_argument("--verbose", action="store_true")
+    a = ap.parse_args(argv)
+    logging.basicConfig(level=logging.INFO if a.verbose else logging.WARNING)
+    tok = None
+    if a.tokenizer_path:
+        from .tokenizers import LLaMA2Tokenizer, LLaMA3Tokenizer
+        tok = (LLaMA3Tokenizer if a.is_llama3 else LLaMA2Tokenizer)(a.tokenizer_path)
+    cfg = save_sharded_from_meta(a.out_dir, a.ckpt_dir, tok, a.tp, max_seq_len=a.max_seq_len,
+                                 dtype=getattr(torch, a.dtype))
+    logger.info("wrote %d rank file(s) to %s (%d layers, hidden %d)", a.tp, a.out_dir, cfg.num_hidden_layers,
+                cfg.hidden_size)
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

@@ -1,0 +1,46 @@
+"""The command-line entry points a reference user would reach for: parity harness (jax_test.py counterpart),
+converter CLI (what convert.sh calls), packaging."""
+import os
+import subprocess
+import sys
+
+import torch
+
+from jax_llama_b200 import LLaMAConfig
+from jax_llama_b200.checkpoint import load_rank, read_layout
+from jax_llama_b200.convert_weights import main as convert_main
+from jax_llama_b200.convert_weights import write_meta_checkpoint
+from jax_llama_b200.models import reference as ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_parity_harness_runs_on_cpu():
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "parity_test.py"), "--trials", "3"], env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "ALL PASSED" in r.stdout
+    for name in ("RMSNorm", "precompute_freqs_cis", "apply_rotary_emb", "Attention", "FeedForward",
+                 "TransformerBlock", "Transformer", "ModelLogits", "ModelGenerations"):
+        assert f"PASS {name}" in r.stdout, name
+
+
+def test_convert_cli_writes_rank_files(tmp_path):
+    cfg = LLaMAConfig(vocab_size=64, hidden_size=64, intermediate_size=256, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2, max_sequence_length=64)
+    tree = ref.init_params(cfg, seed=0)
+    src, dst = tmp_path / "meta", tmp_path / "cache"
+    write_meta_checkpoint(tree, cfg, str(src), mp=2, dtype=torch.float32, multiple_of=256)
+    assert convert_main(["--ckpt_dir", str(src), "--out_dir", str(dst), "--tp", "2", "--dtype", "float32"]) == 0
+    assert read_layout(str(dst))["tp"] == 2
+    for r in range(2):
+        shard, c = load_rank(str(dst), r)
+        assert c.hidden_size == 64
+        wq = tree["transformer"]["h"]["0"]["attention"]["wq"]["kernel"]
+        assert torch.equal(shard["transformer"]["h"]["0"]["attention"]["wq"]["kernel"], wq[:, r * 32:(r + 1) * 32])
+
+
+def test_setup_py_lists_the_package():
+    r = subprocess.run([sys.executable, "setup.py", "--name", "--version"], cwd=ROOT, capture_output=True, text=True)
+    assert r.returncode == 0 and "jax_llama_b200" in r.stdout

@@ -100,6 +100,34 @@ def main():
     got_nccl = eng.forward(ids_sp.to(dev), cache=cache2, last_only=True).logits[:, 0]
     del os.environ["JLLAMA_NO_SP"]
     assert rel(got_sp, got_nccl) < 3e-2 and rel(cache.k, cache2.k) < 2e-2
+    # ---- 4. flag / epoch protocol stress: ranks enter every collective at random, different times
+    # (a device-side sleep of up to ~200 us per rank per call) for many back-to-back calls; payloads change
+    # every iteration so that a stale inbox slot, a reused flag or a parity mix-up shows up as a wrong sum.
+    import random
+    rnd = random.Random(1234 + rank)
+    iters = int(os.environ.get("TP_STRESS_ITERS", "150"))
+    K_, N = 256 * world, 512
+    w_full = (torch.randn(N, K_, generator=torch.Generator().manual_seed(77)) * 0.05).to(torch.bfloat16)
+    w_loc = w_full[:, rank * 256:(rank + 1) * 256].contiguous().to(dev)
+    zero = torch.zeros(1, N, dtype=torch.bfloat16, device=dev)
+    outs, gath = [], []
+    for it in range(iters):
+        x_full = torch.full((1, K_), 1.0 + (it % 7), dtype=torch.bfloat16)
+        x_loc = x_full[:, rank * 256:(rank + 1) * 256].contiguous().to(dev)
+        src = torch.full((8,), float(rank * 1000 + it), dtype=torch.float32, device=dev)
+        comm.begin_sequence()
+        torch.cuda._sleep(rnd.randrange(0, 400_000))
+        outs.append(comm.gemv_allreduce(x_loc, w_loc, zero))
+        torch.cuda._sleep(rnd.randrange(0, 400_000))
+        gath.append(comm.allgather_small(src, torch.empty(world, 8, dtype=torch.float32, device=dev)))
+        comm.end_sequence()
+    torch.cuda.synchronize()
+    base = w_full.float().sum(1)
+    for it in range(iters):
+        want_it = (base * (1.0 + (it % 7))).to(torch.bfloat16).float()
+        assert rel(outs[it][0], want_it) < 2e-2, ("stress all-reduce", it, rel(outs[it][0], want_it))
+        exp = torch.tensor([[r * 1000.0 + it] * 8 for r in range(world)], device=dev)
+        assert torch.equal(gath[it], exp), ("stress all-gather", it)
     dist.barrier()
     if rank == 0:
         print(f"TP_WORKER_OK world={world}")
