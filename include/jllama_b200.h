@@ -100,6 +100,7 @@ int jl_decode_attn_noalloc(const void* q, const void* k_cache, const void* v_cac
 /* model.py:236-288 at S>1 — causal flash attention of S new tokens per row (cache slots start..start+S,
  * already appended) on tcgen05: q [B*S, nh*hd] rotated, caches [B][nkv][T][hd], out [B*S, nh*hd].
  * Keys [pad_left[b], slot of the query] are visible.  head_dim 128 only.  cache_len_ptr is reserved. */
+int jl_flash_prefill_occupancy(int smem_override /* -1 */); /* resident CTAs per SM (diagnostic; 2 expected) */
 int jl_flash_prefill(const void* q, const void* k_cache, const void* v_cache, const int* cache_len_ptr,
                      const int* pad_left, void* out, int B, int S, int nh, int nkv, int hd, int T, int start,
                      float scale, void* stream);

@@ -197,6 +197,26 @@ def test_flash_prefill(B, S, start, nh, nkv, pads):
     assert ((g - w).abs().max() / (w.abs().max() + 1e-6)).item() < 2e-2
 
 
+@pytest.mark.parametrize("ramp", [0.02, -0.02])
+def test_flash_prefill_growing_and_shrinking_scores(ramp):
+    """Scores whose row maximum keeps rising along the keys (ramp > 0) force the in-TMEM rescale of O over
+    and over; falling scores (ramp < 0) exercise the 'reference maximum stays put' path with tiny tails."""
+    B, S, nh, nkv, hd = 1, 640, 2, 1, 128
+    q = rnd(B, S, nh, hd, seed=40)
+    base = rnd(B, nkv, S, hd, seed=41).float()
+    # key t gets a component along a fixed direction that grows with t; queries all have +3 along it
+    direction = torch.zeros(hd)
+    direction[:8] = 1.0
+    kc = (base * 0.3 + direction * (ramp * torch.arange(S).float())[None, None, :, None] * 6).to(torch.bfloat16)
+    q = (q.float() * 0.3 + 3.0 * direction).to(torch.bfloat16)
+    vc = rnd(B, nkv, S, hd, seed=42)
+    pad = torch.tensor([0], dtype=torch.int32)
+    want = K.prefill_attn_ref(q.float(), kc.float(), vc.float(), 0, S, pad)
+    got = K.prefill_attn(q.to(DEV), kc.to(DEV), vc.to(DEV), 0, S, pad.to(DEV))
+    assert torch.isfinite(got.float()).all()
+    assert ((got.float().cpu() - want).abs().max() / (want.abs().max() + 1e-6)).item() < 2e-2
+
+
 @pytest.mark.parametrize("nh,nkv,hd", [(8, 2, 128), (8, 8, 128), (8, 1, 128), (4, 2, 64)])
 @pytest.mark.parametrize("B,filled,max_len", [(1, 0, 64), (2, 77, 256), (1, 2048, 2304), (3, 700, 4096)])
 def test_decode_attention_fused(nh, nkv, hd, B, filled, max_len):
