@@ -86,10 +86,15 @@ __device__ __forceinline__ void mg_consumer_bar() { asm volatile("bar.sync 1, %0
 __device__ __forceinline__ uint4 ldcg16(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
 
 __device__ __forceinline__ void mg_stamp(const MegaParams& p, int layer, int ev) {
-  if (p.trace != nullptr && threadIdx.x == 32 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1)) {
+  if (p.trace != nullptr && threadIdx.x == 32) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    p.trace[((blockIdx.x == 0 ? 0 : 1) * p.L + layer) * 32 + ev] = t;
+    p.trace[((size_t)blockIdx.x * p.L + layer) * 32 + ev] = t;
+    if (ev == 0) {
+      unsigned int smid;
+      asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+      p.trace[((size_t)blockIdx.x * p.L + layer) * 32 + 31] = smid;
+    }
   }
 }
 
@@ -317,6 +322,7 @@ __device__ __forceinline__ void mg_gemv(MegaCtx& c, int N, int K, void* out, con
 
 }  // namespace jl
 #include "decode_mega_gemv.cuh"
+#include "decode_mega_mma.cuh"
 namespace jl {
 
 // grid-wide barrier among the consumer warps of all CTAs
@@ -646,6 +652,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   __shared__ float red[M][MG_CONSUMERS];
   __shared__ float s_part[2][MG_CONSUMERS][M][4];
   __shared__ float s_res[2][M][MG_CONSUMERS];
+  __shared__ __align__(16) float s_acc[2][MG_CONSUMERS][MG_MMA_MAX_M][8];
   __shared__ int s_last;
   constexpr int NG = MG_CONSUMERS * (32 / (MG_HD / 8));
 
@@ -692,8 +699,12 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
         if (tc::mbar_try_wait(c.bars + 8u * (c.stages + c.stage), c.phase ^ 1)) {
           const uint32_t full = c.bars + 8u * c.stage;
           tc::mbar_expect_tx(full, ld.bytes());
-          tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.ks * (MG_KS / 256), ld.row(),
-                          tc::EVICT_FIRST);
+          if (p.gemv_mode == 2)       // swizzled [k-block][row][128 B] stage for the tensor-core GEMV
+            tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.row(), ld.ks * (MG_KS / 64),
+                            tc::EVICT_FIRST);
+          else
+            tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.ks * (MG_KS / 256), ld.row(),
+                            tc::EVICT_FIRST);
           if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
           ld.next(p, qdim);
           if (ahead > 0) --ahead; else pf = ld;
@@ -710,9 +721,15 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
 
   // ===================================================== consumers
   // K == 4096 (and M <= 2): activations stay in registers for the whole op (see mg_gemv)
+#define MG_STAGE(SRC_, K_, NORM_)                                                                            \
+  do {                                                                                                       \
+    if (p.gemv_mode == 2) mg_stage_input_mma<M>(c, SRC_, K_, NORM_, p.eps, red);                             \
+    else mg_stage_input<M>(c, SRC_, K_, NORM_, p.eps, red);                                                  \
+  } while (0)
 #define MG_GEMV(MODE_, N_, K_, OUT_, RES_, ROWS_)                                                            \
   do {                                                                                                       \
-    if ((K_) == 4 * MG_KS && M == 1 && ROWS_ == 8 && p.gemv_mode == 0)                                       \
+    if (p.gemv_mode == 2) mg_gemv_mma<M, MODE_>(c, N_, K_, OUT_, RES_, s_acc);                               \
+    else if ((K_) == 4 * MG_KS && M == 1 && ROWS_ == 8 && p.gemv_mode == 0)                                  \
       mg_gemv<M, MODE_, (M == 1 ? 4 : 0)>(c, N_, K_, OUT_, RES_, s_res);                                     \
     else if ((K_) <= 4 * MG_KS) mg_gemv2<M, MODE_, 4, true, ROWS_>(c, N_, K_, OUT_, RES_, s_part);            \
     else if ((K_) <= 16 * MG_KS && M == 1)                                                                   \
@@ -740,7 +757,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   for (int l = 0; l < p.L; ++l) {
     // ---- fused qkv projection (RMSNorm in the prologue)
     mg_stamp(p, l, 0);
-    mg_stage_input<M>(c, p.x, p.H, p.attn_norm + (size_t)l * p.H, p.eps, red);
+    MG_STAGE(p.x, p.H, p.attn_norm + (size_t)l * p.H);
     mg_stamp(p, l, 1);
     MG_GEMV(MG_PLAIN, p.NQKV, p.H, p.qkv, nullptr, 8);
     mg_stamp(p, l, 2);
@@ -763,7 +780,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     }
     mg_stamp(p, l, 5);
     // ---- wo + residual
-    mg_stage_input<M>(c, p.attn, qdim, nullptr, 0.f, red);
+    MG_STAGE(p.attn, qdim, nullptr);
     mg_stamp(p, l, 6);
     c.ar_epoch = ar_base + 2 * l + 1;
     MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x, 8);
@@ -772,14 +789,14 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 8);
     // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
-    mg_stage_input<M>(c, p.x, p.H, p.ffn_norm + (size_t)l * p.H, p.eps, red);
+    MG_STAGE(p.x, p.H, p.ffn_norm + (size_t)l * p.H);
     mg_stamp(p, l, 9);
     MG_GEMV(MG_SWIGLU, 2 * p.F, p.H, p.hmlp, nullptr, 8);
     mg_stamp(p, l, 10);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 11);
     // ---- w2 + residual
-    mg_stage_input<M>(c, p.hmlp, p.F, nullptr, 0.f, red);
+    MG_STAGE(p.hmlp, p.F, nullptr);
     mg_stamp(p, l, 12);
     c.ar_epoch = ar_base + 2 * l + 2;
     MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x, 8);
@@ -789,7 +806,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     mg_stamp(p, l, 14);
   }
   // ---- final norm + LM head
-  mg_stage_input<M>(c, p.x, p.H, p.final_norm, p.eps, red);
+  MG_STAGE(p.x, p.H, p.final_norm);
   MG_GEMV(MG_LOGITS, p.V, p.H, p.logits, nullptr, 8);
   mg_grid_barrier(p, gen_base, bar_idx);
   if (blockIdx.x == 0 && threadIdx.x == 32) *p.bar_gen = gen_base + (unsigned)bar_idx;
@@ -801,7 +818,7 @@ using namespace jl;
 
 extern "C" JL_API int jl_decode_mega_barriers(int L) { return 2 + 5 * L; }
 
-// optional per-op timestamp buffer ([2][L][16] u64, device memory); NULL disables tracing
+// optional per-op timestamp buffer ([grid][L][32] u64, device memory; slot 31 = %smid); NULL disables tracing
 static unsigned long long* g_mega_trace = nullptr;
 extern "C" JL_API void jl_decode_mega_set_trace(void* buf) { g_mega_trace = (unsigned long long*)buf; }
 
@@ -841,14 +858,25 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
       configured = true;
     }
   }
+  // GEMV flavour: 2 = tensor-core (mma.sync) consumers on swizzled stages (default), 0 / 1 = the SIMT paths
+  static const int gemv_mode = [] { const char* e = getenv("JLLAMA_MEGA_GEMV"); return e ? atoi(e) : 2; }();
   MegaTmaps tm;
   int rc;
+  if (gemv_mode == 2) {
+    if ((rc = make_tmap_kblock_bf16(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, MG_KS / 64, MG_GROUP))) return rc;
+    if ((rc = make_tmap_kblock_bf16(&tm.m[1], wo_all, (uint64_t)L * H, nh * hd, nh * hd, MG_KS / 64, MG_GROUP))) return rc;
+    if ((rc = make_tmap_kblock_bf16(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, MG_KS / 64, MG_GROUP))) return rc;
+    if ((rc = make_tmap_kblock_bf16(&tm.m[3], w2_all, (uint64_t)L * H, F, F, MG_KS / 64, MG_GROUP))) return rc;
+    if ((rc = make_tmap_kblock_bf16(&tm.m[4], lm_head, (uint64_t)V, H, H, MG_KS / 64, MG_GROUP))) return rc;
+    tm.m[5] = tm.m[3];
+  } else {
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, MG_KS / 256, MG_GROUP))) return rc;
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[1], wo_all, (uint64_t)L * H, nh * hd, nh * hd, MG_KS / 256, MG_GROUP))) return rc;
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, MG_KS / 256, MG_GROUP))) return rc;
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[3], w2_all, (uint64_t)L * H, F, F, MG_KS / 256, MG_GROUP))) return rc;
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[4], lm_head, (uint64_t)V, H, H, MG_KS / 256, MG_GROUP))) return rc;
   if ((rc = make_tmap_slab_bf16_plain(&tm.m[5], w2_all, (uint64_t)L * H, F, F, MG_KS / 256, 4))) return rc;
+  }
 
   MegaParams p{};
   p.L = L; p.H = H; p.F = F; p.V = V; p.nh = nh; p.nkv = nkv; p.NQKV = NQKV; p.vocab_full = vocab_full;
@@ -878,19 +906,20 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
     for (int i = 0; i < p.ar.tp; ++i) { p.ar.inbox[i] = (float*)peer_inbox[i]; p.ar.flags[i] = (int*)peer_flags[i]; }
   }
   p.trace = g_mega_trace;
-  {
-    static const int mode = [] { const char* e = getenv("JLLAMA_MEGA_GEMV"); return e ? atoi(e) : 0; }();
-    p.gemv_mode = mode;
-  }
+  p.gemv_mode = gemv_mode;
 
   const int kmax = (H > F ? H : F) > nh * hd ? (H > F ? H : F) : nh * hd;
-  const size_t xin_bytes = (size_t)M * kmax * 2;
+  const size_t xin_bytes = (size_t)M * ((kmax + MG_KS - 1) / MG_KS * MG_KS) * 2;      // whole k-stages (zero padded)
   const size_t attn_bytes = (size_t)(MG_CONSUMERS * 2) * G * (MG_HD + 2) * sizeof(float);
   const size_t fixed = 1024 + xin_bytes + attn_bytes + 64;
   const size_t budget = 225 * 1024;
   JL_CHECK_ARG(fixed + 4 * (MG_STAGE_BYTES + 16) <= budget, "jl_decode_mega: M=%d, F=%d leave no room for the weight ring", M, F);
   int stages = (int)((budget - fixed) / (MG_STAGE_BYTES + 16));
   if (stages > 12) stages = 12;
+  {
+    static const int cap = [] { const char* e = getenv("JLLAMA_MEGA_STAGES"); return e ? atoi(e) : 0; }();   // A/B: ring depth
+    if (cap >= 4 && cap < stages) stages = cap;
+  }
   p.stages = stages;
   const size_t smem = fixed + (size_t)stages * (MG_STAGE_BYTES + 16);
 

@@ -243,6 +243,8 @@ int make_tmap_2d_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, u
                             uint32_t box_cols, uint32_t box_rows);
 // Un-swizzled "slab" view of a [rows, cols] matrix as [rows, cols/256, 256]: one request moves
 // box_rows x box_slabs x 256 elements (e.g. 8 rows x 4 slabs = 16 KB); smem layout [row][slab][256].
+int make_tmap_kblock_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                          uint32_t box_kblocks, uint32_t box_rows);
 int make_tmap_slab_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
                               uint32_t box_slabs, uint32_t box_rows);
 // 3-D variant: [d2, rows, cols] with element strides (ld2, ld1, 1); box {64, box_rows, 1}.

@@ -82,6 +82,20 @@ int make_tmap_slab_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows,
   return encode(out, base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE);
 }
 
+// [rows, cols] viewed as [cols/64 k-blocks][rows][64]: one request moves box_kblocks x box_rows rows of 128 B,
+// stored k-block-major with the 128-byte swizzle — the canonical K-major tile ldmatrix / UMMA read conflict-free
+int make_tmap_kblock_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                          uint32_t box_kblocks, uint32_t box_rows) {
+  if (cols % 64 != 0) {
+    set_error("k-block tensor map needs a column count that is a multiple of 64 (got %llu)", (unsigned long long)cols);
+    return JL_ERR_ARG;
+  }
+  cuuint64_t dims[3] = {64, rows, cols / 64};
+  cuuint64_t strides[2] = {ld * 2, 64 * 2};
+  cuuint32_t box[3] = {64, box_rows, box_kblocks};
+  return encode(out, base, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t d2, uint64_t rows, uint64_t cols,
                       uint64_t ld2, uint64_t ld1, uint32_t box_rows) {
   cuuint64_t dims[3] = {cols, rows, d2};

@@ -131,7 +131,7 @@ int jl_decode_advance(const int* tok, int* next_ids, int* finished, int* sequenc
  * caller advances the epoch counter behind seq_ptr by 2*L per step (jl_comm_bump; see parallel/comm.py). */
 int jl_decode_mega_barriers(int L);
 size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, int num_sms);
-void jl_decode_mega_set_trace(void* buf /* device u64 [2][L][16] %globaltimer stamps, NULL = off */);
+void jl_decode_mega_set_trace(void* buf /* device u64 [num_sms][L][32] %globaltimer stamps, NULL = off */);
 int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
                    const void* lm_head, const void* attn_norm, const void* ffn_norm, const void* final_norm,
                    const void* embedding, const int* ids, void* x, void* qkv, void* attn, void* hmlp,

@@ -57,6 +57,9 @@ def lib() -> C.CDLL:
     if _lib is not None:
         return _lib
     path = LIB_PATH
+    if os.environ.get("JLLAMA_LIB"):           # A/B of two builds on one box (scripts/sweep_env.sh JLLAMA_LIB "a.so b.so")
+        from pathlib import Path
+        path = Path(os.environ["JLLAMA_LIB"])
     if not path.exists():
         if os.environ.get("JLLAMA_NO_AUTOBUILD"):
             raise NativeLibraryError(f"{path} is missing: run `python -m jax_llama_b200.ops.build`")

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Per-op timeline of the persistent decode kernel (globaltimer stamps from block 0 and the last block)."""
+"""Per-op timeline of the persistent decode kernel (globaltimer stamps from every block)."""
 import ctypes as C
 import os
 import sys
@@ -28,14 +28,16 @@ samp = (False, 1.0, 0, 1.0, 0)
 eng._select_and_advance_after_prefill(st, cache, samp, -1, 0)
 for _ in range(3):
     eng._decode_step(st, cache, samp, -1, 0)
-trace = torch.zeros(2 * L * EV, dtype=torch.int64, device="cuda")
+NB = torch.cuda.get_device_properties(local).multi_processor_count
+trace = torch.zeros(NB * L * EV, dtype=torch.int64, device="cuda")
 lib = _lib.lib()
 lib.jl_decode_mega_set_trace.argtypes = [C.c_void_p]
 lib.jl_decode_mega_set_trace(trace.data_ptr())
 eng._decode_step(st, cache, samp, -1, 0)
 torch.cuda.synchronize()
 lib.jl_decode_mega_set_trace(None)
-t = trace.view(2, L, EV).cpu().double()
+tall = trace.view(NB, L, EV).cpu().double()
+t = tall[[0, NB - 1]]
 if rank != 0:
     sys.exit(0)
 names = ["stage_qkv", "gemv_qkv", "bar", "attn", "bar(+merge)", "stage_wo", "gemv_wo", "bar", "stage_w13", "gemv_w13",
@@ -49,3 +51,17 @@ for blk in range(2):
 a = (t[0, lo:hi, 16:21] - t[0, lo:hi, 3:4]) / 1e3
 print("block 0 attention internals (µs after the phase starts): " + "  ".join(
     f"{n}={v:.1f}" for n, v in zip(["setup", "q+rope", "kv_loop", "new_tok", "fold+write"], a.mean(0).tolist())))
+
+# spread across blocks: when does each block finish each phase, relative to the earliest block entering it
+ends = {"gemv_qkv": 2, "attn": 4, "gemv_wo": 7, "gemv_w13": 10, "gemv_w2": 13}
+starts = {"gemv_qkv": 1, "attn": 3, "gemv_wo": 6, "gemv_w13": 9, "gemv_w2": 12}
+smid = tall[:, lo, 31].long()
+for n in ends:
+    begin = tall[:, lo:hi, starts[n]].min(0).values                      # [layers]
+    fin = (tall[:, lo:hi, ends[n]] - begin[None]) / 1e3                  # [blocks, layers]
+    own = (tall[:, lo:hi, ends[n]] - tall[:, lo:hi, starts[n]]) / 1e3
+    m = fin.mean(1)
+    order = m.argsort()
+    print(f"{n:9s} finish after phase start: min {m.min():5.1f}  p50 {m.median():5.1f}  p90 {m.quantile(0.9):5.1f}  max {m.max():5.1f} us"
+          f" | own duration p50 {own.mean(1).median():5.1f} max {own.mean(1).max():5.1f}"
+          f" | slowest blocks {order[-6:].tolist()} (sm {smid[order[-6:]].tolist()}) fastest {order[:4].tolist()}")
