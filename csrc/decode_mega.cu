@@ -1,4 +1,4 @@
-// Persistent whole-model decode step ("megakernel") for small batches (M <= 4 tokens).
+// Persistent whole-model decode step ("megakernel") for small batches (M <= 8 tokens).
 //
 // Why: a decode step of an 8B model is ~225 dependent kernels whose useful work is 5-40 µs each.  Measured
 // with ncu on B200, every one of them loses 5-10 µs to CTA launch ramp, prologue and tail (SMs active for
@@ -6,15 +6,23 @@
 // streaming kernels fill the SM.  Here ONE cooperative kernel with one CTA per SM runs the entire step:
 //
 //   * warp 0 is a TMA producer that streams every weight matrix of the model, layer after layer, through a
-//     shared-memory ring (16 KB stages, 4 tensor-map boxes of [8 rows x 256 cols] each).  It depends on
-//     nothing but free ring slots, so it runs ahead across op boundaries: while the consumers sit in a grid
-//     barrier or do attention, the next op's weights are already landing.  HBM never idles.
-//   * warps 1..8 are consumers: RMSNorm + GEMV (one weight row per warp per stage), residual / SwiGLU
-//     epilogues, RoPE + KV append + split-KV GQA attention (one (batch, kv-head, split) item per CTA, merge
-//     by the last-arriving CTA), final norm + LM head.
+//     shared-memory ring: one 16 KB request per stage ([16 k-blocks][8 rows][128 B], 128-byte swizzle).  It
+//     depends on nothing but free ring slots, so it runs ahead across op boundaries: while the consumers sit in
+//     a grid barrier or do attention, the next op's weights are already landing.
+//   * warps 1..8 are consumers: RMSNorm + tensor-core GEMV (ldmatrix + mma.sync, see decode_mega_mma.cuh),
+//     residual / SwiGLU epilogues, RoPE + KV append + split-KV GQA attention (one (batch, kv-head, split) item
+//     per CTA, merge spread over the grid), final norm + LM head.
 //   * ops are separated by a grid-wide barrier (monotonic atomic counter, acquire spin with a watchdog);
 //     activations cross CTAs through L2 (ld.global.cg), never through stale L1 lines.
 //   * rows of each GEMV are cut into 148 contiguous, near-equal ranges (±1 group of 8 rows).
+//
+// History (all measured on B200, LLaMA-3 8B, batch 1, ms per token): SIMT consumers with one weight row per
+// warp 3.69 → one 16 KB TMA request per stage 3.64 → activations in registers 3.18-3.39 (box dependent; ncu:
+// ~1 instruction issued per cycle per SM, ~1100 warp-instructions per stage — instruction-latency bound, `w2`
+// at 35 GB/s per SM whatever the ring depth) → tensor-core consumers 3.04 on the box that gave 3.39 (GEMV
+// phases at 6.4-7.3 TB/s).  An L2 prefetch cursor running ahead of the ring was tried twice and was slower
+// every time (+9 % at 16 stages ahead, +60 % at 64); 4-row work units to even out the 24/32-row split were
+// neutral once the phases were HBM-bound.
 //
 // Weights of all layers are stacked per op ([L·N, K]) so five tensor maps describe the whole model.
 // Math is identical to the unfused kernels (gemv.cu, decode_attn_fused.cu); the tests compare the two.
@@ -32,13 +40,12 @@ constexpr int MG_THREADS = (MG_CONSUMERS + 1) * 32;
 constexpr int MG_CT = MG_CONSUMERS * 32;           // consumer threads
 constexpr int MG_GROUP = 8;                        // weight rows per stage (one per consumer warp)
 constexpr int MG_KS = 1024;                        // K elements per stage
-constexpr int MG_BOX_BYTES = MG_GROUP * 256 * 2;   // 4 KB box [8 rows x 256 cols]
-constexpr int MG_STAGE_BYTES = 4 * MG_BOX_BYTES;   // 16 KB
+constexpr int MG_STAGE_BYTES = MG_GROUP * MG_KS * 2;   // 16 KB
 constexpr int MG_HD = 128;
 constexpr int MG_KPI = 4;
 
 struct alignas(64) MegaTmaps {
-  CUtensorMap m[6];          // wqkv_all, wo_all, w13_all, w2_all (8-row boxes), lm_head, w2_all (4-row boxes)
+  CUtensorMap m[5];          // wqkv_all, wo_all, w13_all, w2_all, lm_head
 };
 
 // Tensor-parallel all-reduce state (tp == 1: unused).  Same inbox / flag protocol as comm.cu.
@@ -77,7 +84,6 @@ struct MegaParams {
   unsigned int* bar_gen;             // barriers completed by previous launches
   int T, max_pos, splits, stages;
   unsigned long long* trace;         // optional [2][L][16] globaltimer stamps (block 0 and the last block)
-  int gemv_mode;                     // 0: row-owner warps when K == 4096, column-owner otherwise; 1: always column-owner
 };
 
 enum { MG_PLAIN = 0, MG_RESIDUAL = 1, MG_SWIGLU = 2, MG_LOGITS = 3 };
@@ -131,15 +137,9 @@ __device__ __forceinline__ void mg_push_partial(const MegaCtx& c, int m, int row
 }
 
 // ------------------------------------------------------------------------------------ producer side
-// Stages the L2 prefetch cursor may run ahead of the ring; settable at run time (JLLAMA_MEGA_L2_AHEAD) because
-// the right value is an empirical trade: 40 (95 MB over 148 SMs) measured SLOWER than none (121.8 vs 107.6 µs
-// per layer) — the prefetch stream competes with the latency-critical barrier / attention traffic.
-__device__ int g_mg_l2_ahead = 0;
-#define MG_L2_AHEAD g_mg_l2_ahead
-
 // Position in the model-wide weight stream of one CTA: (layer, op, row group, k stage).
 struct MegaCursor {
-  int l, op, g, g1, ks, n_ks, row_base, rows;      // rows: weight rows per stage of this op (8, or 4 for w2)
+  int l, op, g, g1, ks, n_ks, row_base;
   bool done;
   __device__ __forceinline__ bool step_op() {
     if (op == 4) { done = true; return false; }
@@ -154,11 +154,10 @@ struct MegaCursor {
         case 0: N = p.NQKV; K = p.H; row_base = l * p.NQKV; break;
         case 1: N = p.H; K = qdim; row_base = l * p.H; break;
         case 2: N = 2 * p.F; K = p.H; row_base = l * 2 * p.F; break;
-        case 3: N = p.H; K = p.F; row_base = l * p.H; break;      // 4-row groups: see decode_mega_gemv.cuh
+        case 3: N = p.H; K = p.F; row_base = l * p.H; break;
         default: N = p.V; K = p.H; row_base = 0; break;
       }
-      rows = MG_GROUP;        // (4-row groups for w2 were tried: 8 KB stages double the per-stage overhead, 33 vs 23 µs)
-      mg_range(N / rows, g, g1);
+      mg_range(N / MG_GROUP, g, g1);
       ks = 0;
       n_ks = (K + MG_KS - 1) / MG_KS;
       if (g < g1) return;
@@ -173,155 +172,10 @@ struct MegaCursor {
     if (step_op()) load_op(p, qdim);
   }
   __device__ __forceinline__ int map() const { return op; }
-  __device__ __forceinline__ uint32_t bytes() const { return (uint32_t)rows * (MG_KS * 2); }
-  __device__ __forceinline__ int row() const { return row_base + g * rows; }
+  __device__ __forceinline__ int row() const { return row_base + g * MG_GROUP; }
 };
 
-// ------------------------------------------------------------------------------------ consumer side
-// stage [M, K] activations from global (written by other CTAs → L2 loads) into smem, optional RMSNorm
-template <int M>
-__device__ __forceinline__ void mg_stage_input(MegaCtx& c, const __nv_bfloat16* src, int K,
-                                               const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS]) {
-  const int ct = threadIdx.x - 32, lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
-  const int K8 = K >> 3;
-  if (norm_w != nullptr) {
-    float ss[M];
-#pragma unroll
-    for (int m = 0; m < M; ++m) ss[m] = 0.f;
-    for (int i = ct; i < K8; i += MG_CT) {
-#pragma unroll
-      for (int m = 0; m < M; ++m) {
-        const uint4 a = ldcg16(src + ((size_t)m * K8 + i) * 8);
-        c.xin[m * K8 + i] = a;                         // raw copy; normalised in place below
-        const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float lo = bf16_lo(aw[j]), hi = bf16_hi(aw[j]);
-          ss[m] += lo * lo + hi * hi;
-        }
-      }
-    }
-#pragma unroll
-    for (int m = 0; m < M; ++m) {
-      const float t = warp_sum(ss[m]);
-      if (lane == 0) red[m][cw] = t;
-    }
-    mg_consumer_bar();
-    float rinv[M];
-#pragma unroll
-    for (int m = 0; m < M; ++m) {
-      float t = lane < MG_CONSUMERS ? red[m][lane] : 0.f;
-      t = warp_sum(t);
-      rinv[m] = rsqrtf(t / (float)K + eps);
-    }
-    for (int i = ct; i < K8; i += MG_CT) {
-      const uint4 g = __ldg(reinterpret_cast<const uint4*>(norm_w) + i);
-      const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
-#pragma unroll
-      for (int m = 0; m < M; ++m) {
-        const uint4 a = c.xin[m * K8 + i];             // written by this same thread above
-        const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-        uint32_t o[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          o[j] = pack_bf16(bf16_lo(aw[j]) * rinv[m] * bf16_lo(gw[j]), bf16_hi(aw[j]) * rinv[m] * bf16_hi(gw[j]));
-        c.xin[m * K8 + i] = make_uint4(o[0], o[1], o[2], o[3]);
-      }
-    }
-  } else {
-    for (int i = ct; i < M * K8; i += MG_CT) c.xin[i] = ldcg16(src + (size_t)i * 8);
-  }
-  mg_consumer_bar();
-}
-
-// one GEMV op over this CTA's row range: out rows = op(W[row_base + r, :] · xin)
-// NKS_REG > 0: K == NKS_REG·1024 is known at compile time and this lane's activation chunks live in registers
-// for the whole op (shared memory then carries only the TMA write and one read of the weights — with the
-// activations also read from smem every stage the three streams add up to ~126 B/clk/SM, the smem limit).
-template <int M, int MODE, int NKS_REG>
-__device__ __forceinline__ void mg_gemv(MegaCtx& c, int N, int K, void* out, const __nv_bfloat16* residual,
-                                        float (*s_res)[M][MG_CONSUMERS]) {
-  const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
-  const int K8 = K >> 3;
-  int g0, g1;
-  mg_range(N / MG_GROUP, g0, g1);
-  constexpr bool XREG = NKS_REG > 0;
-  const int n_ks = XREG ? NKS_REG : (K + MG_KS - 1) / MG_KS;
-  uint4 xr[XREG ? M : 1][XREG ? NKS_REG * 4 : 1];
-  if constexpr (XREG) {
-#pragma unroll
-    for (int m = 0; m < M; ++m)
-#pragma unroll
-      for (int j = 0; j < NKS_REG * 4; ++j) xr[m][j] = c.xin[m * K8 + (j >> 2) * (MG_KS / 8) + (j & 3) * 32 + lane];
-  }
-  for (int g = g0; g < g1; ++g) {
-    float acc[M];
-#pragma unroll
-    for (int m = 0; m < M; ++m) acc[m] = 0.f;
-#pragma unroll
-    for (int ks = 0; ks < n_ks; ++ks) {
-      tc::mbar_wait(c.bars + 8u * c.stage, c.phase);
-      // stage layout [row][slab][256 cols]: this warp's row, slab b, this lane's 16-byte chunk
-      const uint4* wr = reinterpret_cast<const uint4*>(c.ring_ptr + c.stage * MG_STAGE_BYTES) + cw * 128 + lane;
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const int ch = ks * (MG_KS / 8) + b * 32 + lane;
-        if (ch < K8) {
-          const uint4 wv = wr[b * 32];
-          const float wf[8] = {bf16_lo(wv.x), bf16_hi(wv.x), bf16_lo(wv.y), bf16_hi(wv.y),
-                               bf16_lo(wv.z), bf16_hi(wv.z), bf16_lo(wv.w), bf16_hi(wv.w)};
-#pragma unroll
-          for (int m = 0; m < M; ++m) {
-            uint4 xv;
-            if constexpr (XREG) xv = xr[m][ks * 4 + b];
-            else xv = c.xin[m * K8 + ch];
-            const float xf[8] = {bf16_lo(xv.x), bf16_hi(xv.x), bf16_lo(xv.y), bf16_hi(xv.y),
-                                 bf16_lo(xv.z), bf16_hi(xv.z), bf16_lo(xv.w), bf16_hi(xv.w)};
-#pragma unroll
-            for (int e = 0; e < 8; ++e) acc[m] = fmaf(wf[e], xf[e], acc[m]);
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) tc::mbar_arrive(c.bars + 8u * (c.stages + c.stage));
-      if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
-    }
-#pragma unroll
-    for (int m = 0; m < M; ++m) acc[m] = warp_sum(acc[m]);
-    const int row = g * MG_GROUP + cw;
-    if constexpr (MODE == MG_SWIGLU) {
-      // (gate, up) rows sit in adjacent warps: exchange through smem, even warps finish the pair
-      float (*buf)[MG_CONSUMERS] = s_res[g & 1];
-      if (lane == 0) {
-#pragma unroll
-        for (int m = 0; m < M; ++m) buf[m][cw] = __bfloat162float(__float2bfloat16(acc[m]));
-      }
-      // only the two warps of a (gate, up) pair meet: named barrier 2 + pair index, 64 threads
-      asm volatile("bar.sync %0, 64;" ::"r"(2 + (cw >> 1)) : "memory");
-      if ((cw & 1) == 0 && lane < M) {
-        const float gate = buf[lane][cw], up = buf[lane][cw + 1];
-        reinterpret_cast<__nv_bfloat16*>(out)[(size_t)lane * (N / 2) + row / 2] = __float2bfloat16(silu(gate) * up);
-      }
-    } else if (lane == 0) {
-#pragma unroll
-      for (int m = 0; m < M; ++m) {
-        float v = acc[m];
-        if constexpr (MODE == MG_LOGITS) {
-          reinterpret_cast<float*>(out)[(size_t)m * N + row] = v;
-        } else {
-          if constexpr (MODE == MG_RESIDUAL) {
-            if (c.ar->tp > 1) { mg_push_partial<M>(c, m, row, N, v); continue; }      // reduced in mg_ar_finish
-            v = __bfloat162float(__float2bfloat16(v)) + __bfloat162float(__ldcg(residual + (size_t)m * N + row));
-          }
-          reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * N + row] = __float2bfloat16(v);
-        }
-      }
-    }
-  }
-}
-
 }  // namespace jl
-#include "decode_mega_gemv.cuh"
 #include "decode_mega_mma.cuh"
 namespace jl {
 
@@ -650,8 +504,6 @@ __global__ void __launch_bounds__(MG_THREADS, 1)
 decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ float red[M][MG_CONSUMERS];
-  __shared__ float s_part[2][MG_CONSUMERS][M][4];
-  __shared__ float s_res[2][M][MG_CONSUMERS];
   __shared__ __align__(16) float s_acc[2][MG_CONSUMERS][MG_MMA_MAX_M][8];
   __shared__ int s_last;
   constexpr int NG = MG_CONSUMERS * (32 / (MG_HD / 8));
@@ -671,7 +523,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 6; ++i) tc::prefetch_tensormap(&tm.m[i]);
+    for (int i = 0; i < 5; ++i) tc::prefetch_tensormap(&tm.m[i]);
     for (int s = 0; s < p.stages; ++s) {
       tc::mbar_init(c.bars + 8u * s, 1);
       tc::mbar_init(c.bars + 8u * (p.stages + s), MG_CONSUMERS);
@@ -684,35 +536,19 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   if (warp == 0) {
     // ===================================================== producer: the whole model's weights, in order
     if (lane == 0) {
-      // Two cursors walk the same (layer, op, row group, k stage) sequence: `ld` feeds the shared-memory ring,
-      // `pf` runs up to MG_L2_AHEAD stages further and only asks the L2 to fetch.  Whenever the ring is full
-      // (consumers are in a grid barrier or in attention) the producer spends the wait prefetching, so the
-      // HBM stream does not stop at op boundaries; the later ring loads then hit L2.
-      MegaCursor ld, pf;
+      MegaCursor ld;
       ld.init(p, qdim);
-      pf = ld;
-      int ahead = 0;
       while (!ld.done) {
         // try_wait suspends the thread in hardware until the slot frees or a time-out elapses; a busy
         // test_wait loop here steals issue slots from the two consumer warps that share this scheduler
         // (measured: 122 vs 108 µs per layer)
         if (tc::mbar_try_wait(c.bars + 8u * (c.stages + c.stage), c.phase ^ 1)) {
           const uint32_t full = c.bars + 8u * c.stage;
-          tc::mbar_expect_tx(full, ld.bytes());
-          if (p.gemv_mode == 2)       // swizzled [k-block][row][128 B] stage for the tensor-core GEMV
-            tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.row(), ld.ks * (MG_KS / 64),
-                            tc::EVICT_FIRST);
-          else
-            tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.ks * (MG_KS / 256), ld.row(),
-                            tc::EVICT_FIRST);
+          tc::mbar_expect_tx(full, MG_STAGE_BYTES);
+          tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.row(), ld.ks * (MG_KS / 64),
+                          tc::EVICT_FIRST);
           if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
           ld.next(p, qdim);
-          if (ahead > 0) --ahead; else pf = ld;
-        } else if (!pf.done && ahead < MG_L2_AHEAD) {
-          if (ahead >= c.stages)       // the first `stages` positions are about to be loaded anyway
-            tc::tma_prefetch_3d(&tm.m[pf.map()], 0, pf.ks * (MG_KS / 256), pf.row());
-          pf.next(p, qdim);
-          ++ahead;
         }
       }
     }
@@ -720,22 +556,8 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   }
 
   // ===================================================== consumers
-  // K == 4096 (and M <= 2): activations stay in registers for the whole op (see mg_gemv)
-#define MG_STAGE(SRC_, K_, NORM_)                                                                            \
-  do {                                                                                                       \
-    if (p.gemv_mode == 2) mg_stage_input_mma<M>(c, SRC_, K_, NORM_, p.eps, red);                             \
-    else mg_stage_input<M>(c, SRC_, K_, NORM_, p.eps, red);                                                  \
-  } while (0)
-#define MG_GEMV(MODE_, N_, K_, OUT_, RES_, ROWS_)                                                            \
-  do {                                                                                                       \
-    if (p.gemv_mode == 2) mg_gemv_mma<M, MODE_>(c, N_, K_, OUT_, RES_, s_acc);                               \
-    else if ((K_) == 4 * MG_KS && M == 1 && ROWS_ == 8 && p.gemv_mode == 0)                                  \
-      mg_gemv<M, MODE_, (M == 1 ? 4 : 0)>(c, N_, K_, OUT_, RES_, s_res);                                     \
-    else if ((K_) <= 4 * MG_KS) mg_gemv2<M, MODE_, 4, true, ROWS_>(c, N_, K_, OUT_, RES_, s_part);            \
-    else if ((K_) <= 16 * MG_KS && M == 1)                                                                   \
-      mg_gemv2<M, MODE_, (M == 1 ? 16 : 4), (M == 1), ROWS_>(c, N_, K_, OUT_, RES_, s_part);                 \
-    else mg_gemv2<M, MODE_, 1, false, ROWS_>(c, N_, K_, OUT_, RES_, s_part);                                 \
-  } while (0)
+#define MG_STAGE(SRC_, K_, NORM_) mg_stage_input_mma<M>(c, SRC_, K_, NORM_, p.eps, red)
+#define MG_GEMV(MODE_, N_, K_, OUT_, RES_) mg_gemv_mma<M, MODE_>(c, N_, K_, OUT_, RES_, s_acc)
   const unsigned int gen_base = *reinterpret_cast<volatile unsigned int*>(p.bar_gen);
   int bar_idx = 0;
   const MgPos pos0 = mg_pos(p, 0, lane % (MG_HD / 8));      // batch row 0: constant for the whole step
@@ -759,7 +581,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     mg_stamp(p, l, 0);
     MG_STAGE(p.x, p.H, p.attn_norm + (size_t)l * p.H);
     mg_stamp(p, l, 1);
-    MG_GEMV(MG_PLAIN, p.NQKV, p.H, p.qkv, nullptr, 8);
+    MG_GEMV(MG_PLAIN, p.NQKV, p.H, p.qkv, nullptr);
     mg_stamp(p, l, 2);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 3);
@@ -783,7 +605,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     MG_STAGE(p.attn, qdim, nullptr);
     mg_stamp(p, l, 6);
     c.ar_epoch = ar_base + 2 * l + 1;
-    MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x, 8);
+    MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x);
     if (p.ar.tp > 1) mg_ar_finish<M>(p, c, ar_base + 2 * l + 1, p.H);
     mg_stamp(p, l, 7);
     mg_grid_barrier(p, gen_base, bar_idx);
@@ -791,7 +613,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
     MG_STAGE(p.x, p.H, p.ffn_norm + (size_t)l * p.H);
     mg_stamp(p, l, 9);
-    MG_GEMV(MG_SWIGLU, 2 * p.F, p.H, p.hmlp, nullptr, 8);
+    MG_GEMV(MG_SWIGLU, 2 * p.F, p.H, p.hmlp, nullptr);
     mg_stamp(p, l, 10);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 11);
@@ -799,7 +621,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     MG_STAGE(p.hmlp, p.F, nullptr);
     mg_stamp(p, l, 12);
     c.ar_epoch = ar_base + 2 * l + 2;
-    MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x, 8);
+    MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x);
     if (p.ar.tp > 1) mg_ar_finish<M>(p, c, ar_base + 2 * l + 2, p.H);
     mg_stamp(p, l, 13);
     mg_grid_barrier(p, gen_base, bar_idx);
@@ -807,7 +629,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   }
   // ---- final norm + LM head
   MG_STAGE(p.x, p.H, p.final_norm);
-  MG_GEMV(MG_LOGITS, p.V, p.H, p.logits, nullptr, 8);
+  MG_GEMV(MG_LOGITS, p.V, p.H, p.logits, nullptr);
   mg_grid_barrier(p, gen_base, bar_idx);
   if (blockIdx.x == 0 && threadIdx.x == 32) *p.bar_gen = gen_base + (unsigned)bar_idx;
 }
@@ -830,7 +652,27 @@ extern "C" JL_API size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, in
   return parts + (size_t)M * nkv * sizeof(int) + 2 * sizeof(unsigned int) + 64;
 }
 
-// One decode step of the whole model for M <= 4 rows.  Weight pointers are the per-op stacks [L·N, K].
+// Shared-memory plan: the staged activations (M rows of the widest GEMV input, whole k-stages), the attention
+// scratch and whatever is left for the weight ring.  Returns the ring depth (< 4: the configuration does not fit).
+static int mega_ring_stages(int M, int H, int F, int nh, int nkv, int hd, size_t* fixed_out) {
+  const int G = nkv > 0 ? nh / nkv : 1;
+  const int kmax = (H > F ? H : F) > nh * hd ? (H > F ? H : F) : nh * hd;
+  const size_t xin_bytes = (size_t)M * ((kmax + MG_KS - 1) / MG_KS * MG_KS) * 2;      // whole k-stages (zero padded)
+  const size_t attn_bytes = (size_t)(MG_CONSUMERS * 2) * G * (MG_HD + 2) * sizeof(float);
+  const size_t fixed = 1024 + xin_bytes + attn_bytes + 64;
+  const size_t budget = 225 * 1024;
+  if (fixed_out) *fixed_out = fixed;
+  if (fixed + 4 * (MG_STAGE_BYTES + 16) > budget) return 0;
+  int stages = (int)((budget - fixed) / (MG_STAGE_BYTES + 16));
+  return stages > 12 ? 12 : stages;
+}
+// ring depth jl_decode_mega would use for this shape, 0 when the batch does not fit (use the per-op path then)
+extern "C" JL_API int jl_decode_mega_stages(int M, int H, int F, int nh, int nkv, int hd) {
+  if (M < 1 || M > 8 || hd != MG_HD || nkv <= 0 || nh % nkv) return 0;
+  return mega_ring_stages(M, H, F, nh, nkv, hd, nullptr);
+}
+
+// One decode step of the whole model for M <= 8 rows.  Weight pointers are the per-op stacks [L·N, K].
 extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
                                      const void* lm_head, const void* attn_norm, const void* ffn_norm,
                                      const void* final_norm, const void* embedding, const int* ids, void* x, void* qkv,
@@ -840,7 +682,7 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
                                      int hd, int T, int max_pos, float eps, float scale, int num_sms, int tp, int rank,
                                      void* const* peer_inbox, void* const* peer_flags, size_t inbox_parity_stride_floats,
                                      int flag_offset, const int* seq_ptr, void* stream) {
-  JL_CHECK_ARG(M >= 1 && M <= 4, "jl_decode_mega: M=%d outside 1..4", M);
+  JL_CHECK_ARG(M >= 1 && M <= 8, "jl_decode_mega: M=%d outside 1..8", M);
   JL_CHECK_ARG(hd == MG_HD, "jl_decode_mega: head_dim=%d (only 128 is built)", hd);
   JL_CHECK_ARG(nkv > 0 && nh % nkv == 0, "jl_decode_mega: nh=%d not a multiple of nkv=%d", nh, nkv);
   const int G = nh / nkv;
@@ -849,35 +691,13 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   JL_CHECK_ARG(H % 256 == 0 && F % 256 == 0 && (nh * hd) % 256 == 0 && V % 8 == 0 && NQKV % 8 == 0,
                "jl_decode_mega: H=%d, F=%d and nh*hd must be multiples of 256, V=%d of 8", H, F, V);
   if (num_sms <= 0) num_sms = 148;
-  {
-    static bool configured = false;            // one-time: L2 look-ahead depth from the environment
-    if (!configured) {
-      const char* e = getenv("JLLAMA_MEGA_L2_AHEAD");
-      const int v = e ? atoi(e) : 0;
-      JL_CUDA(cudaMemcpyToSymbol(g_mg_l2_ahead, &v, sizeof(int)));
-      configured = true;
-    }
-  }
-  // GEMV flavour: 2 = tensor-core (mma.sync) consumers on swizzled stages (default), 0 / 1 = the SIMT paths
-  static const int gemv_mode = [] { const char* e = getenv("JLLAMA_MEGA_GEMV"); return e ? atoi(e) : 2; }();
   MegaTmaps tm;
   int rc;
-  if (gemv_mode == 2) {
-    if ((rc = make_tmap_kblock_bf16(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, MG_KS / 64, MG_GROUP))) return rc;
-    if ((rc = make_tmap_kblock_bf16(&tm.m[1], wo_all, (uint64_t)L * H, nh * hd, nh * hd, MG_KS / 64, MG_GROUP))) return rc;
-    if ((rc = make_tmap_kblock_bf16(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, MG_KS / 64, MG_GROUP))) return rc;
-    if ((rc = make_tmap_kblock_bf16(&tm.m[3], w2_all, (uint64_t)L * H, F, F, MG_KS / 64, MG_GROUP))) return rc;
-    if ((rc = make_tmap_kblock_bf16(&tm.m[4], lm_head, (uint64_t)V, H, H, MG_KS / 64, MG_GROUP))) return rc;
-    tm.m[5] = tm.m[3];
-  } else {
-  if ((rc = make_tmap_slab_bf16_plain(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, MG_KS / 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_slab_bf16_plain(&tm.m[1], wo_all, (uint64_t)L * H, nh * hd, nh * hd, MG_KS / 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_slab_bf16_plain(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, MG_KS / 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_slab_bf16_plain(&tm.m[3], w2_all, (uint64_t)L * H, F, F, MG_KS / 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_slab_bf16_plain(&tm.m[4], lm_head, (uint64_t)V, H, H, MG_KS / 256, MG_GROUP))) return rc;
-  if ((rc = make_tmap_slab_bf16_plain(&tm.m[5], w2_all, (uint64_t)L * H, F, F, MG_KS / 256, 4))) return rc;
-  }
-
+  if ((rc = make_tmap_kblock_bf16(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, MG_KS / 64, MG_GROUP))) return rc;
+  if ((rc = make_tmap_kblock_bf16(&tm.m[1], wo_all, (uint64_t)L * H, nh * hd, nh * hd, MG_KS / 64, MG_GROUP))) return rc;
+  if ((rc = make_tmap_kblock_bf16(&tm.m[2], w13_all, (uint64_t)L * 2 * F, H, H, MG_KS / 64, MG_GROUP))) return rc;
+  if ((rc = make_tmap_kblock_bf16(&tm.m[3], w2_all, (uint64_t)L * H, F, F, MG_KS / 64, MG_GROUP))) return rc;
+  if ((rc = make_tmap_kblock_bf16(&tm.m[4], lm_head, (uint64_t)V, H, H, MG_KS / 64, MG_GROUP))) return rc;
   MegaParams p{};
   p.L = L; p.H = H; p.F = F; p.V = V; p.nh = nh; p.nkv = nkv; p.NQKV = NQKV; p.vocab_full = vocab_full;
   p.eps = eps; p.scale_log2 = scale * 1.4426950408889634f;
@@ -906,16 +726,10 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
     for (int i = 0; i < p.ar.tp; ++i) { p.ar.inbox[i] = (float*)peer_inbox[i]; p.ar.flags[i] = (int*)peer_flags[i]; }
   }
   p.trace = g_mega_trace;
-  p.gemv_mode = gemv_mode;
 
-  const int kmax = (H > F ? H : F) > nh * hd ? (H > F ? H : F) : nh * hd;
-  const size_t xin_bytes = (size_t)M * ((kmax + MG_KS - 1) / MG_KS * MG_KS) * 2;      // whole k-stages (zero padded)
-  const size_t attn_bytes = (size_t)(MG_CONSUMERS * 2) * G * (MG_HD + 2) * sizeof(float);
-  const size_t fixed = 1024 + xin_bytes + attn_bytes + 64;
-  const size_t budget = 225 * 1024;
-  JL_CHECK_ARG(fixed + 4 * (MG_STAGE_BYTES + 16) <= budget, "jl_decode_mega: M=%d, F=%d leave no room for the weight ring", M, F);
-  int stages = (int)((budget - fixed) / (MG_STAGE_BYTES + 16));
-  if (stages > 12) stages = 12;
+  size_t fixed = 0;
+  int stages = mega_ring_stages(M, H, F, nh, nkv, hd, &fixed);
+  JL_CHECK_ARG(stages >= 4, "jl_decode_mega: M=%d, F=%d leave no room for the weight ring", M, F);
   {
     static const int cap = [] { const char* e = getenv("JLLAMA_MEGA_STAGES"); return e ? atoi(e) : 0; }();   // A/B: ring depth
     if (cap >= 4 && cap < stages) stages = cap;
@@ -925,8 +739,9 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
 
   void (*kern)(const MegaTmaps, const MegaParams) = nullptr;
 #define JL_MG(M_, G_) if (M == M_ && G == G_) kern = decode_mega_kernel<M_, G_>;
-  JL_MG(1, 1) JL_MG(1, 2) JL_MG(1, 4) JL_MG(1, 8) JL_MG(2, 1) JL_MG(2, 2) JL_MG(2, 4) JL_MG(2, 8)
-  JL_MG(3, 1) JL_MG(3, 2) JL_MG(3, 4) JL_MG(3, 8) JL_MG(4, 1) JL_MG(4, 2) JL_MG(4, 4) JL_MG(4, 8)
+#define JL_MG_ROW(M_) JL_MG(M_, 1) JL_MG(M_, 2) JL_MG(M_, 4) JL_MG(M_, 8)
+  JL_MG_ROW(1) JL_MG_ROW(2) JL_MG_ROW(3) JL_MG_ROW(4) JL_MG_ROW(5) JL_MG_ROW(6) JL_MG_ROW(7) JL_MG_ROW(8)
+#undef JL_MG_ROW
 #undef JL_MG
   JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};

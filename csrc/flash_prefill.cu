@@ -475,6 +475,12 @@ flash_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_co
         fence_proxy_async();               // generic-proxy smem writes → visible to the tensor core
       }
       l_run += psum;
+      // Phase discipline of p_full: the MMA warp may still be parked on the V-tile barrier when this warp is
+      // done with tile j; without a guard all four softmax warps could complete phase j AND phase j+1 before
+      // the MMA warp looks at phase j, and a parity wait cannot tell "two phases later" from "not yet"
+      // (observed once as a hang at batch 8).  P·V_{j-1} having completed proves the MMA warp consumed phase
+      // j-1, so at most one phase is ever outstanding; the wait is almost always already satisfied.
+      if (P_TMEM && j > 0) tc::mbar_wait(o_full, (j - 1) & 1);
       tc::fence_before_sync();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(p_full);

@@ -121,7 +121,7 @@ int jl_decode_advance(const int* tok, int* next_ids, int* finished, int* sequenc
 
 /* ---------------------------------------------------------------------------------------------------------
  * Whole-model decode step (model.py:743-790 at S=1, i.e. everything FlaxLLaMAForCausalLMModule.__call__ does
- * for one new token) in ONE persistent cooperative kernel for M <= 4 rows: embedding, L x (RMSNorm+wqkv, RoPE,
+ * for one new token) in ONE persistent cooperative kernel for M <= 8 rows: embedding, L x (RMSNorm+wqkv, RoPE,
  * cache append, GQA attention, wo+residual, RMSNorm+w13+SwiGLU, w2+residual), final norm and LM head.
  * Weights are the per-op stacks [L*N, K]; x/qkv/attn/hmlp are bf16 activations the kernel uses between
  * phases; logits fp32 [M, V] (V = this rank's vocab shard, vocab_full the whole vocabulary); scratch must hold
@@ -131,6 +131,7 @@ int jl_decode_advance(const int* tok, int* next_ids, int* finished, int* sequenc
  * caller advances the epoch counter behind seq_ptr by 2*L per step (jl_comm_bump; see parallel/comm.py). */
 int jl_decode_mega_barriers(int L);
 size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, int num_sms);
+int jl_decode_mega_stages(int M, int H, int F, int nh, int nkv, int hd); /* weight-ring depth; 0 = shape does not fit */
 void jl_decode_mega_set_trace(void* buf /* device u64 [num_sms][L][32] %globaltimer stamps, NULL = off */);
 int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
                    const void* lm_head, const void* attn_norm, const void* ffn_norm, const void* final_norm,

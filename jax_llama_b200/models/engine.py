@@ -121,10 +121,22 @@ class B200Engine:
         self.cos, self.sin = cos.to(self.device), sin.to(self.device)
         self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
         self.warned_slow_prefill = False
+        self._mega_fit_cache: Dict[int, bool] = {}
         self.use_megakernel = use_megakernel and self.hd == 128 \
             and config.hidden_size % 256 == 0 and (config.intermediate_size // self.tp) % 256 == 0 \
             and (self.nh * self.hd) % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
         self._stack_weights()
+
+    def _mega_fits(self, batch: int) -> bool:
+        """Whole-step kernel usable for this batch: its staged activations (batch x widest GEMV input) must
+        leave room for a weight ring of at least 4 stages in shared memory (8B model: batch <= 4 at TP=1)."""
+        if not self.use_megakernel or batch > 8:
+            return False
+        if batch not in self._mega_fit_cache:
+            c = self.config
+            self._mega_fit_cache[batch] = int(_lib.lib().jl_decode_mega_stages(
+                batch, c.hidden_size, c.intermediate_size // self.tp, self.nh, self.nkv, self.hd)) >= 4
+        return self._mega_fit_cache[batch]
 
     def _mega_tp_args(self) -> Tuple:
         """(tp, rank, peer inbox table, peer flag table, parity stride in floats, flag offset, epoch counter)."""
@@ -465,7 +477,7 @@ class B200Engine:
         c = self.config
         if self.comm is not None:
             self.comm.begin_sequence()
-        if self.use_megakernel and st.B <= 4:
+        if self._mega_fits(st.B):
             # whole model in one persistent kernel: embedding → L layers → final norm → LM head
             L = _lib.lib()
             if getattr(st, "mega_scratch", None) is None:

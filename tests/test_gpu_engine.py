@@ -123,7 +123,7 @@ def test_public_generate_api_on_gpu():
     assert out.sequences.shape == (2, 12) and out.sequences.is_cuda
 
 
-@pytest.mark.parametrize("B", [1, 2, 4])
+@pytest.mark.parametrize("B", [1, 2, 4, 7, 8])
 def test_megakernel_step_matches_unfused_step(B):
     """The persistent whole-model decode kernel against the per-op kernels, several consecutive steps."""
     cfg = LLaMAConfig(vocab_size=1000, hidden_size=512, intermediate_size=1536, num_hidden_layers=3,

@@ -197,6 +197,28 @@ def test_flash_prefill(B, S, start, nh, nkv, pads):
     assert ((g - w).abs().max() / (w.abs().max() + 1e-6)).item() < 2e-2
 
 
+def test_flash_prefill_many_ctas_repeated():
+    """Thousands of CTAs, two per SM, launched back to back with cold caches: the barrier-phase discipline
+    between the softmax warps and the MMA warp must hold when tile loads are slow (a missing guard showed up
+    as an intermittent hang at batch 8)."""
+    B, S, nh, nkv, hd = 8, 1024, 16, 4, 128
+    q = rnd(B, S, nh, hd, seed=50).to(DEV)
+    kc, vc = rnd(B, nkv, S, hd, seed=51).to(DEV), rnd(B, nkv, S, hd, seed=52).to(DEV)
+    pad = torch.zeros(B, dtype=torch.int32, device=DEV)
+    flush = torch.empty(192 << 20, dtype=torch.uint8, device=DEV)
+    first = None
+    for it in range(25):
+        flush.zero_()
+        out = K.prefill_attn(q, kc, vc, 0, S, pad)
+        torch.cuda.synchronize()
+        if first is None:
+            first = out.clone()
+            want = K.prefill_attn_ref(q[:1].float().cpu(), kc[:1].float().cpu(), vc[:1].float().cpu(), 0, S, pad[:1].cpu())
+            assert ((first[:1].float().cpu() - want).abs().max() / want.abs().max()).item() < 2e-2
+        else:
+            assert torch.equal(out, first)
+
+
 @pytest.mark.parametrize("ramp", [0.02, -0.02])
 def test_flash_prefill_growing_and_shrinking_scores(ramp):
     """Scores whose row maximum keeps rising along the keys (ramp > 0) force the in-TMEM rescale of O over
