@@ -660,7 +660,7 @@ static int mega_ring_stages(int M, int H, int F, int nh, int nkv, int hd, size_t
   const size_t xin_bytes = (size_t)M * ((kmax + MG_KS - 1) / MG_KS * MG_KS) * 2;      // whole k-stages (zero padded)
   const size_t attn_bytes = (size_t)(MG_CONSUMERS * 2) * G * (MG_HD + 2) * sizeof(float);
   const size_t fixed = 1024 + xin_bytes + attn_bytes + 64;
-  const size_t budget = 225 * 1024;
+  const size_t budget = 220 * 1024;      // 227 KB per CTA minus ~5 KB of static shared memory (reduction buffers)
   if (fixed_out) *fixed_out = fixed;
   if (fixed + 4 * (MG_STAGE_BYTES + 16) > budget) return 0;
   int stages = (int)((budget - fixed) / (MG_STAGE_BYTES + 16));
