@@ -82,7 +82,7 @@ struct MegaParams {
   int* tickets;                      // [M·nkv]
   unsigned int* bar_counter;         // monotonically increasing arrival counter
   unsigned int* bar_gen;             // barriers completed by previous launches
-  int T, max_pos, splits, stages;
+  int T, max_pos, splits, stages, l2_ahead;
   unsigned long long* trace;         // optional [2][L][16] globaltimer stamps (block 0 and the last block)
 };
 
@@ -505,6 +505,9 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ float red[M][MG_CONSUMERS];
   __shared__ __align__(16) float s_acc[2][MG_CONSUMERS][MG_MMA_MAX_M][8];
+  __shared__ volatile int s_idle_flag;          // consumers → producer: "no GEMV is consuming the ring right now"
+  volatile int* s_idle = &s_idle_flag;
+  if (threadIdx.x == 0) s_idle_flag = 0;
   __shared__ int s_last;
   constexpr int NG = MG_CONSUMERS * (32 / (MG_HD / 8));
 
@@ -536,19 +539,39 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   if (warp == 0) {
     // ===================================================== producer: the whole model's weights, in order
     if (lane == 0) {
-      MegaCursor ld;
+      // `ld` feeds the ring.  While the consumers are NOT consuming (attention, merge and the barriers around
+      // them: s_idle is set) and the ring is full, `pf` walks up to p.l2_ahead stages further down the same
+      // sequence and only asks the L2 to fetch them, so HBM keeps streaming through the ~12 µs per layer in
+      // which no GEMV runs.  (Prefetching all the time was measured twice and loses: it queues in front of
+      // the loads the GEMV is waiting for.)
+      MegaCursor ld, pf;
       ld.init(p, qdim);
+      pf = ld;
+      int ahead = 0;                       // stages between ld and pf
       while (!ld.done) {
-        // try_wait suspends the thread in hardware until the slot frees or a time-out elapses; a busy
-        // test_wait loop here steals issue slots from the two consumer warps that share this scheduler
-        // (measured: 122 vs 108 µs per layer)
-        if (tc::mbar_try_wait(c.bars + 8u * (c.stages + c.stage), c.phase ^ 1)) {
+        const uint32_t empty = c.bars + 8u * (c.stages + c.stage);
+        bool ready;
+        if (p.l2_ahead > 0 && *s_idle != 0 && !pf.done && ahead < p.l2_ahead) {
+          ready = tc::mbar_test_wait(empty, c.phase ^ 1);
+          if (!ready) {
+            if (ahead >= c.stages) tc::tma_prefetch_3d(&tm.m[pf.map()], 0, pf.row(), pf.ks * (MG_KS / 64));
+            pf.next(p, qdim);
+            ++ahead;
+          }
+        } else {
+          // try_wait suspends the thread in hardware until the slot frees or a time-out elapses; a busy
+          // test_wait loop here steals issue slots from the two consumer warps that share this scheduler
+          // (measured: 122 vs 108 µs per layer)
+          ready = tc::mbar_try_wait(empty, c.phase ^ 1);
+        }
+        if (ready) {
           const uint32_t full = c.bars + 8u * c.stage;
           tc::mbar_expect_tx(full, MG_STAGE_BYTES);
           tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.row(), ld.ks * (MG_KS / 64),
                           tc::EVICT_FIRST);
           if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
           ld.next(p, qdim);
+          if (ahead > 0) --ahead; else pf = ld;
         }
       }
     }
@@ -585,6 +608,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     mg_stamp(p, l, 2);
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 3);
+    if (threadIdx.x == 32) *s_idle = 1;
     // ---- attention
     {
       const int items = M * p.nkv * p.splits;
@@ -604,6 +628,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     // ---- wo + residual
     MG_STAGE(p.attn, qdim, nullptr);
     mg_stamp(p, l, 6);
+    if (threadIdx.x == 32) *s_idle = 0;
     c.ar_epoch = ar_base + 2 * l + 1;
     MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x);
     if (p.ar.tp > 1) mg_ar_finish<M>(p, c, ar_base + 2 * l + 1, p.H);
@@ -735,6 +760,11 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
     if (cap >= 4 && cap < stages) stages = cap;
   }
   p.stages = stages;
+  {
+    // measured on one box, ms/token: 0 → 2.92, 8 → 2.875, 16 → 2.871, 32 → 2.905, 64 → 2.906
+    static const int ahead = [] { const char* e = getenv("JLLAMA_MEGA_L2_AHEAD"); return e ? atoi(e) : 16; }();
+    p.l2_ahead = ahead;
+  }
   const size_t smem = fixed + (size_t)stages * (MG_STAGE_BYTES + 16);
 
   void (*kern)(const MegaTmaps, const MegaParams) = nullptr;
