@@ -181,6 +181,26 @@ def main() -> None:
         if i > 0:
             prefill_ms.append(max_over_ranks(e0.elapsed_time(e1)))
     prefill_best = min(prefill_ms)
+    # the fused sequence-parallel chain (all-gather→GEMM / GEMM→reduce-scatter over peer memory), timed for the
+    # record next to the default path (tcgen05 GEMM + NCCL all-reduce), whichever of the two is the default
+    prefill_alt = None
+    if world > 1 and (B * P) % (128 * world) == 0:
+        was = eng.sequence_parallel_prefill
+        eng.sequence_parallel_prefill = not was
+        alt = []
+        for i in range(1 + args.prefill_reps):
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            eng.prepare(st, ids_dev, None, 0)
+            e1.record()
+            torch.cuda.synchronize()
+            if i > 0:
+                alt.append(max_over_ranks(e0.elapsed_time(e1)))
+        eng.sequence_parallel_prefill = was
+        eng.prepare(st, ids_dev, None, 0)
+        prefill_alt = {"path": "fused sequence-parallel" if not was else "GEMM + NCCL all-reduce",
+                       "ms": round(min(alt), 3), "tokens_per_sec": round(B * P / (min(alt) / 1e3), 1)}
 
     # ---------------------------------------------------------------- device-timed decode steps
     stream = llama.stream(prompt, mask, max_gen_len=max_len - P, temperature=0.0, top_p=1.0)
@@ -272,7 +292,10 @@ def main() -> None:
             "p50_ms_per_token": round(ms_per_step, 4),
             "hbm_roofline_frac_of_measured": round((weight_bytes / (ms_per_step / 1e3)) / (hbm * 1e9), 4),
             "prefill": {"tokens_per_sec": round(B * P / (prefill_best / 1e3), 1), "ms": round(prefill_best, 3),
-                        "prompt_len": P, "includes": "embedding..lm_head(last token) of the prompt"},
+                        "prompt_len": P, "includes": "embedding..lm_head(last token) of the prompt",
+                        "path": ("single GPU" if world == 1 else
+                                 "fused sequence-parallel" if eng.sequence_parallel_prefill else "GEMM + NCCL all-reduce"),
+                        "other_path": prefill_alt},
             "e2e": {"value": round(B * args.steps / (e2e_ms / 1e3), 2), "unit": "tokens/s",
                     "h2d_bytes_per_step": stream2.h2d_bytes, "d2h_bytes_per_step": stream2.d2h_bytes,
                     "api": "LLaMA.stream(...).step(feed)"},

@@ -48,6 +48,7 @@ struct GemmParams {
   unsigned int* gather_counters;     // [a_blocks], monotonically increasing
   unsigned int gather_target;        // value counters reach when this call's copies of a row block are done
   int ready_epoch, tp, rank, mloc, gather_parts;
+  bool gather_pushed;                // rows are pushed into the A buffer by their owners; nothing to copy here
 };
 
 enum { COMM_NONE = 0, COMM_GATHER = 1, COMM_SCATTER = 2 };
@@ -104,6 +105,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // ===================================================== TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
+      uint32_t seen = 0;                                   // sources whose "rows pushed" flag was already observed
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         const int b_blk = t / p.a_blocks;
         int a_blk = t % p.a_blocks;
@@ -111,8 +113,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         if constexpr (COMM == COMM_GATHER) {
           // local rows first: remote row blocks arrive over NVLink while these tiles compute
           a_blk = (a_blk + p.rank * (p.mloc / GEMM_BM)) % p.a_blocks;
-          a_is_local = (a_blk * GEMM_BM) / p.mloc == p.rank;
-          if (a_is_local) {
+          a_is_local = (a_blk * GEMM_BM) / p.mloc == p.rank && !p.gather_pushed;
+          if (p.gather_pushed) {
+            // the row owners push their rows into this rank's A buffer (jl_rs_reduce); wait for the owner's flag
+            const int src = (a_blk * GEMM_BM) / p.mloc;
+            if (!((seen >> src) & 1u)) { wait_flag(p.ready_flags + src, p.ready_epoch, p.rank, src, 5); seen |= 1u << src; }
+          } else if (a_is_local) {
             // this rank's own rows are read in place from its shard (no copy); it must be final
             wait_flag(p.ready_flags + p.rank, p.ready_epoch, p.rank, p.rank, 5);
           } else {
@@ -164,7 +170,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const int per_rb = GEMM_BM * K16;                          // chunks per 128-row block
       const int per_part = (per_rb + p.gather_parts - 1) / p.gather_parts;
       const int local_blocks = p.mloc / GEMM_BM;
-      const int n_items = (p.a_blocks - local_blocks) * p.gather_parts;          // remote row blocks only
+      const int n_items = p.gather_pushed ? 0 : (p.a_blocks - local_blocks) * p.gather_parts;   // remote row blocks only
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int part = item % p.gather_parts;
         // k-th remote row block in the order the tiles will want them (the blocks after this rank's own)
@@ -349,8 +355,10 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
   if (grid > num_sms) grid = num_sms;
   CUtensorMap tl = ta;                          // local-shard map (COMM_GATHER only; otherwise a copy of A's)
   if constexpr (COMM == COMM_GATHER) {
-    rc = make_tmap_2d_bf16(&tl, p.gather_src[p.rank], p.mloc, K, K, GEMM_BM);
-    if (rc) return rc;
+    if (!p.gather_pushed) {
+      rc = make_tmap_2d_bf16(&tl, p.gather_src[p.rank], p.mloc, K, K, GEMM_BM);
+      if (rc) return rc;
+    }
   }
   JL_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), smem, stream, ta, tb, tl, p));
   return JL_OK;
@@ -419,7 +427,8 @@ extern "C" JL_API int jl_ag_gemm(void* const* peer_shards, void* a_full, const v
   p.out = out; p.K = K; p.ldo = mode == EPI_SWIGLU ? N / 2 : N;
   p.Ra = M; p.Rb = N; p.hint_a = tc::EVICT_LAST; p.hint_b = tc::EVICT_NORMAL;
   p.tp = tp; p.rank = rank; p.mloc = M / tp;
-  for (int i = 0; i < tp; ++i) p.gather_src[i] = peer_shards[i];
+  p.gather_pushed = peer_shards == nullptr;       // rows arrive by push (jl_rs_reduce): only the flags are waited for
+  for (int i = 0; i < tp; ++i) p.gather_src[i] = peer_shards ? peer_shards[i] : nullptr;
   p.gather_dst = a_full; p.ready_flags = ready_flags; p.ready_epoch = ready_epoch;
   p.gather_counters = (unsigned int*)counters;
   const int a_blocks = M / GEMM_BM;

@@ -122,6 +122,11 @@ class B200Engine:
         self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
         self.warned_slow_prefill = False
         self._mega_fit_cache: Dict[int, bool] = {}
+        # Prefill at tp > 1.  Measured on 8xB200, LLaMA-3 8B, 2048 tokens (ms): fused sequence-parallel chain
+        # (rows pushed by their owners, tiles scattered from the GEMM epilogue) 18.0 / 15.3 at tp = 2 / 8, the
+        # earlier pull-gather 17.3 / 17.9, tcgen05 GEMM + NCCL all-reduce (NVLS in-switch reduction) 16.7 / 13.0.
+        # The fastest path is the default; JLLAMA_SP=1 selects the fused chain (tested in tests/tp_worker.py).
+        self.sequence_parallel_prefill = os.environ.get("JLLAMA_SP", "0") == "1"
         self.use_megakernel = use_megakernel and self.hd == 128 \
             and config.hidden_size % 256 == 0 and (config.intermediate_size // self.tp) % 256 == 0 \
             and (self.nh * self.hd) % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
@@ -372,7 +377,7 @@ class B200Engine:
         if position_ids is not None:
             positions = position_ids.to(torch.int32).reshape(-1).contiguous()
         if (self.tp > 1 and S > 1 and last_only and with_head and positions is None and self.hd == 128
-                and (B * S) % (128 * self.tp) == 0 and not os.environ.get("JLLAMA_NO_SP")):
+                and (B * S) % (128 * self.tp) == 0 and self.sequence_parallel_prefill):
             # sequence-parallel prefill: all-gather→GEMM and GEMM→reduce-scatter fused over NVLink peer memory
             logits = self._prefill_sp(input_ids, cache, B, S)
             cache.set_index(cache.index + S)

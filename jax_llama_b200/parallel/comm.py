@@ -45,7 +45,7 @@ _EXTRA_SIGNATURES = {
     "jl_gemm_rs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                              C.c_void_p]),
     "jl_rs_reduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
-                               C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
+                               C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
                                C.c_void_p]),
 }
 
@@ -232,9 +232,9 @@ class PeerComm:
 class SPState:
     """Buffers and epochs of the sequence-parallel prefill chain for one (tokens, hidden) shape.
 
-    rs_buf  [tp][mloc][H] bf16   receive buffer for the partial tiles peers scatter out of their GEMM epilogues
-    xn[2]   [mloc][H] bf16       this rank's normalised shard, read by peers' in-kernel all-gather (double-buffered)
-    a_full  [M][kmax] bf16       local destination of the gather
+    rs_buf     [tp][mloc][H] bf16   receive buffer for the partial tiles peers scatter out of their GEMM epilogues
+    a_full[2]  [M][H] bf16          the gathered, normalised activations (peer-visible, double-buffered by parity):
+                                    every row owner pushes its rows into every rank's copy from `rs_reduce`
     """
 
     def __init__(self, comm: PeerComm, M: int, H: int, kmax: int):
@@ -244,11 +244,12 @@ class SPState:
         self.comm, self.M, self.H, self.mloc = comm, M, H, M // tp
         dev = comm.device
         self.rs_local, self.rs_ptrs = comm.symmetric_alloc(tp * self.mloc * H * 2)
-        xn0, self.xn_ptrs0 = comm.symmetric_alloc(self.mloc * H * 2)
-        xn1, self.xn_ptrs1 = comm.symmetric_alloc(self.mloc * H * 2)
-        self.xn_local = (xn0, xn1)
-        self.xn_ptrs = (self.xn_ptrs0, self.xn_ptrs1)
-        self.a_full = torch.empty((M, kmax), dtype=torch.bfloat16, device=dev)
+        if kmax != H:
+            raise ValueError("the gathered operand of both column-parallel GEMMs is the hidden state (kmax == H)")
+        a0, ptrs0 = comm.symmetric_alloc(M * H * 2)
+        a1, ptrs1 = comm.symmetric_alloc(M * H * 2)
+        self.a_local = (a0, a1)
+        self.a_ptrs = (ptrs0, ptrs1)
         self.counters = torch.zeros(M // 128, dtype=torch.int32, device=dev)
         self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
         self.gemm_off = comm.flag_block(("sp_gemm",), MAX_TP)
@@ -265,21 +266,24 @@ class SPState:
         self.ep["ready"] += 1
         if n_src:
             self.ep["gemm"] += 1
-        _lib.check(_L().jl_rs_reduce(x_shard.data_ptr(), self.rs_local, norm_w.data_ptr(), self.xn_local[self.parity],
-                                     self.mloc, self.H, n_src, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off, self.ready_off,
+        _lib.check(_L().jl_rs_reduce(x_shard.data_ptr(), self.rs_local, norm_w.data_ptr(), self.a_ptrs[self.parity],
+                                     cm.rank * self.mloc, self.mloc, self.H, n_src, cm.tp, cm.rank, cm.flag_ptrs,
+                                     self.gemm_off, self.ready_off,
                                      self.ep["gemm"], self.ep["ready"], self.ticket.data_ptr(), float(eps), K._stream()),
                    "jl_rs_reduce")
 
     def ag_gemm(self, w: torch.Tensor, mode: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """y = all_gather(normalised shards) · wᵀ; the gather happens inside the GEMM kernel."""
+        """y = all_gather(normalised shards) · wᵀ: the rows were pushed by their owners (`rs_reduce`); the GEMM's TMA
+        producer waits for an owner's flag before the first tile that needs its rows."""
         cm = self.comm
         n, k = w.shape
         odim = n // 2 if mode == K.SWIGLU else n
         if out is None:
             out = torch.empty((self.M, odim), dtype=torch.bfloat16, device=cm.device)
-        a_full = self.a_full if k == self.a_full.shape[1] else self.a_full.view(-1)[:self.M * k].view(self.M, k)
+        if k != self.H:
+            raise ValueError(f"ag_gemm expects K == hidden size ({self.H}), got {k}")
         flags_local = cm._own_flags + 4 * self.ready_off
-        _lib.check(_L().jl_ag_gemm(self.xn_ptrs[self.parity], a_full.data_ptr(), w.data_ptr(), out.data_ptr(), self.M, n,
+        _lib.check(_L().jl_ag_gemm(None, self.a_local[self.parity], w.data_ptr(), out.data_ptr(), self.M, n,
                                    k, mode, cm.tp, cm.rank, flags_local, self.ep["ready"], self.counters.data_ptr(),
                                    K.num_sms(cm.device), K._stream()), "jl_ag_gemm")
         return out
@@ -294,6 +298,7 @@ class SPState:
     def read_rows(self, rows: torch.Tensor) -> torch.Tensor:
         """Rows (global token indices owned by this rank) of the current normalised shard as a torch tensor."""
         out = torch.empty((self.mloc, self.H), dtype=torch.bfloat16, device=self.comm.device)
-        _lib.check(_L().jl_memcpy_d2d(out.data_ptr(), self.xn_local[self.parity], out.numel() * 2, K._stream()),
+        src = self.a_local[self.parity] + self.comm.rank * self.mloc * self.H * 2
+        _lib.check(_L().jl_memcpy_d2d(out.data_ptr(), src, out.numel() * 2, K._stream()),
                    "jl_memcpy_d2d")
         return out[rows - self.comm.rank * self.mloc]

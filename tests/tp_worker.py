@@ -91,14 +91,14 @@ def main():
     ids_sp = torch.randint(3, cfg.vocab_size, (2, S), generator=torch.Generator().manual_seed(9))
     assert (2 * S) % (128 * world) == 0
     want_sp = ref.forward(full32, cfg, ids_sp).logits[:, -1]
+    eng.sequence_parallel_prefill = True                # the fused chain is opt-in (JLLAMA_SP=1): see engine.py
     for _ in range(2):                                  # twice: epochs, parities and counters must re-arm
         cache = eng.new_cache(2, S + 8)
         got_sp = eng.forward(ids_sp.to(dev), cache=cache, last_only=True).logits[:, 0]
         assert got_sp.shape == want_sp.shape and rel(got_sp, want_sp) < 3e-2, rel(got_sp, want_sp)
-    os.environ["JLLAMA_NO_SP"] = "1"                    # same prefill through the NCCL-all-reduce path
+    eng.sequence_parallel_prefill = False               # same prefill through the NCCL-all-reduce path
     cache2 = eng.new_cache(2, S + 8)
     got_nccl = eng.forward(ids_sp.to(dev), cache=cache2, last_only=True).logits[:, 0]
-    del os.environ["JLLAMA_NO_SP"]
     assert rel(got_sp, got_nccl) < 3e-2 and rel(cache.k, cache2.k) < 2e-2
     # ---- 4. flag / epoch protocol stress: ranks enter every collective at random, different times
     # (a device-side sleep of up to ~200 us per rank per call) for many back-to-back calls; payloads change
