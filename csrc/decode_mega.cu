@@ -732,8 +732,11 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   p.hmlp = (__nv_bfloat16*)hmlp; p.logits = logits; p.kc = (__nv_bfloat16*)k_cache; p.vc = (__nv_bfloat16*)v_cache;
   p.cos_t = cos_t; p.sin_t = sin_t; p.cache_len = cache_len; p.pad_left = pad_left;
   int splits = num_sms / (M * nkv);
-  if (splits < 1) splits = 1;
   if (splits > 64) splits = 64;
+  // a split shorter than one 128-key batch only adds partials to merge (tp = 8 has one KV head per rank:
+  // 148 candidate splits for a 2k context): cap by the cache capacity
+  if (splits > (T + 127) / 128) splits = (T + 127) / 128;
+  if (splits < 1) splits = 1;
   p.splits = splits;
   const size_t part_floats = (size_t)M * nh * splits * MG_HD;
   p.o_part = (float*)scratch;
