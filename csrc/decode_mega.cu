@@ -734,8 +734,9 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   int splits = num_sms / (M * nkv);
   if (splits > 64) splits = 64;
   // a split shorter than one 128-key batch only adds partials to merge (tp = 8 has one KV head per rank:
-  // 148 candidate splits for a 2k context): cap by the cache capacity
-  if (splits > (T + 127) / 128) splits = (T + 127) / 128;
+  // 148 candidate splits for a 2k context): cap by the cache capacity over one load batch
+  const int batch_keys = G <= 4 ? 128 : 64;           // keys one item handles per load batch (UNR x 64 in mg_attention_item)
+  if (splits > (T + batch_keys - 1) / batch_keys) splits = (T + batch_keys - 1) / batch_keys;
   if (splits < 1) splits = 1;
   p.splits = splits;
   const size_t part_floats = (size_t)M * nh * splits * MG_HD;
