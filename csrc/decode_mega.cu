@@ -83,6 +83,7 @@ struct MegaParams {
   unsigned int* bar_counter;         // monotonically increasing arrival counter
   unsigned int* bar_gen;             // barriers completed by previous launches
   int T, max_pos, splits, stages, l2_ahead;
+  int w2_passes;                     // 2: w2 is walked in two K ranges (batch rows of its full input do not fit in smem)
   unsigned long long* trace;         // optional [2][L][16] globaltimer stamps (block 0 and the last block)
 };
 
@@ -139,13 +140,15 @@ __device__ __forceinline__ void mg_push_partial(const MegaCtx& c, int m, int row
 // ------------------------------------------------------------------------------------ producer side
 // Position in the model-wide weight stream of one CTA: (layer, op, row group, k stage).
 struct MegaCursor {
-  int l, op, g, g1, ks, n_ks, row_base;
-  bool done;
+  int l, op, g, g0, g1, ks, ks_end, n_ks, row_base;
+  bool done, second_pass;
   __device__ __forceinline__ bool step_op() {
     if (op == 4) { done = true; return false; }
     if (++op == 4) { op = 0; ++l; }
     return true;
   }
+  // TWO: the kernel instance supports the two-pass w2 walk (batch > 4); otherwise the plain sequence is compiled
+  template <bool TWO>
   __device__ __forceinline__ void load_op(const MegaParams& p, int qdim) {
     for (;;) {
       if (l >= p.L && op != 4) op = 4;                   // all layers streamed → LM head
@@ -158,18 +161,37 @@ struct MegaCursor {
         default: N = p.V; K = p.H; row_base = 0; break;
       }
       mg_range(N / MG_GROUP, g, g1);
+      g0 = g;
       ks = 0;
       n_ks = (K + MG_KS - 1) / MG_KS;
+      // two-pass w2: every row group over the first K range, then every row group over the second
+      second_pass = false;
+      ks_end = (TWO && op == 3 && p.w2_passes == 2) ? (n_ks + 1) / 2 : n_ks;
       if (g < g1) return;
       if (!step_op()) return;                            // empty range for this CTA: skip the op
     }
   }
-  __device__ __forceinline__ void init(const MegaParams& p, int qdim) { l = 0; op = 0; done = false; load_op(p, qdim); }
+  template <bool TWO>
+  __device__ __forceinline__ void init(const MegaParams& p, int qdim) { l = 0; op = 0; done = false; load_op<TWO>(p, qdim); }
+  template <bool TWO>
   __device__ __forceinline__ void next(const MegaParams& p, int qdim) {
-    if (++ks < n_ks) return;
-    ks = 0;
-    if (++g < g1) return;
-    if (step_op()) load_op(p, qdim);
+    if constexpr (TWO) {
+      if (++ks < ks_end) return;
+      ks = second_pass ? (n_ks + 1) / 2 : 0;
+      if (++g < g1) return;
+      if (ks_end < n_ks) {                               // first pass of a two-pass op done: same rows, second K range
+        second_pass = true;
+        g = g0;
+        ks = ks_end;
+        ks_end = n_ks;
+        return;
+      }
+    } else {
+      if (++ks < n_ks) return;
+      ks = 0;
+      if (++g < g1) return;
+    }
+    if (step_op()) load_op<TWO>(p, qdim);
   }
   __device__ __forceinline__ int map() const { return op; }
   __device__ __forceinline__ int row() const { return row_base + g * MG_GROUP; }
@@ -505,6 +527,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ float red[M][MG_CONSUMERS];
   __shared__ __align__(16) float s_acc[2][MG_CONSUMERS][MG_MMA_MAX_M][8];
+  __shared__ float s_carry[M > 4 ? M : 1][64];         // two-pass w2: sums of the first K range (this CTA's rows)
   __shared__ volatile int s_idle_flag;          // consumers → producer: "no GEMV is consuming the ring right now"
   volatile int* s_idle = &s_idle_flag;
   if (threadIdx.x == 0) s_idle_flag = 0;
@@ -545,7 +568,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
       // which no GEMV runs.  (Prefetching all the time was measured twice and loses: it queues in front of
       // the loads the GEMV is waiting for.)
       MegaCursor ld, pf;
-      ld.init(p, qdim);
+      ld.template init<(M > 4)>(p, qdim);
       pf = ld;
       int ahead = 0;                       // stages between ld and pf
       while (!ld.done) {
@@ -555,7 +578,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
           ready = tc::mbar_test_wait(empty, c.phase ^ 1);
           if (!ready) {
             if (ahead >= c.stages) tc::tma_prefetch_3d(&tm.m[pf.map()], 0, pf.row(), pf.ks * (MG_KS / 64));
-            pf.next(p, qdim);
+            pf.template next<(M > 4)>(p, qdim);
             ++ahead;
           }
         } else {
@@ -570,7 +593,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
           tc::tma_load_3d(c.ring + c.stage * MG_STAGE_BYTES, &tm.m[ld.map()], full, 0, ld.row(), ld.ks * (MG_KS / 64),
                           tc::EVICT_FIRST);
           if (++c.stage == c.stages) { c.stage = 0; c.phase ^= 1; }
-          ld.next(p, qdim);
+          ld.template next<(M > 4)>(p, qdim);
           if (ahead > 0) --ahead; else pf = ld;
         }
       }
@@ -643,10 +666,25 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     mg_grid_barrier(p, gen_base, bar_idx);
     mg_stamp(p, l, 11);
     // ---- w2 + residual
-    MG_STAGE(p.hmlp, p.F, nullptr);
-    mg_stamp(p, l, 12);
-    c.ar_epoch = ar_base + 2 * l + 2;
-    MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x);
+    bool w2_done = false;
+    if constexpr (M > 4) {
+      if (p.w2_passes == 2) {
+        const int ka = ((p.F + MG_KS - 1) / MG_KS + 1) / 2 * MG_KS;       // first K range: whole k-stages
+        mg_stage_input_mma<M>(c, p.hmlp, ka, nullptr, p.eps, red, p.F);
+        mg_stamp(p, l, 12);
+        c.ar_epoch = ar_base + 2 * l + 2;
+        mg_gemv_mma<M, MG_RESIDUAL, 1>(c, p.H, ka, p.x, p.x, s_acc, s_carry);
+        mg_stage_input_mma<M>(c, p.hmlp + ka, p.F - ka, nullptr, p.eps, red, p.F);
+        mg_gemv_mma<M, MG_RESIDUAL, 2>(c, p.H, p.F - ka, p.x, p.x, s_acc, s_carry);
+        w2_done = true;
+      }
+    }
+    if (!w2_done) {
+      MG_STAGE(p.hmlp, p.F, nullptr);
+      mg_stamp(p, l, 12);
+      c.ar_epoch = ar_base + 2 * l + 2;
+      MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x);
+    }
     if (p.ar.tp > 1) mg_ar_finish<M>(p, c, ar_base + 2 * l + 2, p.H);
     mg_stamp(p, l, 13);
     mg_grid_barrier(p, gen_base, bar_idx);
@@ -679,9 +717,11 @@ extern "C" JL_API size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, in
 
 // Shared-memory plan: the staged activations (M rows of the widest GEMV input, whole k-stages), the attention
 // scratch and whatever is left for the weight ring.  Returns the ring depth (< 4: the configuration does not fit).
-static int mega_ring_stages(int M, int H, int F, int nh, int nkv, int hd, size_t* fixed_out) {
+static int mega_ring_stages(int M, int H, int F, int nh, int nkv, int hd, size_t* fixed_out, int w2_passes = 1) {
   const int G = nkv > 0 ? nh / nkv : 1;
-  const int kmax = (H > F ? H : F) > nh * hd ? (H > F ? H : F) : nh * hd;
+  int fw = F;                                            // widest K range of w2 that is staged at once
+  if (w2_passes == 2) fw = ((F + MG_KS - 1) / MG_KS + 1) / 2 * MG_KS;
+  const int kmax = (H > fw ? H : fw) > nh * hd ? (H > fw ? H : fw) : nh * hd;
   const size_t xin_bytes = (size_t)M * ((kmax + MG_KS - 1) / MG_KS * MG_KS) * 2;      // whole k-stages (zero padded)
   const size_t attn_bytes = (size_t)(MG_CONSUMERS * 2) * G * (MG_HD + 2) * sizeof(float);
   const size_t fixed = 1024 + xin_bytes + attn_bytes + 64;
@@ -692,9 +732,18 @@ static int mega_ring_stages(int M, int H, int F, int nh, int nkv, int hd, size_t
   return stages > 12 ? 12 : stages;
 }
 // ring depth jl_decode_mega would use for this shape, 0 when the batch does not fit (use the per-op path then)
+// 1 or 2 K passes for w2: two when the batch is > 4, one pass does not fit, and the CTA's rows fit the carry buffer
+static int mega_w2_passes(int M, int H, int F, int nh, int nkv, int hd, int num_sms) {
+  const char* force = getenv("JLLAMA_MEGA_W2_PASSES");       // tests: force the two-pass walk at small shapes
+  const bool rows_ok = ((H / MG_GROUP + num_sms - 1) / num_sms) * MG_GROUP <= 64 && F > MG_KS;
+  if (M <= 4 || !rows_ok) return 1;
+  if (force && atoi(force) == 2) return 2;
+  if (mega_ring_stages(M, H, F, nh, nkv, hd, nullptr, 1) >= 4) return 1;
+  return mega_ring_stages(M, H, F, nh, nkv, hd, nullptr, 2) >= 4 ? 2 : 1;
+}
 extern "C" JL_API int jl_decode_mega_stages(int M, int H, int F, int nh, int nkv, int hd) {
   if (M < 1 || M > 8 || hd != MG_HD || nkv <= 0 || nh % nkv) return 0;
-  return mega_ring_stages(M, H, F, nh, nkv, hd, nullptr);
+  return mega_ring_stages(M, H, F, nh, nkv, hd, nullptr, mega_w2_passes(M, H, F, nh, nkv, hd, 148));
 }
 
 // One decode step of the whole model for M <= 8 rows.  Weight pointers are the per-op stacks [L·N, K].
@@ -757,7 +806,8 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   p.trace = g_mega_trace;
 
   size_t fixed = 0;
-  int stages = mega_ring_stages(M, H, F, nh, nkv, hd, &fixed);
+  p.w2_passes = mega_w2_passes(M, H, F, nh, nkv, hd, num_sms);
+  int stages = mega_ring_stages(M, H, F, nh, nkv, hd, &fixed, p.w2_passes);
   JL_CHECK_ARG(stages >= 4, "jl_decode_mega: M=%d, F=%d leave no room for the weight ring", M, F);
   {
     static const int cap = [] { const char* e = getenv("JLLAMA_MEGA_STAGES"); return e ? atoi(e) : 0; }();   // A/B: ring depth

@@ -45,9 +45,12 @@ __device__ __forceinline__ int mg_xperm_word(int m, int n_ks, int k) {
 // stage [M, K] activations (optional RMSNorm) into the permuted layout; positions k >= K are zero
 template <int M>
 __device__ __forceinline__ void mg_stage_input_mma(MegaCtx& c, const __nv_bfloat16* src, int K,
-                                                   const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS]) {
+                                                   const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS],
+                                                   int ld = 0) {
+  // `ld` = row pitch of src in elements when only a K-range [src, src + K) of wider rows is staged (two-pass w2)
   const int ct = threadIdx.x - 32, lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
   const int K8 = K >> 3, n_ks = (K + MG_KS - 1) / MG_KS;
+  const int LD8 = ld > 0 ? ld >> 3 : K8;
   uint32_t* xw = reinterpret_cast<uint32_t*>(c.xin);
   float ss[M];
 #pragma unroll
@@ -55,7 +58,7 @@ __device__ __forceinline__ void mg_stage_input_mma(MegaCtx& c, const __nv_bfloat
   for (int i = ct; i < n_ks * (MG_KS / 8); i += MG_CT) {
 #pragma unroll
     for (int m = 0; m < M; ++m) {
-      const uint4 a = i < K8 ? ldcg16(src + ((size_t)m * K8 + i) * 8) : make_uint4(0, 0, 0, 0);
+      const uint4 a = i < K8 ? ldcg16(src + ((size_t)m * LD8 + i) * 8) : make_uint4(0, 0, 0, 0);
       const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
       const int base = mg_xperm_word(m, n_ks, i * 8);
 #pragma unroll
@@ -97,9 +100,12 @@ __device__ __forceinline__ void mg_stage_input_mma(MegaCtx& c, const __nv_bfloat
   mg_consumer_bar();
 }
 
-template <int M, int MODE>
+// CARRY (two-pass GEMV over K, used when M rows of the full input do not fit in shared memory): 1 = this call
+// covers the first K range and parks its sums in `carry` ([M][64] floats, this CTA's rows); 2 = this call covers
+// the rest, adds the parked sums and runs the epilogue.  0 = ordinary single pass.
+template <int M, int MODE, int CARRY = 0>
 __device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, void* out, const __nv_bfloat16* residual,
-                                            float (*s_acc)[MG_CONSUMERS][MG_MMA_MAX_M][8]) {
+                                            float (*s_acc)[MG_CONSUMERS][MG_MMA_MAX_M][8], float (*carry)[64] = nullptr) {
   static_assert(M <= MG_MMA_MAX_M, "batch rows ride in the first 8 rows of the MMA M dimension");
   const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1, ct = threadIdx.x - 32;
   const int g = lane >> 2, t = lane & 3;                   // MMA fragment coordinates: batch row g, quad lane t
@@ -163,10 +169,13 @@ __device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, void* out,
 #pragma unroll
         for (int w = 0; w < MG_CONSUMERS; ++w) v += buf[w][m][n];
         const int row = grp * MG_GROUP + n;
-        if constexpr (MODE == MG_LOGITS) {
+        if constexpr (CARRY == 1) {
+          carry[m][(grp - g0) * MG_GROUP + n] = v;         // read back by this same thread in the second pass
+        } else if constexpr (MODE == MG_LOGITS) {
           reinterpret_cast<float*>(out)[(size_t)m * N + row] = v;
         } else {
           bool pushed = false;
+          if constexpr (CARRY == 2) v += carry[m][(grp - g0) * MG_GROUP + n];
           if constexpr (MODE == MG_RESIDUAL) {
             if (c.ar->tp > 1) { mg_push_partial<M>(c, m, row, N, v); pushed = true; }     // reduced in mg_ar_finish
             else v = __bfloat162float(__float2bfloat16(v)) + __bfloat162float(__ldcg(residual + (size_t)m * N + row));

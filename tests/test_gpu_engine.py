@@ -123,9 +123,12 @@ def test_public_generate_api_on_gpu():
     assert out.sequences.shape == (2, 12) and out.sequences.is_cuda
 
 
-@pytest.mark.parametrize("B", [1, 2, 4, 7, 8])
-def test_megakernel_step_matches_unfused_step(B):
+@pytest.mark.parametrize("B", [1, 2, 4, 7, 8, -6, -8])
+def test_megakernel_step_matches_unfused_step(B, monkeypatch):
     """The persistent whole-model decode kernel against the per-op kernels, several consecutive steps."""
+    if B < 0:          # batch > 4 with w2 walked in two K passes (what a wide FFN forces; forced here at a small shape)
+        monkeypatch.setenv("JLLAMA_MEGA_W2_PASSES", "2")
+        B = -B
     cfg = LLaMAConfig(vocab_size=1000, hidden_size=512, intermediate_size=1536, num_hidden_layers=3,
                       num_attention_heads=4, num_key_value_heads=2, max_sequence_length=256, initializer_range=0.05)
     tree = tree_to(ref.init_params(cfg, seed=2), dtype=torch.bfloat16, device="cuda")
