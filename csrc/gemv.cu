@@ -2,8 +2,9 @@
 // RMSNorm prologue and residual / SwiGLU epilogues.  Weight-streaming bound: every weight byte is read
 // from HBM exactly once per step with 16-byte non-allocating loads, 8 loads in flight per lane, and the
 // first batch is issued *before* griddepcontrol.wait so that under Programmatic Dependent Launch the
-// HBM stream of layer i+1 starts while layer i drains.  Tensor cores are pointless at M <= 4 (the
-// op is 1-4 FLOP/byte); M > 8 goes to the tcgen05 swap-AB kernel in gemm_tcgen05.cu.
+// HBM stream of layer i+1 starts while layer i drains.  This SIMT form is instruction-latency bound at
+// ~5-6 TB/s (profiles/README.md); the whole-step kernel (decode_mega_mma.cuh) does the same GEMV with ldmatrix +
+// mma.sync and reaches the HBM roofline.  M > 8 goes to the tcgen05 swap-AB kernel in gemm_tcgen05.cu.
 //
 // Covers the reference's wq/wk/wv (fused), wo, w1/w3 (fused, interleaved), w2 and lm_head at decode
 // (/root/reference/jax_llama/model.py:119-150,311-338,699-706).

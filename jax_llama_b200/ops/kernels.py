@@ -152,9 +152,10 @@ def _linear_ref(x, w, norm_w, eps, residual, mode, out_f32):
 def linear(x: torch.Tensor, w: torch.Tensor, *, norm_w: Optional[torch.Tensor] = None, eps: float = 1e-5,
            residual: Optional[torch.Tensor] = None, mode: int = PLAIN, out_f32: bool = False,
            out: Optional[torch.Tensor] = None, force: Optional[str] = None) -> torch.Tensor:
-    """y = f(x) Wᵀ with W [N, K].  Dispatch by token count: M ≤ 4 → TMA-streamed GEMV (RMSNorm fused; falls
-    back to the register-streaming GEMV when the activations do not fit next to the ring), otherwise the
-    tcgen05 GEMM (swap-AB up to M = 128).  `force` ∈ {"gemv_tma", "gemv", "gemm"} pins the kernel."""
+    """y = f(x) Wᵀ with W [N, K] for the per-op path (the whole-step decode kernel has its own GEMV).  Dispatch
+    by token count: M ≤ 4 → register-streaming GEMV with RMSNorm fused (JLLAMA_SMALL_M=gemv_tma selects the
+    TMA-ring GEMV, which falls back when the activations do not fit next to its ring), otherwise the tcgen05
+    GEMM (swap-AB up to M = 128).  `force` ∈ {"gemv_tma", "gemv", "gemm"} pins the kernel."""
     if not x.is_cuda:
         return _linear_ref(x, w, norm_w, eps, residual, mode, out_f32)
     _bf16c(x, "x"); _bf16c(w, "w")
