@@ -49,6 +49,13 @@ struct GemmParams {
   unsigned int gather_target;        // value counters reach when this call's copies of a row block are done
   int ready_epoch, tp, rank, mloc, gather_parts;
   bool gather_pushed;                // rows are pushed into the A buffer by their owners; nothing to copy here
+  // ---- split-K for swap-AB launches with fewer weight-row tiles than SMs (decode at batch 9..128: N = 4096
+  // gives 32 tiles, i.e. 22 % of the SMs streaming): each tile's K range is cut into `ksplit` work items, the
+  // fp32 partials meet in `ws` ([ksplit][tokens][features]) and the last item to arrive (ticket) sums them in
+  // split order — deterministic — and runs the epilogue.  ksplit == 1: off.
+  int ksplit;
+  float* ws;
+  int* tickets;                      // [tiles], zero between launches (the finishing item resets its ticket)
 };
 
 enum { COMM_NONE = 0, COMM_GATHER = 1, COMM_SCATTER = 2 };
@@ -82,6 +89,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
   const int num_tiles = p.a_blocks * p.b_blocks;
+  const int ksplit = SWAP ? p.ksplit : 1;
+  const int num_work = num_tiles * ksplit;              // (tile, K split) items; split-major so neighbours differ in tile
+  __shared__ int s_last_split;
 
   if (warp == 0 && lane == 0) {
     tc::prefetch_tensormap(&tmap_a);
@@ -106,7 +116,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       uint32_t seen = 0;                                   // sources whose "rows pushed" flag was already observed
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
+        const int t = wi % num_tiles, split = wi / num_tiles;
+        const int kb0 = split * num_kb / ksplit, kb1 = (split + 1) * num_kb / ksplit;
         const int b_blk = t / p.a_blocks;
         int a_blk = t % p.a_blocks;
         bool a_is_local = false;
@@ -129,7 +141,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           }
           asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores → TMA (async proxy) reads
         }
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
           tc::mbar_expect_tx(full_bar(stage), A_BYTES + B_BYTES);
@@ -144,19 +156,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // ===================================================== MMA issuer (single thread)
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0; int it = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x, ++it) {
+        const int split = wi / num_tiles;
+        const int kb0 = split * num_kb / ksplit, kb1 = (split + 1) * num_kb / ksplit;
         const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
         tc::mbar_wait(tempty_bar(as), aphase ^ 1);          // epilogue has drained this accumulator
         tc::fence_after_sync();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(full_bar(stage), phase);
           tc::fence_after_sync();
           const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
           const uint64_t da = tc::smem_desc_kmajor_sw128(sa), db = tc::smem_desc_kmajor_sw128(sb);
 #pragma unroll
           for (int k = 0; k < GEMM_BK / 16; ++k)            // +32 bytes per UMMA_K inside the swizzle span
-            tc::mma_ss(d_tmem, da + 2 * k, db + 2 * k, IDESC, (kb | k) != 0);
+            tc::mma_ss(d_tmem, da + 2 * k, db + 2 * k, IDESC, kb != kb0 || k != 0);
           tc::mma_commit(empty_bar(stage));                 // frees the smem slot when these MMAs retire
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
@@ -200,7 +214,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // ===================================================== epilogue: TMEM → registers → global
     const int quarter = warp & 3;                           // TMEM lanes [32·quarter, 32·quarter+32)
     int it = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+    for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x, ++it) {
+      const int t = wi % num_tiles, split = wi / num_tiles;
       const int b_blk = t / p.a_blocks;
       int a_blk = t % p.a_blocks;
       if constexpr (COMM == COMM_GATHER) a_blk = (a_blk + p.rank * (p.mloc / GEMM_BM)) % p.a_blocks;
@@ -210,6 +225,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const int ra = a_blk * GEMM_BM + quarter * 32 + lane;  // A-side row of this thread
       const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
       constexpr int CH = BN >= 32 ? 32 : 16;
+      // swap-AB epilogue of one (token, feature = this lane's weight row) value; whole warps call it together
+      auto swap_emit = [&](const int tok, float x) {
+        if constexpr (EPI == EPI_SWIGLU) {
+          // (gate, up) sit in adjacent lanes: even lane gets its neighbour's value
+          const float xb = __bfloat162float(__float2bfloat16(x));
+          const float up = __shfl_down_sync(0xffffffffu, xb, 1);
+          if ((lane & 1) == 0 && tok < p.Rb && ra + 1 < p.Ra)
+            reinterpret_cast<__nv_bfloat16*>(p.out)[(size_t)tok * p.ldo + ra / 2] = __float2bfloat16(silu(xb) * up);
+        } else if (tok < p.Rb && ra < p.Ra) {
+          if constexpr (OUT_F32) {
+            reinterpret_cast<float*>(p.out)[(size_t)tok * p.ldo + ra] = x;
+          } else {
+            if constexpr (EPI == EPI_RESIDUAL)
+              x = __bfloat162float(__float2bfloat16(x)) + __bfloat162float(p.residual[(size_t)tok * p.ldo + ra]);
+            reinterpret_cast<__nv_bfloat16*>(p.out)[(size_t)tok * p.ldo + ra] = __float2bfloat16(x);
+          }
+        }
+      };
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += CH) {
         uint32_t v[CH];
@@ -297,22 +330,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 #pragma unroll
           for (int j = 0; j < CH; ++j) {
             const int tok = cb0 + j;
-            float x = __uint_as_float(v[j]);
-            if constexpr (EPI == EPI_SWIGLU) {
-              // (gate, up) sit in adjacent lanes: even lane gets its neighbour's value
-              const float xb = __bfloat162float(__float2bfloat16(x));
-              const float up = __shfl_down_sync(0xffffffffu, xb, 1);
-              if ((lane & 1) == 0 && tok < p.Rb && ra + 1 < p.Ra)
-                reinterpret_cast<__nv_bfloat16*>(p.out)[(size_t)tok * p.ldo + ra / 2] =
-                    __float2bfloat16(silu(xb) * up);
-            } else if (tok < p.Rb && ra < p.Ra) {
-              if constexpr (OUT_F32) {
-                reinterpret_cast<float*>(p.out)[(size_t)tok * p.ldo + ra] = x;
-              } else {
-                if constexpr (EPI == EPI_RESIDUAL)
-                  x = __bfloat162float(__float2bfloat16(x)) + __bfloat162float(p.residual[(size_t)tok * p.ldo + ra]);
-                reinterpret_cast<__nv_bfloat16*>(p.out)[(size_t)tok * p.ldo + ra] = __float2bfloat16(x);
-              }
+            const float x = __uint_as_float(v[j]);
+            if (ksplit > 1) {
+              if (tok < p.Rb && ra < p.Ra) p.ws[((size_t)split * p.Rb + tok) * p.Ra + ra] = x;     // fp32 partial
+            } else {
+              swap_emit(tok, x);
             }
           }
         }
@@ -320,6 +342,38 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       tc::fence_before_sync();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(tempty_bar(as));
+      if constexpr (SWAP) {
+        if (ksplit > 1) {
+          // ---- split-K finish: the last of this tile's K splits to get here sums all partials and emits
+          __threadfence();
+          asm volatile("bar.sync 1, 128;" ::: "memory");                // the four epilogue warps
+          if (threadIdx.x == 128) s_last_split = atomicAdd(p.tickets + t, 1) == ksplit - 1;
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (s_last_split) {
+            __threadfence();
+            // 4 tokens x up to 16 splits of independent L2 loads in flight per thread (a token-at-a-time loop
+            // paid one L2 round trip per token: 45 us for 64 tokens)
+            const size_t split_stride = (size_t)p.Rb * p.Ra;
+#pragma unroll 1
+            for (int j0 = 0; j0 < BN; j0 += 4) {
+              float x[4] = {0.f, 0.f, 0.f, 0.f};
+              const float* src = p.ws + (size_t)(b_blk * BN + j0) * p.Ra + ra;
+#pragma unroll
+              for (int sp = 0; sp < 16; ++sp) {
+                if (sp < ksplit) {
+#pragma unroll
+                  for (int u = 0; u < 4; ++u)
+                    if (b_blk * BN + j0 + u < p.Rb && ra < p.Ra) x[u] += __ldcg(src + sp * split_stride + (size_t)u * p.Ra);
+                }
+              }
+#pragma unroll
+              for (int u = 0; u < 4; ++u) swap_emit(b_blk * BN + j0 + u, x[u]);
+            }
+            if (threadIdx.x == 128) p.tickets[t] = 0;
+          }
+          asm volatile("bar.sync 1, 128;" ::: "memory");                // s_last_split is reused by the next item
+        }
+      }
     }
   }
 
@@ -327,6 +381,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 2) tc::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// Caller-provided scratch for split-K (jl_gemm_set_workspace), one per device; none registered → no split-K
+struct SplitKWorkspace { float* ws; size_t ws_bytes; int* tickets; int n_tickets; };
+static SplitKWorkspace g_splitk[16] = {};
+static SplitKWorkspace splitk_workspace() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return SplitKWorkspace{};
+  return g_splitk[dev];
 }
 
 template <int BN, int EPI, bool SWAP, bool OUT_F32, int COMM = COMM_NONE>
@@ -352,6 +415,19 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
   auto kern = gemm_kernel<BN, EPI, SWAP, OUT_F32, COMM>;
   JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = p.a_blocks * p.b_blocks;
+  p.ksplit = 1;
+  if constexpr (SWAP && COMM == COMM_NONE) {
+    // few weight-row tiles (N <= ~9k at decode batch sizes): cut K so that (nearly) every SM streams weights
+    const SplitKWorkspace wsp = splitk_workspace();
+    // measured (8B decode, ms/step, split vs not): batch 16 5.10 vs 6.20, batch 32 6.44 vs 7.09, batch 64 9.29 vs 8.72
+    if (wsp.ws != nullptr && Rb <= 32 && grid * 2 <= num_sms && grid <= wsp.n_tickets) {
+      int ks = num_sms / grid;
+      if (ks > num_kb / 4) ks = num_kb / 4;               // at least 4 k-blocks (256 columns) per item
+      if (ks > 16) ks = 16;
+      while (ks > 1 && (size_t)ks * Rb * Ra * sizeof(float) > wsp.ws_bytes) --ks;
+      if (ks > 1) { p.ksplit = ks; p.ws = wsp.ws; p.tickets = wsp.tickets; grid *= ks; }
+    }
+  }
   if (grid > num_sms) grid = num_sms;
   CUtensorMap tl = ta;                          // local-shard map (COMM_GATHER only; otherwise a copy of A's)
   if constexpr (COMM == COMM_GATHER) {
@@ -388,6 +464,16 @@ static int dispatch_gemm(const void* x, const void* w, const GemmParams& p, int 
 }  // namespace jl
 
 using namespace jl;
+
+// Registers (or, with ws == NULL, removes) the split-K scratch of the CURRENT device: `ws` fp32 workspace of
+// ws_bytes, `tickets` n_tickets ints that must be zero.  The library keeps the pointers; the caller owns the memory.
+extern "C" JL_API int jl_gemm_set_workspace(void* ws, size_t ws_bytes, int* tickets, int n_tickets) {
+  int dev = 0;
+  JL_CUDA(cudaGetDevice(&dev));
+  JL_CHECK_ARG(dev >= 0 && dev < 16, "jl_gemm_set_workspace: device %d out of range", dev);
+  g_splitk[dev] = SplitKWorkspace{(float*)ws, ws ? ws_bytes : 0, tickets, ws ? n_tickets : 0};
+  return JL_OK;
+}
 
 extern "C" JL_API int jl_gemm(const void* x, const void* w, const void* residual, void* out, int M, int N, int K,
                        int mode, int out_f32, int num_sms, void* stream) {

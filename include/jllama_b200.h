@@ -61,6 +61,13 @@ int jl_gemv_tma(const void* x, const void* w, const void* norm_w, const void* re
  * SwiGLU needs N % 16 == 0. */
 int jl_gemm(const void* x, const void* w, const void* residual, void* out, int M, int N, int K, int mode,
             int out_f32, int num_sms, void* stream);
+/* Optional scratch for jl_gemm on the CURRENT device: with it, small-batch (M <= 128) launches that have fewer
+ * 128-row weight tiles than half the SMs (N = 4096: 32 tiles) split K over the idle SMs; partial sums meet in `ws`
+ * (fp32, ws_bytes) and the last split of a tile, found with `tickets` (n_tickets ints, zero on entry and between
+ * calls), adds them in split order and runs the epilogue — results do not depend on arrival order.  The caller
+ * owns both buffers and keeps them alive; ws == NULL unregisters.  Calls that share the scratch must be ordered
+ * on one stream. */
+int jl_gemm_set_workspace(void* ws, size_t ws_bytes, int* tickets, int n_tickets);
 
 /* model.py:194-198,263-288 at S=1 — split-KV GQA decode attention over [pad_left[b], *cache_len+n_new).
  * q [B,nh,hd] with batch pitch q_bstride elements (0 = dense; lets q live inside the fused qkv

@@ -122,6 +122,8 @@ class B200Engine:
         self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
         self.warned_slow_prefill = False
         self._mega_fit_cache: Dict[int, bool] = {}
+        if self.device.type == "cuda":
+            K.ensure_gemm_workspace(self.device)          # split-K scratch of the small-batch GEMMs (before any capture)
         # Prefill at tp > 1.  Measured on 8xB200, LLaMA-3 8B, 2048 tokens (ms): fused sequence-parallel chain
         # (rows pushed by their owners, tiles scattered from the GEMM epilogue) 18.0 / 15.3 at tp = 2 / 8, the
         # earlier pull-gather 17.3 / 17.9, tcgen05 GEMM + NCCL all-reduce (NVLS in-switch reduction) 16.7 / 13.0.

@@ -8,6 +8,7 @@ no native library raises.
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -17,7 +18,7 @@ from . import _lib
 
 PLAIN, RESIDUAL, SWIGLU = 0, 1, 2
 _NUM_SMS = {}
-_SMALL_M_PATH = __import__("os").environ.get("JLLAMA_SMALL_M", "gemv")    # measured faster in the graph-replayed step than "gemv_tma"
+_SMALL_M_PATH = os.environ.get("JLLAMA_SMALL_M", "gemv")    # measured faster in the graph-replayed step than "gemv_tma"
 
 
 def _stream() -> int:
@@ -29,6 +30,24 @@ def num_sms(device: Optional[torch.device] = None) -> int:
     if idx not in _NUM_SMS:
         _NUM_SMS[idx] = torch.cuda.get_device_properties(idx).multi_processor_count
     return _NUM_SMS[idx]
+
+
+_GEMM_WS: dict = {}
+
+
+def ensure_gemm_workspace(device: Optional[torch.device] = None, nbytes: int = 32 << 20) -> None:
+    """Give the library its split-K scratch for this device (fp32 partials + per-tile tickets).  Small-batch
+    GEMMs with few weight-row tiles (N = 4096 at batch 9..128) then spread their K range over all SMs.  Done once,
+    outside any stream capture (the engine calls it at construction); without it such GEMMs simply do not split."""
+    idx = torch.cuda.current_device() if device is None or device.index is None else device.index
+    if idx in _GEMM_WS or torch.cuda.is_current_stream_capturing() or os.environ.get("JLLAMA_NO_SPLITK") == "1":
+        return
+    with torch.cuda.device(idx):
+        ws = torch.empty(nbytes // 4, dtype=torch.float32, device=f"cuda:{idx}")
+        tickets = torch.zeros(2048, dtype=torch.int32, device=f"cuda:{idx}")
+        _lib.check(_lib.lib().jl_gemm_set_workspace(ws.data_ptr(), ws.numel() * 4, tickets.data_ptr(), tickets.numel()),
+                   "jl_gemm_set_workspace")
+    _GEMM_WS[idx] = (ws, tickets)
 
 
 def _p(t: Optional[torch.Tensor]) -> int:
@@ -185,6 +204,8 @@ def linear(x: torch.Tensor, w: torch.Tensor, *, norm_w: Optional[torch.Tensor] =
     elif path == "gemm":
         if norm_w is not None:
             x = rmsnorm(x.view(m, k), norm_w, eps)
+        if m <= 128:
+            ensure_gemm_workspace(x.device)
         _lib.check(L.jl_gemm(x.data_ptr(), w.data_ptr(), _p(residual), out.data_ptr(), m, n, k, mode,
                              int(out_f32), sms, _stream()), "jl_gemm")
     elif path != "gemv_tma":

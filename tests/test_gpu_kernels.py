@@ -144,6 +144,27 @@ def test_gemm_tcgen05(M, N, K_):
     assert rel_err(got32, want) < 2e-3
 
 
+@pytest.mark.parametrize("M,N,K_,mode", [(16, 4096, 14336, "residual"), (64, 4096, 4096, "plain"),
+                                         (9, 6144, 4096, "f32"), (100, 2048, 2048, "swiglu")])
+def test_gemm_small_batch_split_k(M, N, K_, mode):
+    """Few weight-row tiles → the K range is split over the idle SMs; partials are summed in split order by
+    the last arriving split (tickets re-arm themselves), so repeated calls agree bit for bit."""
+    x, w = rnd(M, K_, seed=60), rnd(N, K_, scale=0.03, seed=61)
+    xd, wd = x.to(DEV), w.to(DEV)
+    if mode == "residual":
+        res = rnd(M, N, seed=62)
+        want = K.linear(x, w, residual=res, mode=K.RESIDUAL)
+        outs = [K.linear(xd, wd, residual=res.to(DEV), mode=K.RESIDUAL, force="gemm") for _ in range(3)]
+    elif mode == "swiglu":
+        want = K.linear(x, w, mode=K.SWIGLU)
+        outs = [K.linear(xd, wd, mode=K.SWIGLU, force="gemm") for _ in range(3)]
+    else:
+        want = x.float() @ w.float().t()
+        outs = [K.linear(xd, wd, out_f32=(mode == "f32"), force="gemm") for _ in range(3)]
+    assert rel_err(outs[0], want) < 2e-2
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
+
+
 @pytest.mark.parametrize("M", [24, 384])
 def test_gemm_epilogues(M):
     N, K_ = 1024, 512
