@@ -44,3 +44,17 @@ def test_convert_cli_writes_rank_files(tmp_path):
 def test_setup_py_lists_the_package():
     r = subprocess.run([sys.executable, "setup.py", "--name", "--version"], cwd=ROOT, capture_output=True, text=True)
     assert r.returncode == 0 and "jax_llama_b200" in r.stdout
+
+
+def test_megakernel_fit_plan():
+    """Host-side shared-memory plan of the whole-step decode kernel (no GPU needed): which batches stay on it."""
+    from jax_llama_b200.ops import _lib
+    stages = _lib.lib().jl_decode_mega_stages
+    llama3_8b = (4096, 14336, 32, 8, 128)
+    assert stages(1, *llama3_8b) >= 8                       # deep weight ring at batch 1
+    assert stages(4, *llama3_8b) >= 4                       # single pass over w2 still fits
+    assert stages(8, *llama3_8b) >= 4                       # w2 walked in two K passes
+    assert stages(9, *llama3_8b) == 0                       # beyond the 8 batch rows of the MMA's first half
+    assert stages(1, 4096, 14336, 32, 8, 64) == 0           # head_dim 64 is not built
+    assert stages(4, 8192, 3584, 8, 1, 128) >= 4            # LLaMA-3 70B per-rank shape at tp = 8
+    assert stages(8, 8192, 3584, 8, 1, 128) == 0            # 8 rows of an 8192-wide input do not fit: per-op path
