@@ -542,7 +542,9 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   uint8_t* after = const_cast<uint8_t*>(c.ring_ptr) + p.stages * MG_STAGE_BYTES + 16 * p.stages;
   c.s_attn = reinterpret_cast<float*>(after);
   const int kmax = p.H > p.F ? p.H : p.F;
-  c.xin = reinterpret_cast<uint4*>(after + (size_t)NG * G * (MG_HD + 2) * sizeof(float));
+  // the staged GEMV input and the attention scratch are never live together (a GEMV ends before attention
+  // starts and is restaged after it), so they share one region sized for the larger of the two
+  c.xin = reinterpret_cast<uint4*>(after);
   (void)kmax;
   c.stage = 0; c.phase = 0;
   c.ar = &p.ar; c.ar_epoch = 0;
@@ -724,7 +726,7 @@ static int mega_ring_stages(int M, int H, int F, int nh, int nkv, int hd, size_t
   const int kmax = (H > fw ? H : fw) > nh * hd ? (H > fw ? H : fw) : nh * hd;
   const size_t xin_bytes = (size_t)M * ((kmax + MG_KS - 1) / MG_KS * MG_KS) * 2;      // whole k-stages (zero padded)
   const size_t attn_bytes = (size_t)(MG_CONSUMERS * 2) * G * (MG_HD + 2) * sizeof(float);
-  const size_t fixed = 1024 + xin_bytes + attn_bytes + 64;
+  const size_t fixed = 1024 + (xin_bytes > attn_bytes ? xin_bytes : attn_bytes) + 64;      // shared region (see kernel)
   const size_t budget = 220 * 1024;      // 227 KB per CTA minus ~5 KB of static shared memory (reduction buffers)
   if (fixed_out) *fixed_out = fixed;
   if (fixed + 4 * (MG_STAGE_BYTES + 16) > budget) return 0;

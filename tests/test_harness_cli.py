@@ -57,4 +57,4 @@ def test_megakernel_fit_plan():
     assert stages(9, *llama3_8b) == 0                       # beyond the 8 batch rows of the MMA's first half
     assert stages(1, 4096, 14336, 32, 8, 64) == 0           # head_dim 64 is not built
     assert stages(4, 8192, 3584, 8, 1, 128) >= 4            # LLaMA-3 70B per-rank shape at tp = 8
-    assert stages(8, 8192, 3584, 8, 1, 128) == 0            # 8 rows of an 8192-wide input do not fit: per-op path
+    assert stages(8, 8192, 3584, 8, 1, 128) >= 4            # fits because staging and attention scratch share a region
