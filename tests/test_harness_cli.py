@@ -58,3 +58,13 @@ def test_megakernel_fit_plan():
     assert stages(1, 4096, 14336, 32, 8, 64) == 0           # head_dim 64 is not built
     assert stages(4, 8192, 3584, 8, 1, 128) >= 4            # LLaMA-3 70B per-rank shape at tp = 8
     assert stages(8, 8192, 3584, 8, 1, 128) >= 4            # fits because staging and attention scratch share a region
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference` must exit 0 and print one JSON line: a measurement, or why there is none."""
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference"], capture_output=True,
+                       text=True, timeout=300, env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+    assert r.returncode == 0, r.stderr[-1000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and ("unavailable" in line or "value" in line)
