@@ -240,6 +240,16 @@ def write_meta_checkpoint(tree: Tree, config: LLaMAConfig, out_dir: str, mp: int
         json.dump(params, f)
 
 
+def test_intermediate_size(dim: int, ffn_dim_multiplier: Optional[float], multiple_of: int) -> int:
+    """The reference's name for the SwiGLU width formula (convert_weights.py:28-33); same as
+    `config.swiglu_intermediate_size`."""
+    from .config import swiglu_intermediate_size
+    return swiglu_intermediate_size(dim, ffn_dim_multiplier, multiple_of)
+
+
+test_intermediate_size.__test__ = False                  # a helper with a reference-given name, not a pytest test
+
+
 def main(argv: Optional[Sequence[str]] = None) -> int:
     """``python -m jax_llama_b200.convert_weights --ckpt_dir D --out_dir O [--tp N]`` — the command the
     reference's convert.sh calls but never shipped (/root/reference/convert.sh:10): Meta shards → the sharded

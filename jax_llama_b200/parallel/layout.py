@@ -56,6 +56,15 @@ class Mesh:
             return int(np.prod(list(self.shape.values())))
         return int(self.shape[axis])
 
+    # `with mesh:` makes it the ambient mesh, the way `with jax.sharding.Mesh(...)` does for the reference's
+    # `global_mesh_defined()` / `with_sharding_constraint` (partition.py:83-93)
+    def __enter__(self) -> "Mesh":
+        _MESH_STACK.append(self)
+        return self
+
+    def __exit__(self, *exc: Any) -> None:
+        _MESH_STACK.pop()
+
     def coords(self, rank: int) -> Dict[str, int]:
         """Row-major rank → per-axis coordinate (last axis fastest, like jax's device mesh)."""
         out: Dict[str, int] = {}
@@ -63,6 +72,18 @@ class Mesh:
             out[name] = rank % self.shape[name]
             rank //= self.shape[name]
         return out
+
+
+_MESH_STACK: List["Mesh"] = []
+
+
+def global_mesh_defined() -> bool:
+    """True inside a `with Mesh(...):` block (partition.py:83-86; the reference asks jax for its ambient mesh)."""
+    return bool(_MESH_STACK)
+
+
+def current_mesh() -> Optional["Mesh"]:
+    return _MESH_STACK[-1] if _MESH_STACK else None
 
 
 # --------------------------------------------------------------------------- rule tables
@@ -97,6 +118,9 @@ def partition_rules(fsdp: bool = False) -> List[Rule]:
 
 
 # --------------------------------------------------------------------------- tree helpers
+_get_partition_rules_llama = partition_rules        # the reference's (private) name, partition.py:43
+
+
 def flatten_tree(tree: Mapping[str, Any], prefix: Path = ()) -> Dict[Path, Any]:
     flat: Dict[Path, Any] = {}
     for k, v in tree.items():

@@ -88,3 +88,21 @@ def test_constraint_wrappers():
     with pytest.raises(ValueError):
         with_named_sharding_constraint(x, Mesh({"dp": 3, "mp": 1}), P("dp", None))
     assert with_sharding_constraint(x, P("dp", None)) is x
+
+
+def test_reference_named_helpers():
+    """Names a user of the reference may import: ambient-mesh query, private rule table, width formula."""
+    from jax_llama_b200.convert_weights import test_intermediate_size
+    from jax_llama_b200.parallel.layout import (Mesh, _get_partition_rules_llama, current_mesh, global_mesh_defined,
+                                                partition_rules)
+    assert not global_mesh_defined() and current_mesh() is None
+    with Mesh({"dp": 1, "mp": 4}) as m:
+        assert global_mesh_defined() and current_mesh() is m
+        with Mesh({"dp": 2, "mp": 2}) as inner:
+            assert current_mesh() is inner
+        assert current_mesh() is m
+    assert not global_mesh_defined()
+    assert _get_partition_rules_llama(fsdp=True) == partition_rules(fsdp=True)
+    assert test_intermediate_size(4096, 1.3, 1024) == 14336          # LLaMA-3 8B
+    assert test_intermediate_size(8192, 1.3, 4096) == 28672          # LLaMA-3 70B
+    assert test_intermediate_size(4096, None, 256) == 11008          # LLaMA-2 7B
