@@ -35,6 +35,11 @@ class LLaMA:
     tokenizer: Any
     mesh: Optional[Mesh] = None
 
+    def replace(self, **updates: Any) -> "LLaMA":
+        """A copy with some fields swapped (what `flax.struct.PyTreeNode.replace` gave the reference's LLaMA)."""
+        import dataclasses
+        return dataclasses.replace(self, **updates)
+
     def generate(self, tokens: torch.Tensor, attention_mask: torch.Tensor, max_gen_len: int,
                  temperature: float = 0.8, top_p: float = 0.95, top_k: Optional[int] = 50,
                  seed: int = 0) -> torch.Tensor:

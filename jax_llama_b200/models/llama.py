@@ -22,6 +22,7 @@ import torch
 from ..config import LLaMAConfig
 from ..ops.sampling import sample
 from . import reference as ref
+from .modules import LLaMAForCausalLMModule, LLaMAModule
 from .reference import KVCache, ModelOutput
 
 logger = logging.getLogger(__name__)
@@ -197,12 +198,14 @@ class LLaMAModel(LLaMAPreTrainedModel):
     """Backbone without the LM head: returns `last_hidden_state` (model.py:680-681)."""
 
     with_head = False
+    module_class = LLaMAModule            # the reference's `module_class = FlaxLLaMAModule`
 
 
 class LLaMAForCausalLM(LLaMAPreTrainedModel):
     """Backbone + LM head + generation (model.py:745-772)."""
 
     with_head = True
+    module_class = LLaMAForCausalLMModule
 
     # ------------------------------------------------------------------ generation hooks
     def prepare_inputs_for_generation(self, input_ids: torch.Tensor, max_length: int,

@@ -87,3 +87,10 @@ def test_generate_from_str_left_pad_equals_single(spm_model):
     assert tokens[1, 0] == tok.eos_id and mask[1, 0] == 0 and mask[0].all()
     out = gen.generate(tokens, mask, 4, temperature=0.0)
     assert out.shape == (2, tokens.shape[1] + 4)
+
+
+def test_llama_replace_returns_modified_copy():
+    from jax_llama_b200 import LLaMA
+    a = LLaMA(params={"x": 1}, model=None, tokenizer="tok")
+    b = a.replace(tokenizer="other")
+    assert b.tokenizer == "other" and a.tokenizer == "tok" and b.params is a.params

@@ -171,3 +171,35 @@ def test_save_and_from_pretrained(tmp_path, tree):
     m2 = LLaMAForCausalLM.from_pretrained(str(tmp_path))
     ids = torch.randint(0, 256, (1, 5))
     assert torch.equal(m2(ids).logits, m(ids, params=tree).logits) and m2.config == CFG
+
+
+def test_module_style_wrappers(tree, hf):
+    """The reference's Flax module names, driven with `.apply({"params": subtree}, ...)` like jax_test.py does."""
+    from jax_llama_b200.models import (FlaxLLaMAAttention, FlaxLLaMABlock, FlaxLLaMABlockCollection,
+                                       FlaxLLaMAForCausalLMModule, FlaxLLaMAMLP, FlaxLLaMAModule, RMSNorm)
+    layer = tree["transformer"]["h"]["0"]
+    x = torch.randn(2, 10, 32, generator=torch.Generator().manual_seed(4))
+    f = ref._freqs_table(CFG, "cpu")[torch.arange(10)[None].expand(2, 10)]
+    norm = RMSNorm(32, eps=CFG.rms_norm_eps)
+    assert torch.equal(norm.apply({"params": layer["attention_norm"]}, x),
+                       ref.rms_norm(x, layer["attention_norm"]["kernel"], CFG.rms_norm_eps))
+    assert norm.init()["params"]["kernel"].shape == (32,)
+    got = FlaxLLaMAAttention(CFG).apply({"params": layer["attention"]}, x)[0]
+    assert torch.equal(got, ref.attention(layer, CFG, x, f, None, None, 0)[0])
+    assert torch.equal(FlaxLLaMAMLP(CFG).apply({"params": layer["feed_forward"]}, x), ref.feed_forward(layer, x))
+    out, probs = FlaxLLaMABlock(CFG).apply({"params": layer}, x, output_attentions=True)
+    want, wprobs = ref.block(layer, CFG, x, f, None, None, 0, True)
+    assert torch.equal(out, want) and torch.equal(probs, wprobs)
+    ids = torch.randint(0, 256, (2, 12), generator=torch.Generator().manual_seed(6))
+    full = ref.forward(tree, CFG, ids, output_hidden_states=True)
+    h0 = tree["transformer"]["wte"]["embedding"][ids]
+    stack = FlaxLLaMABlockCollection(CFG).apply({"params": tree["transformer"]["h"]}, h0, output_hidden_states=True)
+    assert torch.allclose(ref.rms_norm(stack[0], tree["transformer"]["ln_f"]["kernel"], CFG.rms_norm_eps),
+                          full.last_hidden_state, atol=1e-6) and len(stack[1]) == CFG.num_hidden_layers
+    back = FlaxLLaMAModule(CFG).apply({"params": tree["transformer"]}, ids)
+    assert back.logits is None and torch.equal(back.last_hidden_state, full.last_hidden_state)
+    lm = FlaxLLaMAForCausalLMModule(CFG).apply({"params": tree}, ids)
+    assert torch.equal(lm.logits, full.logits)
+    with torch.no_grad():
+        assert (lm.logits - hf(ids).logits).abs().max() < 1e-4
+    assert LLaMAForCausalLM.module_class is FlaxLLaMAForCausalLMModule and LLaMAModel.module_class is FlaxLLaMAModule
