@@ -53,3 +53,24 @@ def test_invalid():
         LLaMAConfig(hidden_size=100, num_attention_heads=3)
     with pytest.raises(ValueError):
         LLaMAConfig(num_attention_heads=32, num_key_value_heads=5)
+
+
+def test_reference_module_paths_resolve():
+    """`from jax_llama.<module> import <name>` keeps working with the package name swapped."""
+    import importlib
+    wanted = {
+        "model": ["FlaxLLaMAForCausalLM", "FlaxLLaMAModel", "FlaxLLaMAPreTrainedModel", "RMSNorm", "FlaxLLaMAAttention",
+                  "FlaxLLaMAMLP", "FlaxLLaMABlock", "FlaxLLaMABlockCollection", "FlaxLLaMAModule",
+                  "FlaxLLaMAForCausalLMModule", "precompute_freqs_cis", "apply_rotary_emb", "repeat_kv"],
+        "config": ["LLaMAConfig"],
+        "convert_weights": ["ModelArgs", "config_from_params", "convert_llama_weights", "test_intermediate_size"],
+        "generation": ["LLaMA"],
+        "partition": ["get_partition_spec", "get_llama_param_partition_spec", "global_mesh_defined",
+                      "with_sharding_constraint", "with_named_sharding_constraint", "_get_partition_rules_llama"],
+        "llama2_tokenizer": ["Tokenizer"],
+        "llama3_tokenizer": ["Tokenizer", "ChatFormat", "Message", "Dialog", "Role"],
+    }
+    for mod, names in wanted.items():
+        m = importlib.import_module(f"jax_llama_b200.{mod}")
+        for n in names:
+            assert hasattr(m, n), f"jax_llama_b200.{mod}.{n}"
