@@ -68,3 +68,21 @@ def test_bench_reference_arm_contract():
     assert r.returncode == 0, r.stderr[-1000:]
     line = json.loads(r.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and ("unavailable" in line or "value" in line)
+
+
+def test_example_cli_end_to_end_on_cpu(tmp_path, spm_model):
+    """The reference's jax_example.py flow: Meta checkpoint directory + tokenizer.model → printed completions."""
+    import sentencepiece as spm
+    vocab = spm.SentencePieceProcessor(model_file=spm_model).vocab_size()
+    cfg = LLaMAConfig(vocab_size=vocab, hidden_size=64, intermediate_size=256, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2, max_sequence_length=64)
+    write_meta_checkpoint(ref.init_params(cfg, seed=0), cfg, str(tmp_path / "ckpt"), mp=2, dtype=torch.float32,
+                          multiple_of=256)
+    for entry in ("jax_example.py", os.path.join("examples", "example.py")):
+        r = subprocess.run([sys.executable, os.path.join(ROOT, entry), "--ckpt_dir", str(tmp_path / "ckpt"),
+                            "--tokenizer_path", spm_model, "--device", "cpu", "--max_gen_len", "4", "--temperature", "0",
+                            "--prompt", "the capital of germany is", "--prompt", "hello world"],
+                           capture_output=True, text=True, timeout=300, env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+        assert r.returncode == 0, r.stderr[-1500:]
+        assert r.stdout.count("==================================") == 2
+        assert "the capital of germany is" in r.stdout.lower()
