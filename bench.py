@@ -147,7 +147,6 @@ def main() -> None:
     eng = B200Engine.random_init(cfg, dev, seed=0, use_cuda_graph=not args.no_graph, **kw)
     model = LLaMAForCausalLM(cfg, _do_init=False)
     params = {"engine": eng}                              # handle understood by LLaMAForCausalLM._engine_for
-    model._engines[id(params)] = eng
     tok = SyntheticTokenizer(cfg.vocab_size, cfg.bos_token_id, -1)      # eos never fires: fixed-length runs
     llama = LLaMA(params, model, tok)
 

@@ -196,6 +196,13 @@ int jl_rs_reduce(void* x, const void* partials, const void* norm_w, void* const*
                  int H, int n_src, int tp, int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off,
                  int gemm_epoch, int ready_epoch, int* ticket, float eps, void* stream);
 
+/* NVLS self-test over a multicast mapping of a symmetric buffer (parallel/symm.py): `mc` is the multicast
+ * address.  op 0: out[i] = sum over ranks of fp32 buf[i] (multimem.ld_reduce); 1: 8-byte packets {src[i], tag}
+ * stored into every rank's copy (multimem.st); 2: every copy += src[i] (multimem.red); 3 / 4: the bf16 forms of
+ * 0 / (plain store); 5: u32 arrival counter at buf[0] += 1 with release semantics.  The reference's collectives
+ * are NCCL calls emitted by XLA for partition.py:62-78; these instructions are what the fused kernels use instead. */
+int jl_nvls_selftest(void* mc, const void* src, void* out, int n, int op, unsigned int tag, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -373,8 +373,13 @@ class B200Engine:
             cache = self.new_cache(B, S)
         if cache.index + S > cache.capacity:
             raise ValueError(f"KV cache overflow: {cache.index}+{S} > capacity {cache.capacity}")
-        if attention_mask is not None and cache.index == 0:
-            cache.pad_left.copy_(self.pad_left_from_mask(attention_mask, B, S, self.device))
+        if cache.index == 0:
+            # a cache object is reused across requests (`prepare`): the left-pad counts of the previous request
+            # must never leak into a request that comes without a mask
+            if attention_mask is None:
+                cache.pad_left.zero_()
+            else:
+                cache.pad_left.copy_(self.pad_left_from_mask(attention_mask, B, S, self.device))
         positions = None
         if position_ids is not None:
             positions = position_ids.to(torch.int32).reshape(-1).contiguous()

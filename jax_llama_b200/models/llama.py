@@ -15,6 +15,7 @@ from __future__ import annotations
 import logging
 import os
 from dataclasses import dataclass
+import weakref
 from typing import Any, Dict, Optional, Tuple, Union
 
 import torch
@@ -79,7 +80,7 @@ class LLaMAPreTrainedModel:
         self.seed = seed
         self.input_shape = input_shape
         self._params: Optional[Tree] = None
-        self._engines: Dict[int, Any] = {}
+        self._engines: Dict[int, Tuple[Any, Any, Any]] = {}      # id(tree) → (weakref(leaf), version stamp, engine)
         self.runtime_kwargs = kwargs            # tp / max_batch / kernel toggles, forwarded to the engine
         if _do_init:
             self._params = self.init_weights(seed, input_shape, device=device)
@@ -105,12 +106,28 @@ class LLaMAPreTrainedModel:
 
     # ------------------------------------------------------------------ backends
     def _engine_for(self, params: Tree) -> Any:
-        """B200 engine bound to `params` (built once per parameter tree)."""
+        """B200 engine bound to `params` (built once per parameter tree).
+
+        The cache entry is validated against the tree it was built from: a weak reference to the tree's
+        embedding tensor plus the in-place version counters of all leaves.  A tree that was freed (its id may be
+        reused by a new dict) or modified in place therefore gets a fresh engine, and entries of dead trees are
+        dropped.  A dict of the form ``{"engine": B200Engine}`` is a handle to an engine built elsewhere
+        (``B200Engine.random_init`` in the benchmarks)."""
+        pre = params.get("engine") if isinstance(params, dict) else None
+        if pre is not None and not isinstance(pre, (dict, torch.Tensor)):
+            return pre
+        leaves = list(_flatten(params).values())
+        stamp = (len(leaves), tuple(int(t._version) for t in leaves))
+        for k in [k for k, (ref_, _, _) in self._engines.items() if ref_() is None]:
+            del self._engines[k]                                   # trees that no longer exist
         key = id(params)
-        if key not in self._engines:
-            from .engine import B200Engine
-            self._engines[key] = B200Engine.from_tree(self.config, params, **self.runtime_kwargs)
-        return self._engines[key]
+        hit = self._engines.get(key)
+        if hit is not None and hit[0]() is leaves[0] and hit[1] == stamp:
+            return hit[2]
+        from .engine import B200Engine
+        eng = B200Engine.from_tree(self.config, params, **self.runtime_kwargs)
+        self._engines[key] = (weakref.ref(leaves[0]), stamp, eng)
+        return eng
 
     def _use_engine(self, params: Tree, output_attentions: bool, output_hidden_states: bool) -> bool:
         if _tree_device(params).type != "cuda":

@@ -115,6 +115,40 @@ def test_generate_eos_and_sampling_on_device():
     assert torch.equal(a, b) and not torch.equal(a, c)
 
 
+def test_left_pad_counts_do_not_leak_into_the_next_request():
+    """generate(mask with left padding) followed by generate(no mask) on the same (B, max_length) reuses the
+    cached KV object: the second request must run with zero left padding (reference: every call of
+    /root/reference/jax_llama/model.py:748-767 builds its positions from that call's mask alone)."""
+    cfg, tree, tree32 = make("gqa128")
+    eng = B200Engine.from_tree(cfg, tree_to(tree, device="cuda"))
+    ids = torch.randint(3, cfg.vocab_size, (2, 10), generator=torch.Generator().manual_seed(11)).cuda()
+    mask = torch.ones(2, 10, dtype=torch.int32, device="cuda")
+    mask[1, :5] = 0
+    eng.generate(ids, mask, max_length=18, eos_token_id=-7, pad_token_id=0)
+    got = eng.generate(ids, None, max_length=18, eos_token_id=-7, pad_token_id=0)
+    fresh = B200Engine.from_tree(cfg, tree_to(tree, device="cuda")).generate(ids, None, max_length=18, eos_token_id=-7,
+                                                                             pad_token_id=0)
+    assert torch.equal(got, fresh)
+    logits = ref.forward(tree32, cfg, got.cpu()).logits
+    for t in range(10, 18):
+        row = logits[:, t - 1]
+        chosen = row.gather(-1, got[:, t:t + 1].cpu())[:, 0]
+        assert ((row.max(-1).values - chosen) < 3e-2 * row.abs().max()).all(), t
+
+
+def test_engine_cache_follows_the_parameter_tree():
+    """A tree modified in place gets a new engine; the same tree gets the cached one."""
+    cfg, tree, _ = make("gqa128")
+    model = LLaMAForCausalLM(cfg, _do_init=False)
+    gp = tree_to(tree, device="cuda")
+    e1 = model._engine_for(gp)
+    assert model._engine_for(gp) is e1
+    gp["transformer"]["ln_f"]["kernel"].mul_(2.0)
+    e2 = model._engine_for(gp)
+    assert e2 is not e1
+    assert torch.equal(e2.final_norm.float(), gp["transformer"]["ln_f"]["kernel"].float())
+
+
 def test_public_generate_api_on_gpu():
     cfg, tree, tree32 = make("gqa128")
     model = LLaMAForCausalLM(cfg, _do_init=False)
