@@ -100,6 +100,78 @@ class SyntheticTokenizer:
         return self.n_words
 
 
+def tp_check(args, cfg, eng, dev, rank: int, world: int) -> dict:
+    """Correctness of the tensor-parallel engine, measured before the timed region and printed in the JSON line
+    (the reference trusts its sharded model only after /root/reference/jax_test.py:427-522 compared logits and
+    greedy generations over all GPUs).  The single-GPU engine built from the same seed is the same model
+    (`B200Engine.random_init` slices full matrices), so on every rank we compare
+      * last-token prefill logits, TP vs single GPU (max error relative to the largest logit);
+      * 16 greedy tokens, TP vs single GPU, free-running and teacher-forced (each TP token must be the single-GPU
+        arg-max or within bf16 noise of it — random-init logits are nearly flat, so exact ties do occur);
+      * that all ranks produced identical tokens;
+      * the fused sequence-parallel prefill against the all-reduce prefill.
+    Models that do not fit twice in one GPU (70B) are checked on a 4-layer model of the same shapes."""
+    import copy
+
+    import torch
+    import torch.distributed as dist
+
+    from jax_llama_b200.models.engine import B200Engine
+
+    ccfg, eng_tp, own = cfg, eng, False
+    if cfg.num_hidden_layers * cfg.hidden_size * cfg.intermediate_size * 6 > 40e9:      # > ~40 GB of bf16 weights
+        ccfg = copy.deepcopy(cfg)
+        ccfg.num_hidden_layers = 4
+        eng_tp = B200Engine.random_init(ccfg, dev, seed=0, tp=world, rank=rank, comm=eng.comm)
+        own = True
+    full = B200Engine.random_init(ccfg, dev, seed=0)
+    P, n_new, B = 256, 16, 1
+    g = torch.Generator().manual_seed(4321)
+    ids = torch.randint(0, ccfg.vocab_size, (B, P), generator=g).to(dev)
+    want = full.forward(ids, last_only=True).logits[:, 0].float()
+    got = eng_tp.forward(ids, last_only=True).logits[:, 0].float()
+    scale = float(want.abs().max())
+    err = float((got - want).abs().max()) / (scale + 1e-9)
+    seq_tp = eng_tp.generate(ids, None, max_length=P + n_new, eos_token_id=-1)
+    seq_1 = full.generate(ids, None, max_length=P + n_new, eos_token_id=-1)
+    equal = bool(torch.equal(seq_tp, seq_1))
+    # teacher-forced: the single-GPU engine scores the TP engine's tokens
+    forced = full.forward(seq_tp[:, :-1], last_only=False).logits.float()
+    ok_forced = True
+    for t in range(P, P + n_new):
+        row = forced[:, t - 1]
+        chosen = row.gather(-1, seq_tp[:, t:t + 1])[:, 0]
+        ok_forced &= bool(((row.max(-1).values - chosen) <= 2e-2 * row.abs().max()).all())
+    gathered = [torch.empty_like(seq_tp) for _ in range(world)]
+    dist.all_gather(gathered, seq_tp)
+    agree = all(bool(torch.equal(gathered[0], t)) for t in gathered)
+    out = {"layers": ccfg.num_hidden_layers, "prompt_len": P, "new_tokens": n_new,
+           "logits_max_rel_err": round(err, 5), "greedy_tokens_equal": equal,
+           "greedy_tokens_teacher_forced_ok": ok_forced, "ranks_agree": agree}
+    # fused sequence-parallel prefill vs the all-reduce prefill (same engine)
+    if P % (128 * world) == 0 and hasattr(eng_tp, "prefill_paths"):
+        outs = {}
+        for path in eng_tp.prefill_paths():
+            eng_tp.set_prefill_path(path)
+            outs[path] = eng_tp.forward(ids, last_only=True).logits[:, 0].float()
+        names = sorted(outs)
+        if len(names) == 2:
+            out["sp_vs_allreduce_prefill_max_rel_err"] = round(
+                float((outs[names[0]] - outs[names[1]]).abs().max()) / (scale + 1e-9), 5)
+        eng_tp.set_prefill_path(None)
+    flags = torch.tensor([int(equal), int(ok_forced), int(agree)], device=dev)
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)                 # the line reports what held on EVERY rank
+    out["greedy_tokens_equal"], out["greedy_tokens_teacher_forced_ok"], out["ranks_agree"] = (bool(int(x)) for x in flags)
+    e = torch.tensor([err], device=dev)
+    dist.all_reduce(e, op=dist.ReduceOp.MAX)
+    out["logits_max_rel_err"] = round(float(e.item()), 5)
+    del full
+    if own:
+        del eng_tp
+    torch.cuda.empty_cache()
+    return out
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -112,6 +184,7 @@ def main() -> None:
     ap.add_argument("--prefill-reps", type=int, default=3)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-baseline", action="store_true", help="skip the same-box PyTorch (cuBLAS + SDPA + NCCL) arm")
+    ap.add_argument("--no-tp-check", action="store_true", help="skip the pre-run TP-vs-single-GPU correctness check")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
@@ -145,6 +218,9 @@ def main() -> None:
     if world > 1:
         kw = dict(tp=world, rank=rank)
     eng = B200Engine.random_init(cfg, dev, seed=0, use_cuda_graph=not args.no_graph, **kw)
+    check = None
+    if world > 1 and not args.no_tp_check:
+        check = tp_check(args, cfg, eng, dev, rank, world)
     model = LLaMAForCausalLM(cfg, _do_init=False)
     params = {"engine": eng}                              # handle understood by LLaMAForCausalLM._engine_for
     tok = SyntheticTokenizer(cfg.vocab_size, cfg.bos_token_id, -1)      # eos never fires: fixed-length runs
@@ -298,7 +374,7 @@ def main() -> None:
             "e2e": {"value": round(B * args.steps / (e2e_ms / 1e3), 2), "unit": "tokens/s",
                     "h2d_bytes_per_step": stream2.h2d_bytes, "d2h_bytes_per_step": stream2.d2h_bytes,
                     "api": "LLaMA.stream(...).step(feed)"},
-            "gpu_launches": int(gpu_launches), "clocks": clocks,
+            "gpu_launches": int(gpu_launches), "clocks": clocks, "tp_check": check,
             "same_box_library_baseline": baseline,
             "speedup_vs_library_baseline": (round(baseline["ms_per_step"] / ms_per_step, 3)
                                             if baseline and "ms_per_step" in baseline else None),

@@ -7,14 +7,38 @@
 //
 //   * warp 0 is a TMA producer that streams every weight matrix of the model, layer after layer, through a
 //     shared-memory ring: one 16 KB request per stage ([16 k-blocks][8 rows][128 B], 128-byte swizzle).  It
-//     depends on nothing but free ring slots, so it runs ahead across op boundaries: while the consumers sit in
-//     a grid barrier or do attention, the next op's weights are already landing.
+//     depends on nothing but free ring slots, so it runs ahead across op boundaries: while the consumers poll
+//     for their inputs or do attention, the next op's weights are already landing.
 //   * warps 1..8 are consumers: RMSNorm + tensor-core GEMV (ldmatrix + mma.sync, see decode_mega_mma.cuh),
 //     residual / SwiGLU epilogues, RoPE + KV append + split-KV GQA attention (one (batch, kv-head, split) item
-//     per CTA, merge spread over the grid), final norm + LM head.
-//   * ops are separated by a grid-wide barrier (monotonic atomic counter, acquire spin with a watchdog);
-//     activations cross CTAs through L2 (ld.global.cg), never through stale L1 lines.
+//     per CTA, merge spread over the grid), final norm + LM head with a running arg-max.
 //   * rows of each GEMV are cut into 148 contiguous, near-equal ranges (±1 group of 8 rows).
+//
+// DATA-FLOW SYNCHRONISATION (round 2).  The first version separated the ops with 5-6 grid-wide barriers per
+// layer plus two all-reduce waits; the %globaltimer trace put ≈ 12 of 44 µs per layer into them at TP=4, which
+// is why 8 GPUs bought only 2.07x one GPU.  Now there is NO grid barrier.  Every activation that crosses CTAs
+// travels as an 8-byte TAGGED PACKET {payload, tag}: the producer's plain store is data and flag at once (an
+// aligned 8-byte store is single-copy atomic), and a consumer polls exactly the packets it is about to use until
+// their tag equals the tag of this (step, layer, op).  No fence, no counter, no second round trip; a CTA waits
+// only for the data it needs.  Tags grow monotonically over the life of the engine (gen * 2L + 2l + {1,2}), so
+// buffers are never cleared and a stale packet can never match.
+//   - residual stream: each CTA OWNS the rows of x that its `wo` / `w2` row range produces and keeps them in
+//     shared memory for the whole step; the epilogue adds, rounds to bf16 and publishes {bf16 pair, tag} packets
+//     that every CTA's next staging pass polls (x never exists as a plain global array);
+//   - qkv, attention partials, merged attention output and the SwiGLU output travel the same way;
+//   - tensor parallelism: the row-parallel epilogues push their fp32 partials {value, tag} to every rank with ONE
+//     `multimem.st` on the NVLS multicast address of the packet buffer (the NVSwitch replicates it; without
+//     multicast: one unicast store per peer); the owner CTA of a row sums the tp packets in rank order
+//     (bit-identical on all ranks), adds its residual slice and publishes the local x packets.  The wait for the
+//     peers' packets is the only cross-GPU synchronisation of the all-reduce;
+//   - the LM head keeps a running (max, argmax) per CTA and publishes one candidate per CTA and batch row to every
+//     rank (same packet mechanism); `jl_mega_select` merges grid x tp candidates and does the sequence
+//     bookkeeping: a greedy decode step is 2 launches at any tp, and the fp32 [M, V] logits are written only when
+//     the caller asks for them.
+// WAR safety of the single-buffered packet arrays follows from the dependency chain (a CTA can only produce the
+// packets of op k+1 after it has consumed ALL packets of op k, and every later overwrite of op k's buffer is
+// ordered behind such a chain); the cross-GPU buffers and the residual packets alternate by tag parity.  Every
+// poll has a watchdog that names block / kind / tag and traps.
 //
 // History (all measured on B200, LLaMA-3 8B, batch 1, ms per token): SIMT consumers with one weight row per
 // warp 3.69 → one 16 KB TMA request per stage 3.64 → activations in registers 3.18-3.39 (box dependent; ncu:
@@ -27,10 +51,12 @@
 // Weights of all layers are stacked per op ([L·N, K]) so five tensor maps describe the whole model.
 // Math is identical to the unfused kernels (gemv.cu, decode_attn_fused.cu); the tests compare the two.
 // Reference: the body of HF Flax `_sample`'s while-loop that /root/reference/jax_llama/generation.py:28-41
-// runs as one compiled XLA program — this is the hand-written equivalent.
+// runs as one compiled XLA program — this is the hand-written equivalent; the all-reduces are the ones GSPMD
+// inserts for /root/reference/jax_llama/partition.py:67,70.
 #include <stdlib.h>
 
 #include "jllama_b200.h"
+#include "nvls.cuh"
 #include "tcgen05.cuh"
 
 namespace jl {
@@ -43,18 +69,20 @@ constexpr int MG_KS = 1024;                        // K elements per stage
 constexpr int MG_STAGE_BYTES = MG_GROUP * MG_KS * 2;   // 16 KB
 constexpr int MG_HD = 128;
 constexpr int MG_KPI = 4;
+constexpr int MG_PART = MG_HD + 2;                 // packets of one split-KV partial: 128 outputs, max, sum
+constexpr int MG_MAX_OWN = 64;                     // residual rows one CTA may own (H / 8 groups over the grid)
 
 struct alignas(64) MegaTmaps {
   CUtensorMap m[5];          // wqkv_all, wo_all, w13_all, w2_all, lm_head
 };
 
-// Tensor-parallel all-reduce state (tp == 1: unused).  Same inbox / flag protocol as comm.cu.
+// Cross-GPU packet buffers (symmetric heap of parallel/symm.py; tp == 1: cand_peer[0] is local scratch)
 struct MegaAr {
-  float* inbox[8];                   // peer p's inbox, mapped into this process: [parity][src][M][H] fp32
-  int* flags[8];                     // peer p's flag array
-  const int* seq_ptr;                // device epoch counter (bumped once per step by the host-side sequence)
-  size_t parity_stride;              // floats between the two parity halves
-  int flag_offset, tp, rank;
+  uint2* p_peer[8];                  // rank r's copy of the partial-sum packets: [parity][src][M][H] {fp32, tag}
+  uint2* p_mc;                       // NVLS multicast address of the same buffer (null: unicast to every peer)
+  uint2* cand_peer[8];               // rank r's copy of the arg-max candidates: [parity][src][grid][M][2] {bits, tag}
+  uint2* cand_mc;
+  int tp, rank;
 };
 
 struct MegaParams {
@@ -66,31 +94,61 @@ struct MegaParams {
   const __nv_bfloat16* final_norm;   // [H]
   const __nv_bfloat16* embedding;    // [vocab_full, H]
   const int* ids;                    // [M]
-  __nv_bfloat16* x;                  // [M, H]   residual stream
-  __nv_bfloat16* qkv;                // [M, NQKV]
-  __nv_bfloat16* attn;               // [M, nh·hd]
-  __nv_bfloat16* hmlp;               // [M, F]
-  float* logits;                     // [M, V]
+  uint2* r_pk;                       // [2][M][H/2]     residual stream after wo / w2 ({bf16 pair, tag})
+  uint2* qkv_pk;                     // [M][NQKV/2]
+  uint2* part_pk;                    // [M·nh][splits][130]   split-KV partials ({fp32, tag})
+  uint2* attn_pk;                    // [M][nh·hd/2]
+  uint2* h_pk;                       // [M][F/2]
+  float* logits;                     // [M, V] or null
   __nv_bfloat16* kc;                 // [L][M][nkv][T][hd]
   __nv_bfloat16* vc;
   const float* cos_t;
   const float* sin_t;
   const int* cache_len;
   const int* pad_left;
-  float* o_part;                     // [M·nh][splits][hd]
-  float* ml_part;                    // [M·nh][splits][2]
-  int* tickets;                      // [M·nkv]
-  unsigned int* bar_counter;         // monotonically increasing arrival counter
-  unsigned int* bar_gen;             // barriers completed by previous launches
+  unsigned int* gen;                 // steps run so far by this engine (tag base; bumped by block 0 at the end)
   int T, max_pos, splits, stages, l2_ahead;
   int w2_passes;                     // 2: w2 is walked in two K ranges (batch rows of its full input do not fit in smem)
-  unsigned long long* trace;         // optional [2][L][16] globaltimer stamps (block 0 and the last block)
+  unsigned long long* trace;         // optional [grid][L][32] globaltimer stamps
 };
 
 enum { MG_PLAIN = 0, MG_RESIDUAL = 1, MG_SWIGLU = 2, MG_LOGITS = 3 };
+enum { MG_W_X = 0, MG_W_QKV = 1, MG_W_PART = 2, MG_W_ATTN = 3, MG_W_H = 4, MG_W_PEER = 5 };      // what a poll waits for
 
 __device__ __forceinline__ void mg_consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(MG_CT) : "memory"); }
-__device__ __forceinline__ uint4 ldcg16(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
+
+// ---- tagged packets
+__device__ __forceinline__ void st_packet(uint2* dst, uint32_t payload, uint32_t tag) {
+  asm volatile("st.relaxed.gpu.global.v2.u32 [%0], {%1, %2};" ::"l"(dst), "r"(payload), "r"(tag) : "memory");
+}
+__device__ __forceinline__ uint4 ld_relaxed_gpu_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint2 ld_relaxed_gpu_v2(const uint2* p) {
+  uint2 v;
+  asm volatile("ld.relaxed.gpu.global.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+// cold path of every poll: never returns, so the caller keeps nothing alive across the call
+[[noreturn]] __device__ __noinline__ void mg_poll_timeout(int what, uint32_t want, uint32_t got) {
+  printf("jllama_b200: decode kernel block %d thread %d timed out polling packets of kind %d (tag %u, last seen %u)\n",
+         (int)blockIdx.x, (int)threadIdx.x, what, want, got);
+  __trap();
+  for (;;) {}
+}
+[[noreturn]] __device__ __noinline__ void mg_peer_timeout(int rank, int src, uint32_t tag, uint32_t got, int kind) {
+  printf("jllama_b200: rank %d timed out waiting for rank %d (%s, tag %u, last seen %u, block %d)\n", rank, src,
+         kind == 0 ? "partial sums of the all-reduce" : "arg-max candidates", tag, got, (int)blockIdx.x);
+  __trap();
+  for (;;) {}
+}
 
 __device__ __forceinline__ void mg_stamp(const MegaParams& p, int layer, int ev) {
   if (p.trace != nullptr && threadIdx.x == 32) {
@@ -118,22 +176,24 @@ struct MegaCtx {
   float* s_attn;              // attention fold scratch
   int stages;
   int stage; uint32_t phase;  // ring cursor (producer and consumers keep separate copies)
-  const MegaAr* ar;           // tensor-parallel state; ar_epoch tags (and its parity places) the current all-reduce
-  int ar_epoch;
+  const MegaAr* ar;           // tensor-parallel state; ar_tag tags (and its parity places) the current all-reduce
+  uint32_t ar_tag;
 };
 
-// row-parallel epilogue under tensor parallelism: hand this rank's fp32 partial to every peer's inbox.
-// Low-latency protocol: every value travels as one 8-byte store {value, epoch}; the receiver polls the slot
-// itself until the tag matches, so no flag, no fence and a single NVLink traversal are on the critical path
-// (a release-flag version measured ~11 µs per all-reduce at tp = 2).
+// row-parallel epilogue under tensor parallelism: hand this rank's fp32 partial to every rank (itself included).
+// One 8-byte packet {value, tag}; the receiver polls the slot until the tag matches, so no flag, no fence and a
+// single NVLink traversal are on the critical path.  With NVLS the switch replicates one store to all ranks.
 template <int M>
 __device__ __forceinline__ void mg_push_partial(const MegaCtx& c, int m, int row, int N, float v) {
   const MegaAr& a = *c.ar;
-  const size_t off = (size_t)(c.ar_epoch & 1) * (a.parity_stride / 2) + ((size_t)a.rank * M + m) * N + row;
-  const uint2 pkt = make_uint2(__float_as_uint(v), (unsigned)c.ar_epoch);
-  for (int peer = 0; peer < a.tp; ++peer) {
-    uint2* dst = reinterpret_cast<uint2*>(a.inbox[peer]) + off;
-    asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(dst), "r"(pkt.x), "r"(pkt.y) : "memory");
+  const size_t off = (((size_t)(c.ar_tag & 1) * a.tp + a.rank) * M + m) * N + row;
+  if (a.p_mc != nullptr) {
+    mm::st_b64(a.p_mc + off, __float_as_uint(v), c.ar_tag);
+  } else {
+    for (int peer = 0; peer < a.tp; ++peer)
+      asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(a.p_peer[peer] + off), "r"(__float_as_uint(v)),
+                   "r"(c.ar_tag)
+                   : "memory");
   }
 }
 
@@ -201,26 +261,27 @@ struct MegaCursor {
 #include "decode_mega_mma.cuh"
 namespace jl {
 
-// grid-wide barrier among the consumer warps of all CTAs
-__device__ __forceinline__ void mg_grid_barrier(const MegaParams& p, unsigned int gen_base, int& bar_idx) {
-  mg_consumer_bar();                                   // all of this CTA's global writes are issued
-  if (threadIdx.x == 32) {
-    __threadfence();
-    const unsigned int target = (gen_base + (unsigned)bar_idx + 1u) * gridDim.x;
-    atomicAdd(p.bar_counter, 1u);
-    unsigned int spins = 0;
-    while ((int)(ld_acquire_gpu_u32(p.bar_counter) - target) < 0) {
-      if (++spins > (1u << 26)) {
-        printf("jllama_b200: grid barrier %d timed out in block %d\n", bar_idx, (int)blockIdx.x);
-        __trap();
-      }
-    }
+// 8 consecutive bf16 of a packet row (4 packets = two 16-byte loads), polled until all four tags match
+struct MgPoll8 {
+  const uint4* src;
+  uint4 a, b;
+  __device__ __forceinline__ void issue(const uint2* pk) {
+    src = reinterpret_cast<const uint4*>(pk);
+    a = ld_relaxed_gpu_v4(src);
+    b = ld_relaxed_gpu_v4(src + 1);
   }
-  ++bar_idx;
-  mg_consumer_bar();
-}
+  __device__ __forceinline__ uint4 wait(uint32_t tag, int what) {
+    unsigned spins = 0;
+    while (a.y != tag || a.w != tag || b.y != tag || b.w != tag) {
+      a = ld_relaxed_gpu_v4(src);
+      b = ld_relaxed_gpu_v4(src + 1);
+      if (++spins > (1u << 24)) mg_poll_timeout(what, tag, a.y);
+    }
+    return make_uint4(a.x, a.z, b.x, b.z);
+  }
+};
 
-// RoPE + KV append + split-KV attention for one (b, kv head, split) item + ticket merge (8 consumer warps)
+// RoPE + KV append + split-KV attention for one (b, kv head, split) item (8 consumer warps)
 struct MgPos { int len, first; float cs[4], sn[4]; };      // per-step constants of one batch row (this lane's pairs)
 
 __device__ __forceinline__ MgPos mg_pos(const MegaParams& p, int b, int lig) {
@@ -239,7 +300,7 @@ __device__ __forceinline__ MgPos mg_pos(const MegaParams& p, int b, int lig) {
 
 template <int G>
 __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const MegaCtx& c, int layer, int M, int b,
-                                                  int kvh, int split, int* s_last, const MgPos& pp) {
+                                                  int kvh, int split, uint32_t tag, const MgPos& pp) {
   constexpr int HD = MG_HD, LPK = HD / 8, GPW = 32 / LPK, NG = MG_CONSUMERS * GPW;
   constexpr int KEYS_PER_ITER = NG * MG_KPI;
   const int nh = p.nkv * G;
@@ -258,19 +319,20 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
 
   mg_stamp(p, layer, 16);
   const float cs[4] = {pp.cs[0], pp.cs[1], pp.cs[2], pp.cs[3]}, sn[4] = {pp.sn[0], pp.sn[1], pp.sn[2], pp.sn[3]};
-  const __nv_bfloat16* row = p.qkv + (size_t)b * p.NQKV;
-  // the new token's k, v are fetched together with q (consumed after the KV loop by split 0 / warp 0)
-  const bool owns_new = split == 0 && warp == 0;
-  uint4 ka = make_uint4(0, 0, 0, 0), va = ka;
+  // q (all heads of the group) and the new token's k, v arrive as packets from the qkv GEMV of other CTAs
+  const uint2* row = p.qkv_pk + (size_t)b * (p.NQKV / 2);
+  const bool owns_new = split == 0 && warp == 0;      // consumes the new k, v after the KV loop
+  MgPoll8 pq[G], pk_new, pv_new;
+#pragma unroll
+  for (int g = 0; g < G; ++g) pq[g].issue(row + ((size_t)(kvh * G + g) * HD + lig * 8) / 2);
   if (owns_new) {
-    ka = ldcg16(row + (size_t)(nh + kvh) * HD + lig * 8);
-    va = ldcg16(row + (size_t)(nh + p.nkv + kvh) * HD + lig * 8);
+    pk_new.issue(row + ((size_t)(nh + kvh) * HD + lig * 8) / 2);
+    pv_new.issue(row + ((size_t)(nh + p.nkv + kvh) * HD + lig * 8) / 2);
   }
-
   float qf[G][8];
 #pragma unroll
   for (int g = 0; g < G; ++g) {
-    const uint4 a = ldcg16(row + (size_t)(kvh * G + g) * HD + lig * 8);
+    const uint4 a = pq[g].wait(tag, MG_W_QKV);
     const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -279,6 +341,11 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
       qf[g][2 * j] = bf16_lo(r) * p.scale_log2;
       qf[g][2 * j + 1] = bf16_hi(r) * p.scale_log2;
     }
+  }
+  uint4 ka = make_uint4(0, 0, 0, 0), va = ka;
+  if (owns_new) {
+    ka = pk_new.wait(tag, MG_W_QKV);
+    va = pv_new.wait(tag, MG_W_QKV);
   }
   float m[G], l[G], o[G][8];
 #pragma unroll
@@ -412,6 +479,7 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
     if (lig == 0) { s_ml[gid][g][0] = m[g]; s_ml[gid][g][1] = l[g]; }
   }
   mg_consumer_bar();
+  // G·HD is a multiple of 128: the trip count is warp-uniform, so the pair shuffle below has all lanes present
   for (int idx = ct; idx < G * HD; idx += MG_CT) {
     const int g = idx / HD, d = idx - g * HD;
     float Mx = -INFINITY;
@@ -427,97 +495,108 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
     }
     const int h = kvh * G + g;
     if (p.splits == 1) {
-      p.attn[((size_t)b * nh + h) * HD + d] = __float2bfloat16(Ls > 0.f ? acc / Ls : 0.f);
+      const float y = Ls > 0.f ? acc / Ls : 0.f;
+      const float y1 = __shfl_down_sync(0xffffffffu, y, 1);
+      if ((d & 1) == 0) st_packet(p.attn_pk + ((size_t)b * nh + h) * (HD / 2) + (d >> 1), pack_bf16(y, y1), tag);
     } else {
-      const size_t pi = ((size_t)b * nh + h) * p.splits + split;
-      p.o_part[pi * HD + d] = acc;
-      if (d == 0) { p.ml_part[pi * 2] = Mx; p.ml_part[pi * 2 + 1] = Ls; }
+      uint2* dst = p.part_pk + (((size_t)b * nh + h) * p.splits + split) * MG_PART;
+      st_packet(dst + d, __float_as_uint(acc), tag);
+      if (d == 0) { st_packet(dst + HD, __float_as_uint(Mx), tag); st_packet(dst + HD + 1, __float_as_uint(Ls), tag); }
     }
   }
-  (void)s_last;
   mg_stamp(p, layer, 20);
   mg_consumer_bar();                 // s_attn is reused by this CTA's next item
 }
 
-// Merge of the split-KV partials, spread over the whole grid (one output element per thread): runs after a
-// grid barrier.  The earlier "last CTA of each kv head merges" ticket scheme put atomic + two dependent L2
-// round trips of a single CTA on the critical path of every layer (13 µs per attention phase).
-__device__ __forceinline__ void mg_attn_merge(const MegaParams& p, int M) {
-  const int ct = threadIdx.x - 32;
+// Merge of the split-KV partials, spread over the grid one warp at a time (32 outputs per warp, every CTA's first
+// warp before any CTA's second): a thread polls the partial packets of its output, combines them online in chunks
+// of 8 splits, and publishes the merged attention output as {bf16 pair, tag} packets for the `wo` staging.
+__device__ __forceinline__ void mg_attn_merge(const MegaParams& p, int M, uint32_t tag) {
+  const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
   const int total = M * p.nh * MG_HD;
-  for (int idx = blockIdx.x * MG_CT + ct; idx < total; idx += gridDim.x * MG_CT) {
+  for (int idx = (cw * gridDim.x + blockIdx.x) * 32 + lane; idx < total; idx += gridDim.x * MG_CT) {
     const int bh = idx / MG_HD, d = idx - bh * MG_HD;
-    const float2* ml = reinterpret_cast<const float2*>(p.ml_part) + (size_t)bh * p.splits;
-    const float* op = p.o_part + (size_t)bh * p.splits * MG_HD + d;
-    float acc = 0.f, Ls = 0.f;
-    if (p.splits <= 32) {
-      // issue every load of this output up front: one L2 round trip instead of two dependent ones
-      float2 e[32];
-      float ov[32];
+    const uint2* base = p.part_pk + (size_t)bh * p.splits * MG_PART;
+    float Mx = -INFINITY, acc = 0.f, Ls = 0.f;
+    for (int s0 = 0; s0 < p.splits; s0 += 8) {
+      uint2 ov[8];
+      uint4 ml[8];
 #pragma unroll
-      for (int sp = 0; sp < 32; ++sp) {
-        if (sp < p.splits) { e[sp] = __ldcg(ml + sp); ov[sp] = __ldcg(op + (size_t)sp * MG_HD); }
-        else { e[sp] = make_float2(-INFINITY, 0.f); ov[sp] = 0.f; }
+      for (int u = 0; u < 8; ++u) {
+        const uint2* q = base + (size_t)(s0 + u < p.splits ? s0 + u : s0) * MG_PART;
+        ov[u] = ld_relaxed_gpu_v2(q + d);
+        ml[u] = ld_relaxed_gpu_v4(reinterpret_cast<const uint4*>(q + MG_HD));
       }
-      float Mx = -INFINITY;
+      unsigned spins = 0;
 #pragma unroll
-      for (int sp = 0; sp < 32; ++sp) Mx = fmaxf(Mx, e[sp].x);
-      const float Ms = Mx == -INFINITY ? 0.f : Mx;
+      for (int u = 0; u < 8; ++u) {
+        const uint2* q = base + (size_t)(s0 + u < p.splits ? s0 + u : s0) * MG_PART;
+        while (ov[u].y != tag || ml[u].y != tag || ml[u].w != tag) {
+          ov[u] = ld_relaxed_gpu_v2(q + d);
+          ml[u] = ld_relaxed_gpu_v4(reinterpret_cast<const uint4*>(q + MG_HD));
+          if (++spins > (1u << 24)) mg_poll_timeout(MG_W_PART, tag, ov[u].y);
+        }
+      }
+      float cm = Mx;
 #pragma unroll
-      for (int sp = 0; sp < 32; ++sp) {
-        const float w = exp2f(e[sp].x - Ms);
-        acc += w > 0.f ? w * ov[sp] : 0.f;
-        Ls += w * e[sp].y;
+      for (int u = 0; u < 8; ++u)
+        if (s0 + u < p.splits) cm = fmaxf(cm, __uint_as_float(ml[u].x));
+      const float Ms = cm == -INFINITY ? 0.f : cm;
+      const float corr = exp2f(Mx - Ms);                 // Mx = -inf on the first chunk: 0
+      acc *= corr;
+      Ls *= corr;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (s0 + u < p.splits) {
+          const float w = exp2f(__uint_as_float(ml[u].x) - Ms);
+          acc += w > 0.f ? w * __uint_as_float(ov[u].x) : 0.f;
+          Ls += w * __uint_as_float(ml[u].z);
+        }
       }
-    } else {
-      float Mx = -INFINITY;
-#pragma unroll 8
-      for (int sp = 0; sp < p.splits; ++sp) Mx = fmaxf(Mx, __ldcg(ml + sp).x);
-      const float Ms = Mx == -INFINITY ? 0.f : Mx;
-#pragma unroll 8
-      for (int sp = 0; sp < p.splits; ++sp) {
-        const float2 e = __ldcg(ml + sp);
-        const float w = exp2f(e.x - Ms);
-        const float ov = __ldcg(op + (size_t)sp * MG_HD);
-        acc += w > 0.f ? w * ov : 0.f;
-        Ls += w * e.y;
-      }
+      Mx = cm;
     }
-    p.attn[idx] = __float2bfloat16(Ls > 0.f ? acc / Ls : 0.f);
+    const float y = Ls > 0.f ? acc / Ls : 0.f;
+    const float y1 = __shfl_down_sync(0xffffffffu, y, 1);
+    if ((d & 1) == 0) st_packet(p.attn_pk + (size_t)bh * (MG_HD / 2) + (d >> 1), pack_bf16(y, y1), tag);
   }
 }
 
-// Second half of the in-kernel one-shot all-reduce (tp > 1): publish this CTA's slice to every peer, wait for
-// the same-index CTA of every peer (all ranks cut rows identically), reduce in rank order (bit-identical on
-// all ranks), add the residual and store the new residual-stream rows.  The local grid barrier follows.
+// Second half of the in-kernel one-shot all-reduce (tp > 1): the owner CTA of a row range waits for the packets of
+// the same-index CTA of every rank (all ranks cut rows identically), sums them in rank order (bit-identical on
+// all ranks), adds its residual slice and publishes the new residual-stream packets to the CTAs of this GPU.
 template <int M>
-__device__ __forceinline__ void mg_ar_finish(const MegaParams& p, const MegaCtx& c, int epoch, int N) {
+__device__ __forceinline__ void mg_owner_reduce(const MegaParams& p, uint32_t tag, int N, float (*res)[MG_MAX_OWN],
+                                                uint2* r_pk) {
   const MegaAr& a = p.ar;
   const int ct = threadIdx.x - 32;
   int g0, g1;
   mg_range(N / MG_GROUP, g0, g1);
-  const int nrows = (g1 - g0) * MG_GROUP;
-  const uint2* mine = reinterpret_cast<const uint2*>(a.inbox[a.rank]) + (size_t)(epoch & 1) * (a.parity_stride / 2);
-  for (int i = ct; i < nrows * M; i += MG_CT) {
-    const int m = i / nrows, row = g0 * MG_GROUP + (i - m * nrows);
-    float s = 0.f;
-    for (int src = 0; src < a.tp; ++src) {
-      const uint2* slot = mine + ((size_t)src * M + m) * N + row;
-      uint2 pkt;
-      unsigned spins = 0;
-      for (;;) {
-        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(pkt.x), "=r"(pkt.y) : "l"(slot) : "memory");
-        if ((int)pkt.y == epoch) break;
-        if (++spins > (1u << 26)) {
-          printf("jllama_b200: rank %d timed out waiting for peer %d (all-reduce epoch %d, block %d)\n", a.rank, src, epoch,
-                 (int)blockIdx.x);
-          __trap();
+  const int row0 = g0 * MG_GROUP, pairs = (g1 - g0) * MG_GROUP / 2;
+  const uint2* mine = a.p_peer[a.rank] + (size_t)(tag & 1) * a.tp * M * N;
+  for (int i = ct; i < pairs * M; i += MG_CT) {
+    const int m = i / pairs, row = row0 + 2 * (i - m * pairs);
+    uint4 v[8];
+#pragma unroll
+    for (int src = 0; src < 8; ++src)
+      if (src < a.tp) v[src] = ld_relaxed_sys_v4(reinterpret_cast<const uint4*>(mine + ((size_t)src * M + m) * N + row));
+    float s0 = 0.f, s1 = 0.f;
+    unsigned spins = 0;
+#pragma unroll
+    for (int src = 0; src < 8; ++src) {
+      if (src < a.tp) {
+        while (v[src].y != tag || v[src].w != tag) {
+          v[src] = ld_relaxed_sys_v4(reinterpret_cast<const uint4*>(mine + ((size_t)src * M + m) * N + row));
+          if (++spins > (1u << 24)) mg_peer_timeout(a.rank, src, tag, v[src].y, 0);
         }
+        s0 += __uint_as_float(v[src].x);
+        s1 += __uint_as_float(v[src].z);
       }
-      s += __uint_as_float(pkt.x);
     }
-    const float y = __bfloat162float(__float2bfloat16(s)) + __bfloat162float(__ldcg(p.x + (size_t)m * N + row));
-    p.x[(size_t)m * N + row] = __float2bfloat16(y);
+    const float y0 = __bfloat162float(__float2bfloat16(__bfloat162float(__float2bfloat16(s0)) + res[m][row - row0]));
+    const float y1 = __bfloat162float(__float2bfloat16(__bfloat162float(__float2bfloat16(s1)) + res[m][row - row0 + 1]));
+    res[m][row - row0] = y0;
+    res[m][row - row0 + 1] = y1;
+    st_packet(r_pk + (size_t)m * (N / 2) + (row >> 1), pack_bf16(y0, y1), tag);
   }
 }
 
@@ -528,11 +607,10 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   __shared__ float red[M][MG_CONSUMERS];
   __shared__ __align__(16) float s_acc[2][MG_CONSUMERS][MG_MMA_MAX_M][8];
   __shared__ float s_carry[M > 4 ? M : 1][64];         // two-pass w2: sums of the first K range (this CTA's rows)
+  __shared__ float s_res[M][MG_MAX_OWN];               // this CTA's rows of the residual stream (bf16-exact values)
   __shared__ volatile int s_idle_flag;          // consumers → producer: "no GEMV is consuming the ring right now"
   volatile int* s_idle = &s_idle_flag;
   if (threadIdx.x == 0) s_idle_flag = 0;
-  __shared__ int s_last;
-  constexpr int NG = MG_CONSUMERS * (32 / (MG_HD / 8));
 
   MegaCtx c;
   c.stages = p.stages;
@@ -541,13 +619,11 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   c.bars = c.ring + p.stages * MG_STAGE_BYTES;
   uint8_t* after = const_cast<uint8_t*>(c.ring_ptr) + p.stages * MG_STAGE_BYTES + 16 * p.stages;
   c.s_attn = reinterpret_cast<float*>(after);
-  const int kmax = p.H > p.F ? p.H : p.F;
   // the staged GEMV input and the attention scratch are never live together (a GEMV ends before attention
   // starts and is restaged after it), so they share one region sized for the larger of the two
   c.xin = reinterpret_cast<uint4*>(after);
-  (void)kmax;
   c.stage = 0; c.phase = 0;
-  c.ar = &p.ar; c.ar_epoch = 0;
+  c.ar = &p.ar; c.ar_tag = 0;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -564,9 +640,9 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   if (warp == 0) {
     // ===================================================== producer: the whole model's weights, in order
     if (lane == 0) {
-      // `ld` feeds the ring.  While the consumers are NOT consuming (attention, merge and the barriers around
+      // `ld` feeds the ring.  While the consumers are NOT consuming (attention, merge and the polls around
       // them: s_idle is set) and the ring is full, `pf` walks up to p.l2_ahead stages further down the same
-      // sequence and only asks the L2 to fetch them, so HBM keeps streaming through the ~12 µs per layer in
+      // sequence and only asks the L2 to fetch them, so HBM keeps streaming through the part of a layer in
       // which no GEMV runs.  (Prefetching all the time was measured twice and loses: it queues in front of
       // the loads the GEMV is waiting for.)
       MegaCursor ld, pf;
@@ -604,117 +680,243 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   }
 
   // ===================================================== consumers
-#define MG_STAGE(SRC_, K_, NORM_) mg_stage_input_mma<M>(c, SRC_, K_, NORM_, p.eps, red)
-#define MG_GEMV(MODE_, N_, K_, OUT_, RES_) mg_gemv_mma<M, MODE_>(c, N_, K_, OUT_, RES_, s_acc)
-  const unsigned int gen_base = *reinterpret_cast<volatile unsigned int*>(p.bar_gen);
-  int bar_idx = 0;
+  const unsigned int gen = *reinterpret_cast<volatile unsigned int*>(p.gen);
+  const uint32_t base = gen * (uint32_t)(2 * p.L);           // tags of this step: base + 2 l + {1, 2}; base is even
   const MgPos pos0 = mg_pos(p, 0, lane % (MG_HD / 8));      // batch row 0: constant for the whole step
-  const int ar_base = p.ar.tp > 1 ? __ldcg(p.ar.seq_ptr) : 0;      // epoch of collective j is ar_base + j + 1
   const int ct = threadIdx.x - 32;
+  int own0, own1;
+  mg_range(p.H / MG_GROUP, own0, own1);
+  own0 *= MG_GROUP; own1 *= MG_GROUP;                        // rows of the residual stream this CTA owns
 
-  // embedding rows → residual stream (each CTA copies a slice), then everyone sees x
-  {
-    const int H8 = p.H >> 3;
-    for (int i = blockIdx.x * MG_CT + ct; i < M * H8; i += gridDim.x * MG_CT) {
-      const int m = i / H8, j = i - m * H8;
-      int id = p.ids[m];
-      id = id < 0 ? 0 : (id >= p.vocab_full ? p.vocab_full - 1 : id);
-      reinterpret_cast<uint4*>(p.x)[i] = __ldg(reinterpret_cast<const uint4*>(p.embedding) + (size_t)id * H8 + j);
-    }
+  // residual slice ← embedding rows of this step's tokens
+  for (int i = ct; i < M * (own1 - own0); i += MG_CT) {
+    const int m = i / (own1 - own0), j = i - m * (own1 - own0);
+    int id = p.ids[m];
+    id = id < 0 ? 0 : (id >= p.vocab_full ? p.vocab_full - 1 : id);
+    s_res[m][j] = __bfloat162float(p.embedding[(size_t)id * p.H + own0 + j]);
   }
-  mg_grid_barrier(p, gen_base, bar_idx);
+  // (first read of s_res happens after the consumer barriers of the first staging pass)
 
+  const size_t r_half = (size_t)M * (p.H / 2);               // packets of one parity half of the residual buffer
+  MegaOut o;
+  o.res = s_res; o.row0 = own0; o.logits = nullptr; o.best_v = nullptr; o.best_i = nullptr; o.idx_offset = 0;
+  o.pk = nullptr; o.r_pk = nullptr; o.tag = 0;
   for (int l = 0; l < p.L; ++l) {
-    // ---- fused qkv projection (RMSNorm in the prologue)
+    const uint32_t t1 = base + 2u * l + 1u, t2 = t1 + 1u;      // t1 odd, t2 even
+    uint2* r1 = p.r_pk + r_half;                               // residual packets tagged t1 (after wo)
+    uint2* r2 = p.r_pk;                                        // residual packets tagged t2 (after w2)
+    // ---- fused qkv projection (RMSNorm in the prologue); x comes from the previous layer's w2 epilogues
     mg_stamp(p, l, 0);
-    MG_STAGE(p.x, p.H, p.attn_norm + (size_t)l * p.H);
+    if (l == 0) mg_stage_embedding<M>(c, p.embedding, p.ids, p.vocab_full, p.H, p.attn_norm, p.eps, red);
+    else mg_stage_packets<M>(c, r2, t1 - 1u, p.H, p.H / 2, p.attn_norm + (size_t)l * p.H, p.eps, red, MG_W_X);
     mg_stamp(p, l, 1);
-    MG_GEMV(MG_PLAIN, p.NQKV, p.H, p.qkv, nullptr);
+    o.pk = p.qkv_pk; o.tag = t1;
+    mg_gemv_mma<M, MG_PLAIN>(c, p.NQKV, p.H, o, s_acc);
     mg_stamp(p, l, 2);
-    mg_grid_barrier(p, gen_base, bar_idx);
-    mg_stamp(p, l, 3);
     if (threadIdx.x == 32) *s_idle = 1;
-    // ---- attention
+    // ---- attention: each item polls the q / k / v packets it needs
     {
       const int items = M * p.nkv * p.splits;
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
         const int split = it % p.splits, bk = it / p.splits;
         const int bb = bk / p.nkv;
-        mg_attention_item<G>(p, c, l, M, bb, bk % p.nkv, split, &s_last, M == 1 ? pos0 : mg_pos(p, bb, lane % (MG_HD / 8)));
+        mg_attention_item<G>(p, c, l, M, bb, bk % p.nkv, split, t1, M == 1 ? pos0 : mg_pos(p, bb, lane % (MG_HD / 8)));
       }
     }
+    mg_stamp(p, l, 3);
+    if (p.splits > 1) mg_attn_merge(p, M, t1);
     mg_stamp(p, l, 4);
-    mg_grid_barrier(p, gen_base, bar_idx);
-    if (p.splits > 1) {                      // grid-uniform: every CTA takes the same branch
-      mg_attn_merge(p, M);
-      mg_grid_barrier(p, gen_base, bar_idx);
-    }
-    mg_stamp(p, l, 5);
     // ---- wo + residual
-    MG_STAGE(p.attn, qdim, nullptr);
-    mg_stamp(p, l, 6);
+    mg_stage_packets<M>(c, p.attn_pk, t1, qdim, qdim / 2, nullptr, p.eps, red, MG_W_ATTN);
+    mg_stamp(p, l, 5);
     if (threadIdx.x == 32) *s_idle = 0;
-    c.ar_epoch = ar_base + 2 * l + 1;
-    MG_GEMV(MG_RESIDUAL, p.H, qdim, p.x, p.x);
-    if (p.ar.tp > 1) mg_ar_finish<M>(p, c, ar_base + 2 * l + 1, p.H);
-    mg_stamp(p, l, 7);
-    mg_grid_barrier(p, gen_base, bar_idx);
-    mg_stamp(p, l, 8);
+    c.ar_tag = t1;
+    o.r_pk = r1; o.tag = t1;
+    mg_gemv_mma<M, MG_RESIDUAL>(c, p.H, qdim, o, s_acc);
+    if (p.ar.tp > 1) mg_owner_reduce<M>(p, t1, p.H, s_res, r1);
+    mg_stamp(p, l, 6);
     // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
-    MG_STAGE(p.x, p.H, p.ffn_norm + (size_t)l * p.H);
-    mg_stamp(p, l, 9);
-    MG_GEMV(MG_SWIGLU, 2 * p.F, p.H, p.hmlp, nullptr);
-    mg_stamp(p, l, 10);
-    mg_grid_barrier(p, gen_base, bar_idx);
-    mg_stamp(p, l, 11);
+    mg_stage_packets<M>(c, r1, t1, p.H, p.H / 2, p.ffn_norm + (size_t)l * p.H, p.eps, red, MG_W_X);
+    mg_stamp(p, l, 7);
+    o.pk = p.h_pk; o.tag = t2;
+    mg_gemv_mma<M, MG_SWIGLU>(c, 2 * p.F, p.H, o, s_acc);
+    mg_stamp(p, l, 8);
     // ---- w2 + residual
+    c.ar_tag = t2;
+    o.r_pk = r2; o.tag = t2;
     bool w2_done = false;
     if constexpr (M > 4) {
       if (p.w2_passes == 2) {
         const int ka = ((p.F + MG_KS - 1) / MG_KS + 1) / 2 * MG_KS;       // first K range: whole k-stages
-        mg_stage_input_mma<M>(c, p.hmlp, ka, nullptr, p.eps, red, p.F);
-        mg_stamp(p, l, 12);
-        c.ar_epoch = ar_base + 2 * l + 2;
-        mg_gemv_mma<M, MG_RESIDUAL, 1>(c, p.H, ka, p.x, p.x, s_acc, s_carry);
-        mg_stage_input_mma<M>(c, p.hmlp + ka, p.F - ka, nullptr, p.eps, red, p.F);
-        mg_gemv_mma<M, MG_RESIDUAL, 2>(c, p.H, p.F - ka, p.x, p.x, s_acc, s_carry);
+        mg_stage_packets<M>(c, p.h_pk, t2, ka, p.F / 2, nullptr, p.eps, red, MG_W_H);
+        mg_stamp(p, l, 9);
+        mg_gemv_mma<M, MG_RESIDUAL, 1>(c, p.H, ka, o, s_acc, s_carry);
+        mg_stage_packets<M>(c, p.h_pk + ka / 2, t2, p.F - ka, p.F / 2, nullptr, p.eps, red, MG_W_H);
+        mg_gemv_mma<M, MG_RESIDUAL, 2>(c, p.H, p.F - ka, o, s_acc, s_carry);
         w2_done = true;
       }
     }
     if (!w2_done) {
-      MG_STAGE(p.hmlp, p.F, nullptr);
-      mg_stamp(p, l, 12);
-      c.ar_epoch = ar_base + 2 * l + 2;
-      MG_GEMV(MG_RESIDUAL, p.H, p.F, p.x, p.x);
+      mg_stage_packets<M>(c, p.h_pk, t2, p.F, p.F / 2, nullptr, p.eps, red, MG_W_H);
+      mg_stamp(p, l, 9);
+      mg_gemv_mma<M, MG_RESIDUAL>(c, p.H, p.F, o, s_acc);
     }
-    if (p.ar.tp > 1) mg_ar_finish<M>(p, c, ar_base + 2 * l + 2, p.H);
-    mg_stamp(p, l, 13);
-    mg_grid_barrier(p, gen_base, bar_idx);
-    mg_stamp(p, l, 14);
+    if (p.ar.tp > 1) mg_owner_reduce<M>(p, t2, p.H, s_res, r2);
+    mg_stamp(p, l, 10);
   }
-  // ---- final norm + LM head
-  MG_STAGE(p.x, p.H, p.final_norm);
-  MG_GEMV(MG_LOGITS, p.V, p.H, p.logits, nullptr);
-  mg_grid_barrier(p, gen_base, bar_idx);
-  if (blockIdx.x == 0 && threadIdx.x == 32) *p.bar_gen = gen_base + (unsigned)bar_idx;
+  // ---- final norm + LM head with a running arg-max per (batch row, weight-row lane)
+  const uint32_t t_last = base + 2u * p.L;
+  mg_stage_packets<M>(c, p.r_pk, t_last, p.H, p.H / 2, p.final_norm, p.eps, red, MG_W_X);
+  float best_v = -INFINITY;
+  int best_i = 0x7fffffff;
+  o.logits = p.logits; o.best_v = &best_v; o.best_i = &best_i; o.idx_offset = p.ar.rank * p.V;
+  mg_gemv_mma<M, MG_LOGITS>(c, p.V, p.H, o, s_acc);
+  if (ct < 64) {                                             // thread (m, n): fold the 8 weight-row lanes of a batch row
+#pragma unroll
+    for (int off = 1; off < 8; off <<= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best_v, off);
+      const int oi = __shfl_xor_sync(0xffffffffu, best_i, off);
+      if (ov > best_v || (ov == best_v && oi < best_i)) { best_v = ov; best_i = oi; }
+    }
+    const int m = ct >> 3;
+    if ((ct & 7) == 0 && m < M) {
+      // one candidate per (CTA, batch row), published to every rank: {value, tag}, {index, tag}
+      const MegaAr& a = p.ar;
+      const size_t off = ((((size_t)(gen & 1) * a.tp + a.rank) * gridDim.x + blockIdx.x) * M + m) * 2;
+      if (a.cand_mc != nullptr) {
+        mm::st_b64(a.cand_mc + off, __float_as_uint(best_v), t_last);
+        mm::st_b64(a.cand_mc + off + 1, (uint32_t)best_i, t_last);
+      } else {
+        for (int peer = 0; peer < a.tp; ++peer) {
+          asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(a.cand_peer[peer] + off),
+                       "r"(__float_as_uint(best_v)), "r"(t_last) : "memory");
+          asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(a.cand_peer[peer] + off + 1),
+                       "r"((uint32_t)best_i), "r"(t_last) : "memory");
+        }
+      }
+    }
+  }
+  // every block read `gen` before it produced anything, and block 0 got here only after consuming packets of the
+  // last layer from every block: nobody can still be about to read the old value
+  if (blockIdx.x == 0 && threadIdx.x == 32) *p.gen = gen + 1u;
+}
+
+// Greedy selection + sequence bookkeeping after the decode kernel: merges the grid x tp arg-max candidates of every
+// batch row (polling the packets of ranks whose kernel is still finishing), ties → lower vocabulary index, then
+// does what advance_kernel does.  One CTA.
+struct SelectParams {
+  const uint2* cand;           // this rank's copy: [parity][tp][grid][M][2]
+  const unsigned int* gen;     // already bumped by the decode kernel of this step
+  int tp, grid, M, two_l, rank;
+  int* tok; int* next_ids; int* finished; int* sequences;
+  int max_len, eos, pad;
+  int* cur_len; int* cache_len; int* step; int* n_unfinished;
+};
+
+__global__ void __launch_bounds__(256) mega_select_kernel(const SelectParams p) {
+  __shared__ float sv[8];
+  __shared__ int si[8];
+  __shared__ int alive;
+  const unsigned int gen_now = *reinterpret_cast<const volatile unsigned int*>(p.gen);
+  const uint32_t tag = gen_now * (uint32_t)p.two_l;          // = (gen_now - 1) * 2L + 2L
+  const int parity = (gen_now - 1u) & 1u;
+  const int ncand = p.tp * p.grid;
+  const uint2* base = p.cand + (size_t)parity * ncand * p.M * 2;
+  if (threadIdx.x == 0) alive = 0;
+  const int cl = *p.cur_len;
+  for (int m = 0; m < p.M; ++m) {
+    float bv = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int cnd = threadIdx.x; cnd < ncand; cnd += blockDim.x) {
+      const uint4* q = reinterpret_cast<const uint4*>(base + ((size_t)cnd * p.M + m) * 2);
+      uint4 v = ld_relaxed_sys_v4(q);
+      unsigned spins = 0;
+      while (v.y != tag || v.w != tag) {
+        v = ld_relaxed_sys_v4(q);
+        if (++spins > (1u << 24)) mg_peer_timeout(p.rank, cnd / p.grid, tag, v.y, 1);
+      }
+      const float x = __uint_as_float(v.x);
+      const int id = (int)v.z;
+      if (x > bv || (x == bv && id < bi)) { bv = x; bi = id; }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, off);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+      if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int w = 1; w < 8; ++w)
+        if (sv[w] > bv || (sv[w] == bv && si[w] < bi)) { bv = sv[w]; bi = si[w]; }
+      int t = bi == 0x7fffffff ? 0 : bi;
+      int f = p.finished[m];
+      if (f) t = p.pad;
+      f = f | (t == p.eos);
+      p.finished[m] = f;
+      p.tok[m] = t;
+      p.next_ids[m] = t;
+      if (cl < p.max_len) p.sequences[(size_t)m * p.max_len + cl] = t;
+      if (!f) ++alive;
+    }
+  }
+  if (threadIdx.x == 0) {
+    *p.cur_len = cl + 1;
+    *p.cache_len = *p.cache_len + 1;
+    *p.step = *p.step + 1;
+    *p.n_unfinished = alive;
+  }
 }
 
 }  // namespace jl
 
 using namespace jl;
 
-extern "C" JL_API int jl_decode_mega_barriers(int L) { return 2 + 5 * L; }
-
 // optional per-op timestamp buffer ([grid][L][32] u64, device memory; slot 31 = %smid); NULL disables tracing
 static unsigned long long* g_mega_trace = nullptr;
 extern "C" JL_API void jl_decode_mega_set_trace(void* buf) { g_mega_trace = (unsigned long long*)buf; }
 
-extern "C" JL_API size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, int num_sms) {
+static int mega_splits(int M, int nh, int nkv, int T, int num_sms) {
+  const int G = nkv > 0 ? nh / nkv : 1;
   int splits = num_sms / (M * nkv);
-  if (splits < 1) splits = 1;
   if (splits > 64) splits = 64;
-  const size_t parts = (size_t)M * nh * splits * (MG_HD + 2) * sizeof(float);
-  return parts + (size_t)M * nkv * sizeof(int) + 2 * sizeof(unsigned int) + 64;
+  // a split shorter than one 128-key batch only adds partials to merge (tp = 8 has one KV head per rank:
+  // 148 candidate splits for a 2k context): cap by the cache capacity over one load batch
+  const int batch_keys = G <= 4 ? 128 : 64;           // keys one item handles per load batch (UNR x 64 in mg_attention_item)
+  if (T > 0 && splits > (T + batch_keys - 1) / batch_keys) splits = (T + batch_keys - 1) / batch_keys;
+  if (splits < 1) splits = 1;
+  return splits;
+}
+
+// Packet buffers of one (batch, shape): residual x 2 parities, qkv, split-KV partials, attention output, SwiGLU
+// output, local arg-max candidates.  Must be ZERO when first used (tag 0 never matches) and is never cleared again.
+struct MegaLayout { size_t r, qkv, part, attn, h, cand, total; };
+static MegaLayout mega_layout(int M, int H, int F, int nh, int nkv, int num_sms) {
+  MegaLayout o;
+  const int splits = mega_splits(M, nh, nkv, 0, num_sms);            // upper bound over all cache capacities
+  size_t at = 0;
+  auto take = [&](size_t packets) { const size_t off = at; at += (packets * 8 + 255) / 256 * 256; return off; };
+  o.r = take((size_t)2 * M * (H / 2));
+  o.qkv = take((size_t)M * ((nh + 2 * nkv) * MG_HD / 2));
+  o.part = take((size_t)M * nh * splits * MG_PART);
+  o.attn = take((size_t)M * (nh * MG_HD / 2));
+  o.h = take((size_t)M * (F / 2));
+  o.cand = take((size_t)2 * num_sms * M * 2);
+  o.total = at;
+  return o;
+}
+extern "C" JL_API size_t jl_decode_mega_scratch_bytes(int M, int H, int F, int nh, int nkv, int num_sms) {
+  if (num_sms <= 0) num_sms = 148;
+  return mega_layout(M, H, F, nh, nkv, num_sms).total;
+}
+// bytes of the two cross-GPU packet buffers (symmetric heap) for batches up to M on tp ranks
+extern "C" JL_API size_t jl_decode_mega_peer_bytes(int M, int H, int tp, int num_sms, size_t* cand_offset) {
+  if (num_sms <= 0) num_sms = 148;
+  const size_t p_bytes = ((size_t)2 * tp * M * H * 8 + 1023) / 1024 * 1024;
+  if (cand_offset) *cand_offset = p_bytes;
+  return p_bytes + (size_t)2 * tp * num_sms * M * 2 * 8;
 }
 
 // Shared-memory plan: the staged activations (M rows of the widest GEMV input, whole k-stages), the attention
@@ -727,7 +929,7 @@ static int mega_ring_stages(int M, int H, int F, int nh, int nkv, int hd, size_t
   const size_t xin_bytes = (size_t)M * ((kmax + MG_KS - 1) / MG_KS * MG_KS) * 2;      // whole k-stages (zero padded)
   const size_t attn_bytes = (size_t)(MG_CONSUMERS * 2) * G * (MG_HD + 2) * sizeof(float);
   const size_t fixed = 1024 + (xin_bytes > attn_bytes ? xin_bytes : attn_bytes) + 64;      // shared region (see kernel)
-  const size_t budget = 220 * 1024;      // 227 KB per CTA minus ~5 KB of static shared memory (reduction buffers)
+  const size_t budget = 218 * 1024;      // 227 KB per CTA minus ~7 KB of static shared memory (reduction buffers, residual slice)
   if (fixed_out) *fixed_out = fixed;
   if (fixed + 4 * (MG_STAGE_BYTES + 16) > budget) return 0;
   int stages = (int)((budget - fixed) / (MG_STAGE_BYTES + 16));
@@ -737,27 +939,30 @@ static int mega_ring_stages(int M, int H, int F, int nh, int nkv, int hd, size_t
 // 1 or 2 K passes for w2: two when the batch is > 4, one pass does not fit, and the CTA's rows fit the carry buffer
 static int mega_w2_passes(int M, int H, int F, int nh, int nkv, int hd, int num_sms) {
   const char* force = getenv("JLLAMA_MEGA_W2_PASSES");       // tests: force the two-pass walk at small shapes
-  const bool rows_ok = ((H / MG_GROUP + num_sms - 1) / num_sms) * MG_GROUP <= 64 && F > MG_KS;
+  const bool rows_ok = F > MG_KS;
   if (M <= 4 || !rows_ok) return 1;
   if (force && atoi(force) == 2) return 2;
   if (mega_ring_stages(M, H, F, nh, nkv, hd, nullptr, 1) >= 4) return 1;
   return mega_ring_stages(M, H, F, nh, nkv, hd, nullptr, 2) >= 4 ? 2 : 1;
 }
+static bool mega_rows_fit(int H, int num_sms) {
+  return ((H / MG_GROUP + num_sms - 1) / num_sms) * MG_GROUP <= MG_MAX_OWN;       // residual slice of one CTA
+}
 extern "C" JL_API int jl_decode_mega_stages(int M, int H, int F, int nh, int nkv, int hd) {
-  if (M < 1 || M > 8 || hd != MG_HD || nkv <= 0 || nh % nkv) return 0;
+  if (M < 1 || M > 8 || hd != MG_HD || nkv <= 0 || nh % nkv || !mega_rows_fit(H, 148)) return 0;
   return mega_ring_stages(M, H, F, nh, nkv, hd, nullptr, mega_w2_passes(M, H, F, nh, nkv, hd, 148));
 }
 
 // One decode step of the whole model for M <= 8 rows.  Weight pointers are the per-op stacks [L·N, K].
 extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
                                      const void* lm_head, const void* attn_norm, const void* ffn_norm,
-                                     const void* final_norm, const void* embedding, const int* ids, void* x, void* qkv,
-                                     void* attn, void* hmlp, float* logits, void* k_cache, void* v_cache,
-                                     const float* cos_t, const float* sin_t, const int* cache_len, const int* pad_left,
-                                     void* scratch, int M, int L, int H, int F, int V, int vocab_full, int nh, int nkv,
-                                     int hd, int T, int max_pos, float eps, float scale, int num_sms, int tp, int rank,
-                                     void* const* peer_inbox, void* const* peer_flags, size_t inbox_parity_stride_floats,
-                                     int flag_offset, const int* seq_ptr, void* stream) {
+                                     const void* final_norm, const void* embedding, const int* ids, float* logits,
+                                     void* k_cache, void* v_cache, const float* cos_t, const float* sin_t,
+                                     const int* cache_len, const int* pad_left, void* scratch, unsigned int* gen, int M,
+                                     int L, int H, int F, int V, int vocab_full, int nh, int nkv, int hd, int T,
+                                     int max_pos, float eps, float scale, int num_sms, int tp, int rank,
+                                     void* const* peer_partials, void* mc_partials, void* const* peer_cand,
+                                     void* mc_cand, void* stream) {
   JL_CHECK_ARG(M >= 1 && M <= 8, "jl_decode_mega: M=%d outside 1..8", M);
   JL_CHECK_ARG(hd == MG_HD, "jl_decode_mega: head_dim=%d (only 128 is built)", hd);
   JL_CHECK_ARG(nkv > 0 && nh % nkv == 0, "jl_decode_mega: nh=%d not a multiple of nkv=%d", nh, nkv);
@@ -766,7 +971,11 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   const int NQKV = (nh + 2 * nkv) * hd;
   JL_CHECK_ARG(H % 256 == 0 && F % 256 == 0 && (nh * hd) % 256 == 0 && V % 8 == 0 && NQKV % 8 == 0,
                "jl_decode_mega: H=%d, F=%d and nh*hd must be multiples of 256, V=%d of 8", H, F, V);
+  JL_CHECK_ARG(gen != nullptr && scratch != nullptr, "jl_decode_mega: scratch and the step counter are required");
   if (num_sms <= 0) num_sms = 148;
+  JL_CHECK_ARG(mega_rows_fit(H, num_sms), "jl_decode_mega: H=%d gives a CTA more than %d residual rows on %d SMs", H,
+               MG_MAX_OWN, num_sms);
+  if (tp < 1) tp = 1;
   MegaTmaps tm;
   int rc;
   if ((rc = make_tmap_kblock_bf16(&tm.m[0], wqkv_all, (uint64_t)L * NQKV, H, H, MG_KS / 64, MG_GROUP))) return rc;
@@ -779,31 +988,22 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   p.eps = eps; p.scale_log2 = scale * 1.4426950408889634f;
   p.attn_norm = (const __nv_bfloat16*)attn_norm; p.ffn_norm = (const __nv_bfloat16*)ffn_norm;
   p.final_norm = (const __nv_bfloat16*)final_norm; p.embedding = (const __nv_bfloat16*)embedding;
-  p.ids = ids; p.x = (__nv_bfloat16*)x; p.qkv = (__nv_bfloat16*)qkv; p.attn = (__nv_bfloat16*)attn;
-  p.hmlp = (__nv_bfloat16*)hmlp; p.logits = logits; p.kc = (__nv_bfloat16*)k_cache; p.vc = (__nv_bfloat16*)v_cache;
-  p.cos_t = cos_t; p.sin_t = sin_t; p.cache_len = cache_len; p.pad_left = pad_left;
-  int splits = num_sms / (M * nkv);
-  if (splits > 64) splits = 64;
-  // a split shorter than one 128-key batch only adds partials to merge (tp = 8 has one KV head per rank:
-  // 148 candidate splits for a 2k context): cap by the cache capacity over one load batch
-  const int batch_keys = G <= 4 ? 128 : 64;           // keys one item handles per load batch (UNR x 64 in mg_attention_item)
-  if (splits > (T + batch_keys - 1) / batch_keys) splits = (T + batch_keys - 1) / batch_keys;
-  if (splits < 1) splits = 1;
-  p.splits = splits;
-  const size_t part_floats = (size_t)M * nh * splits * MG_HD;
-  p.o_part = (float*)scratch;
-  p.ml_part = p.o_part + part_floats;
-  p.tickets = (int*)(p.ml_part + (size_t)M * nh * splits * 2);
-  uintptr_t bp = (reinterpret_cast<uintptr_t>(p.tickets + M * nkv) + 15) & ~(uintptr_t)15;
-  p.bar_counter = reinterpret_cast<unsigned int*>(bp);
-  p.bar_gen = p.bar_counter + 1;
+  p.ids = ids; p.logits = logits; p.kc = (__nv_bfloat16*)k_cache; p.vc = (__nv_bfloat16*)v_cache;
+  p.cos_t = cos_t; p.sin_t = sin_t; p.cache_len = cache_len; p.pad_left = pad_left; p.gen = gen;
+  p.splits = mega_splits(M, nh, nkv, T, num_sms);
+  const MegaLayout lay = mega_layout(M, H, F, nh, nkv, num_sms);
+  uint8_t* sb = (uint8_t*)scratch;
+  p.r_pk = (uint2*)(sb + lay.r); p.qkv_pk = (uint2*)(sb + lay.qkv); p.part_pk = (uint2*)(sb + lay.part);
+  p.attn_pk = (uint2*)(sb + lay.attn); p.h_pk = (uint2*)(sb + lay.h);
   p.T = T; p.max_pos = max_pos;
-  p.ar.tp = tp < 1 ? 1 : tp; p.ar.rank = rank; p.ar.seq_ptr = seq_ptr; p.ar.parity_stride = inbox_parity_stride_floats;
-  p.ar.flag_offset = flag_offset;
-  if (p.ar.tp > 1) {
-    JL_CHECK_ARG(p.ar.tp <= 8 && peer_inbox && peer_flags && seq_ptr, "jl_decode_mega: tensor-parallel launch needs peer tables");
-    JL_CHECK_ARG((size_t)p.ar.tp * M * H * 2 <= inbox_parity_stride_floats, "jl_decode_mega: inbox too small for the all-reduce");
-    for (int i = 0; i < p.ar.tp; ++i) { p.ar.inbox[i] = (float*)peer_inbox[i]; p.ar.flags[i] = (int*)peer_flags[i]; }
+  p.ar.tp = tp; p.ar.rank = tp > 1 ? rank : 0;
+  if (tp > 1) {
+    JL_CHECK_ARG(tp <= 8 && rank >= 0 && rank < tp && peer_partials && peer_cand,
+                 "jl_decode_mega: tensor-parallel launch needs the peer tables of the packet buffers");
+    for (int i = 0; i < tp; ++i) { p.ar.p_peer[i] = (uint2*)peer_partials[i]; p.ar.cand_peer[i] = (uint2*)peer_cand[i]; }
+    p.ar.p_mc = (uint2*)mc_partials; p.ar.cand_mc = (uint2*)mc_cand;
+  } else {
+    p.ar.cand_peer[0] = (uint2*)(sb + lay.cand);
   }
   p.trace = g_mega_trace;
 
@@ -836,11 +1036,34 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   cfg.dynamicSmemBytes = smem;
   cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident: the grid barrier cannot deadlock
+  attr[0].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident: the packet polls cannot deadlock
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   count_launch();
   JL_CUDA(cudaLaunchKernelEx(&cfg, kern, tm, p));
+  return JL_OK;
+}
+
+// Greedy token of every batch row from the candidates of the decode kernel that just ran on this stream, plus the
+// sequence bookkeeping of jl_decode_advance.  `cand` = this rank's copy of the candidate packets (tp > 1: symmetric
+// heap; tp == 1: inside the scratch of jl_decode_mega, see jl_decode_mega_cand_offset).
+extern "C" JL_API size_t jl_decode_mega_cand_offset(int M, int H, int F, int nh, int nkv, int num_sms) {
+  if (num_sms <= 0) num_sms = 148;
+  return mega_layout(M, H, F, nh, nkv, num_sms).cand;
+}
+extern "C" JL_API int jl_mega_select(const void* cand, const unsigned int* gen, int tp, int rank, int num_sms, int M, int L,
+                                     int* tok, int* next_ids, int* finished, int* sequences, int max_len, int eos,
+                                     int pad, int* cur_len, int* cache_len, int* step, int* n_unfinished, void* stream) {
+  JL_CHECK_ARG(cand && gen && M >= 1 && M <= 8 && tp >= 1 && tp <= 8, "jl_mega_select: bad arguments");
+  if (num_sms <= 0) num_sms = 148;
+  SelectParams p{};
+  p.cand = (const uint2*)cand; p.gen = gen; p.tp = tp; p.grid = num_sms; p.M = M; p.two_l = 2 * L; p.rank = rank;
+  p.tok = tok; p.next_ids = next_ids; p.finished = finished; p.sequences = sequences;
+  p.max_len = max_len; p.eos = eos; p.pad = pad;
+  p.cur_len = cur_len; p.cache_len = cache_len; p.step = step; p.n_unfinished = n_unfinished;
+  count_launch();
+  mega_select_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(p);
+  JL_CUDA(cudaGetLastError());
   return JL_OK;
 }

@@ -15,8 +15,11 @@
 // canonical K-major swizzled tile, so each ldmatrix 8x8 fetch (8 rows x 16 B) is bank-conflict free.
 // Consumer warp w owns k in [128 w, 128 w + 128) of every stage: 8 k16-steps = 4 ldmatrix.x4 + 8 MMAs, two
 // independent accumulator chains.  The activation fragments are read from a PERMUTED copy of x in shared
-// memory (written once per op by mg_stage_input_mma) in which the 16 words a thread needs for one stage are
+// memory (written once per op by the staging functions) in which the 16 words a thread needs for one stage are
 // contiguous: 4 LDS.128 per stage.  Partial sums of the 8 warps meet in shared memory once per 8-row group.
+//
+// Activations travel between CTAs as TAGGED PACKETS (see decode_mega.cu): the epilogues below write
+// {bf16 pair, tag} 8-byte words and the staging functions poll them, so no grid-wide barrier separates the ops.
 #pragma once
 
 namespace jl {
@@ -42,33 +45,14 @@ __device__ __forceinline__ int mg_xperm_word(int m, int n_ks, int k) {
   return ((((m * n_ks + ks) * 8 + w) * 4 + t) << 4) + s * 2 + half;
 }
 
-// stage [M, K] activations (optional RMSNorm) into the permuted layout; positions k >= K are zero
+// second half of a staging pass: RMSNorm scale of what pass one left in shared memory (ss = this thread's partial
+// sums of squares per batch row), then the barrier that publishes the staged activations to all consumer warps
 template <int M>
-__device__ __forceinline__ void mg_stage_input_mma(MegaCtx& c, const __nv_bfloat16* src, int K,
-                                                   const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS],
-                                                   int ld = 0) {
-  // `ld` = row pitch of src in elements when only a K-range [src, src + K) of wider rows is staged (two-pass w2)
+__device__ __forceinline__ void mg_stage_finish(MegaCtx& c, int K, const __nv_bfloat16* norm_w, float eps,
+                                                float (*red)[MG_CONSUMERS], float (&ss)[M]) {
   const int ct = threadIdx.x - 32, lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
   const int K8 = K >> 3, n_ks = (K + MG_KS - 1) / MG_KS;
-  const int LD8 = ld > 0 ? ld >> 3 : K8;
   uint32_t* xw = reinterpret_cast<uint32_t*>(c.xin);
-  float ss[M];
-#pragma unroll
-  for (int m = 0; m < M; ++m) ss[m] = 0.f;
-  for (int i = ct; i < n_ks * (MG_KS / 8); i += MG_CT) {
-#pragma unroll
-    for (int m = 0; m < M; ++m) {
-      const uint4 a = i < K8 ? ldcg16(src + ((size_t)m * LD8 + i) * 8) : make_uint4(0, 0, 0, 0);
-      const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
-      const int base = mg_xperm_word(m, n_ks, i * 8);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        xw[base + j * 16] = aw[j];                       // pair j of the chunk belongs to quad lane t = j
-        const float lo = bf16_lo(aw[j]), hi = bf16_hi(aw[j]);
-        ss[m] += lo * lo + hi * hi;
-      }
-    }
-  }
   if (norm_w != nullptr) {
 #pragma unroll
     for (int m = 0; m < M; ++m) {
@@ -91,7 +75,7 @@ __device__ __forceinline__ void mg_stage_input_mma(MegaCtx& c, const __nv_bfloat
         const int base = mg_xperm_word(m, n_ks, i * 8);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const uint32_t a = xw[base + j * 16];          // written by this same thread above
+          const uint32_t a = xw[base + j * 16];
           xw[base + j * 16] = pack_bf16(bf16_lo(a) * rinv[m] * bf16_lo(gw[j]), bf16_hi(a) * rinv[m] * bf16_hi(gw[j]));
         }
       }
@@ -100,11 +84,107 @@ __device__ __forceinline__ void mg_stage_input_mma(MegaCtx& c, const __nv_bfloat
   mg_consumer_bar();
 }
 
+// stage the embedding rows of this step's tokens (first layer only; optional RMSNorm); positions k >= K are zero
+template <int M>
+__device__ __forceinline__ void mg_stage_embedding(MegaCtx& c, const __nv_bfloat16* table, const int* ids, int vocab,
+                                                   int K, const __nv_bfloat16* norm_w, float eps,
+                                                   float (*red)[MG_CONSUMERS]) {
+  const int ct = threadIdx.x - 32;
+  const int K8 = K >> 3, n_ks = (K + MG_KS - 1) / MG_KS;
+  uint32_t* xw = reinterpret_cast<uint32_t*>(c.xin);
+  float ss[M];
+  const uint4* rows[M];
+#pragma unroll
+  for (int m = 0; m < M; ++m) {
+    ss[m] = 0.f;
+    int id = ids[m];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    rows[m] = reinterpret_cast<const uint4*>(table) + (size_t)id * K8;
+  }
+  for (int i = ct; i < n_ks * (MG_KS / 8); i += MG_CT) {
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      const uint4 a = i < K8 ? __ldg(rows[m] + i) : make_uint4(0, 0, 0, 0);
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+      const int base = mg_xperm_word(m, n_ks, i * 8);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        xw[base + j * 16] = aw[j];                       // pair j of the chunk belongs to quad lane t = j
+        const float lo = bf16_lo(aw[j]), hi = bf16_hi(aw[j]);
+        ss[m] += lo * lo + hi * hi;
+      }
+    }
+  }
+  mg_stage_finish<M>(c, K, norm_w, eps, red, ss);
+}
+
+// Stage [M, K] activations that arrive as tagged packets {bf16 pair, tag} (row pitch `ldp` packets): every thread
+// polls the packets it stages until their tag is `tag` — this poll IS the synchronisation with the producers of
+// the previous op (all CTAs of this GPU), there is no grid barrier.  Up to 4 16-byte loads (8 packets) are in
+// flight per thread.  Optional RMSNorm; positions k >= K are zero.
+template <int M>
+__device__ __forceinline__ void mg_stage_packets(MegaCtx& c, const uint2* pk, uint32_t tag, int K, int ldp,
+                                                 const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS],
+                                                 int what) {
+  const int ct = threadIdx.x - 32;
+  const int n_ks = (K + MG_KS - 1) / MG_KS, K4 = K >> 2;
+  uint32_t* xw = reinterpret_cast<uint32_t*>(c.xin);
+  float ss[M];
+#pragma unroll
+  for (int m = 0; m < M; ++m) ss[m] = 0.f;
+  // item q = it * M + m covers values k = 4 i .. 4 i + 3 of row m, i = ct + it * MG_CT (exactly n_ks items per row)
+  const int items = n_ks * M;
+  for (int q0 = 0; q0 < items; q0 += 4) {
+    uint4 v[4];
+    const uint4* src[4];
+    bool need[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int q = q0 + u, it = q / M, m = q - it * M, i = ct + it * MG_CT;
+      need[u] = q < items && i < K4;
+      src[u] = reinterpret_cast<const uint4*>(pk + (size_t)m * ldp) + i;
+      v[u] = need[u] ? ld_relaxed_gpu_v4(src[u]) : make_uint4(0, tag, 0, tag);
+    }
+    unsigned spins = 0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      while (v[u].y != tag || v[u].w != tag) {
+        v[u] = ld_relaxed_gpu_v4(src[u]);
+        if (++spins > (1u << 24)) mg_poll_timeout(what, tag, v[u].y);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int q = q0 + u, it = q / M, m = q - it * M, i = ct + it * MG_CT;
+      if (q < items) {
+        xw[mg_xperm_word(m, n_ks, i * 4)] = v[u].x;
+        xw[mg_xperm_word(m, n_ks, i * 4 + 2)] = v[u].z;
+        const float a = bf16_lo(v[u].x), b = bf16_hi(v[u].x), d = bf16_lo(v[u].z), e = bf16_hi(v[u].z);
+        ss[m] += a * a + b * b + d * d + e * e;
+      }
+    }
+  }
+  mg_stage_finish<M>(c, K, norm_w, eps, red, ss);
+}
+
+// What the epilogue of a GEMV does with a finished 8-row group (see decode_mega.cu for the packet buffers)
+struct MegaOut {
+  uint2* pk;                // MG_PLAIN / MG_SWIGLU: packet buffer [M][N/2] ({bf16 pair, tag})
+  uint2* r_pk;              // MG_RESIDUAL: packets of the new residual stream [M][H/2]
+  float* logits;            // MG_LOGITS: optional fp32 [M][N] (may be null: candidates only)
+  float (*res)[64];         // MG_RESIDUAL: this CTA's rows of the residual stream (shared memory, bf16-exact values)
+  float* best_v;            // MG_LOGITS: running (max, argmax) of this thread's rows
+  int* best_i;
+  uint32_t tag;
+  int row0;                 // first row of this CTA's range (index base of `res`)
+  int idx_offset;           // MG_LOGITS: global vocabulary index of local row 0
+};
+
 // CARRY (two-pass GEMV over K, used when M rows of the full input do not fit in shared memory): 1 = this call
 // covers the first K range and parks its sums in `carry` ([M][64] floats, this CTA's rows); 2 = this call covers
 // the rest, adds the parked sums and runs the epilogue.  0 = ordinary single pass.
 template <int M, int MODE, int CARRY = 0>
-__device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, void* out, const __nv_bfloat16* residual,
+__device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, const MegaOut& o,
                                             float (*s_acc)[MG_CONSUMERS][MG_MMA_MAX_M][8], float (*carry)[64] = nullptr) {
   static_assert(M <= MG_MMA_MAX_M, "batch rows ride in the first 8 rows of the MMA M dimension");
   const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1, ct = threadIdx.x - 32;
@@ -152,35 +232,54 @@ __device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, void* out,
     if (has_row) *reinterpret_cast<float2*>(&buf[cw][g][2 * t]) = make_float2(d0[0] + d1[0], d0[1] + d1[1]);
     mg_consumer_bar();
     if constexpr (MODE == MG_SWIGLU) {
-      if (ct < M * 4) {                                  // one thread per (batch row, (gate, up) pair)
+      if (ct < 32) {                                     // one thread per (batch row, (gate, up) pair); whole warp for the shuffle
         const int m = ct >> 2, pp = ct & 3;
-        float gate = 0.f, up = 0.f;
+        float h = 0.f;
+        if (m < M) {
+          float gate = 0.f, up = 0.f;
 #pragma unroll
-        for (int w = 0; w < MG_CONSUMERS; ++w) { gate += buf[w][m][2 * pp]; up += buf[w][m][2 * pp + 1]; }
-        gate = __bfloat162float(__float2bfloat16(gate));
-        up = __bfloat162float(__float2bfloat16(up));
-        reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * (N / 2) + grp * (MG_GROUP / 2) + pp] =
-            __float2bfloat16(silu(gate) * up);
+          for (int w = 0; w < MG_CONSUMERS; ++w) { gate += buf[w][m][2 * pp]; up += buf[w][m][2 * pp + 1]; }
+          gate = __bfloat162float(__float2bfloat16(gate));
+          up = __bfloat162float(__float2bfloat16(up));
+          h = silu(gate) * up;
+        }
+        const float h1 = __shfl_down_sync(0xffffffffu, h, 1);
+        if (m < M && (pp & 1) == 0)
+          st_packet(o.pk + (size_t)m * (N / 4) + ((grp * (MG_GROUP / 2) + pp) >> 1), pack_bf16(h, h1), o.tag);
       }
     } else {
-      if (ct < M * 8) {
+      if (ct < 64) {                                     // thread (batch row m, weight row n); two whole warps
         const int m = ct >> 3, n = ct & 7;
+        const bool valid = m < M;
         float v = 0.f;
+        if (valid) {
 #pragma unroll
-        for (int w = 0; w < MG_CONSUMERS; ++w) v += buf[w][m][n];
+          for (int w = 0; w < MG_CONSUMERS; ++w) v += buf[w][m][n];
+        }
         const int row = grp * MG_GROUP + n;
         if constexpr (CARRY == 1) {
-          carry[m][(grp - g0) * MG_GROUP + n] = v;         // read back by this same thread in the second pass
+          if (valid) carry[m][(grp - g0) * MG_GROUP + n] = v;       // read back by this same thread in the second pass
         } else if constexpr (MODE == MG_LOGITS) {
-          reinterpret_cast<float*>(out)[(size_t)m * N + row] = v;
-        } else {
-          bool pushed = false;
-          if constexpr (CARRY == 2) v += carry[m][(grp - g0) * MG_GROUP + n];
-          if constexpr (MODE == MG_RESIDUAL) {
-            if (c.ar->tp > 1) { mg_push_partial<M>(c, m, row, N, v); pushed = true; }     // reduced in mg_ar_finish
-            else v = __bfloat162float(__float2bfloat16(v)) + __bfloat162float(__ldcg(residual + (size_t)m * N + row));
+          if (valid) {
+            if (o.logits != nullptr) o.logits[(size_t)m * N + row] = v;
+            if (v > *o.best_v) { *o.best_v = v; *o.best_i = row + o.idx_offset; }      // rows ascend: ties keep the lower index
           }
-          if (!pushed) reinterpret_cast<__nv_bfloat16*>(out)[(size_t)m * N + row] = __float2bfloat16(v);
+        } else if constexpr (MODE == MG_RESIDUAL) {
+          if constexpr (CARRY == 2) { if (valid) v += carry[m][(grp - g0) * MG_GROUP + n]; }
+          if (c.ar->tp > 1) {
+            if (valid) mg_push_partial<M>(c, m, row, N, v);          // reduced over ranks in mg_owner_reduce
+          } else {
+            float y = 0.f;
+            if (valid) {
+              y = __bfloat162float(__float2bfloat16(__bfloat162float(__float2bfloat16(v)) + o.res[m][row - o.row0]));
+              o.res[m][row - o.row0] = y;
+            }
+            const float y1 = __shfl_down_sync(0xffffffffu, y, 1);
+            if (valid && (n & 1) == 0) st_packet(o.r_pk + (size_t)m * (N / 2) + (row >> 1), pack_bf16(y, y1), o.tag);
+          }
+        } else {
+          const float v1 = __shfl_down_sync(0xffffffffu, v, 1);
+          if (valid && (n & 1) == 0) st_packet(o.pk + (size_t)m * (N / 2) + (row >> 1), pack_bf16(v, v1), o.tag);
         }
       }
     }

@@ -129,25 +129,37 @@ int jl_decode_advance(const int* tok, int* next_ids, int* finished, int* sequenc
 /* ---------------------------------------------------------------------------------------------------------
  * Whole-model decode step (model.py:743-790 at S=1, i.e. everything FlaxLLaMAForCausalLMModule.__call__ does
  * for one new token) in ONE persistent cooperative kernel for M <= 8 rows: embedding, L x (RMSNorm+wqkv, RoPE,
- * cache append, GQA attention, wo+residual, RMSNorm+w13+SwiGLU, w2+residual), final norm and LM head.
- * Weights are the per-op stacks [L*N, K]; x/qkv/attn/hmlp are bf16 activations the kernel uses between
- * phases; logits fp32 [M, V] (V = this rank's vocab shard, vocab_full the whole vocabulary); scratch must hold
- * jl_decode_mega_scratch_bytes() bytes and be ZERO when first used.  Needs a cooperative launch of one CTA
- * per SM (num_sms CTAs must be co-resident).  With tp > 1 the wo / w2 outputs are all-reduced inside the kernel
- * over the peer inboxes (tagged 8-byte packets; partition.py:67,70 is what GSPMD all-reduced there) and the
- * caller advances the epoch counter behind seq_ptr by 2*L per step (jl_comm_bump; see parallel/comm.py). */
-int jl_decode_mega_barriers(int L);
-size_t jl_decode_mega_scratch_bytes(int M, int nh, int nkv, int num_sms);
+ * cache append, GQA attention, wo+residual, RMSNorm+w13+SwiGLU, w2+residual), final norm and LM head with a
+ * running arg-max.  Weights are the per-op stacks [L*N, K].  There is no grid barrier: activations cross CTAs as
+ * tagged 8-byte packets that consumers poll (csrc/decode_mega.cu).  `scratch` holds the packet buffers
+ * (jl_decode_mega_scratch_bytes() bytes, ZERO when first used, never cleared afterwards); `gen` is a device
+ * counter of the steps this engine has run (zero at start; the kernel advances it; it is the tag base, so every
+ * scratch / peer buffer ever used with it must only be used with it).  `logits` fp32 [M, V] (V = this rank's
+ * vocab shard, vocab_full the whole vocabulary) may be NULL: then only the per-CTA arg-max candidates are
+ * produced (read by jl_mega_select).  Needs a cooperative launch of one CTA per SM (num_sms CTAs co-resident).
+ * With tp > 1 the wo / w2 outputs are all-reduced inside the kernel (partition.py:67,70 is what GSPMD
+ * all-reduced there): fp32 partial packets go to every rank with one multimem.st on `mc_partials` (the NVLS
+ * multicast address of the symmetric buffer whose per-rank mappings are `peer_partials`; NULL = one unicast
+ * store per peer), candidates likewise through `peer_cand` / `mc_cand`; sizes from jl_decode_mega_peer_bytes. */
+size_t jl_decode_mega_scratch_bytes(int M, int H, int F, int nh, int nkv, int num_sms);
+size_t jl_decode_mega_cand_offset(int M, int H, int F, int nh, int nkv, int num_sms);   /* tp == 1: candidates inside scratch */
+size_t jl_decode_mega_peer_bytes(int M, int H, int tp, int num_sms, size_t* cand_offset);
 int jl_decode_mega_stages(int M, int H, int F, int nh, int nkv, int hd); /* weight-ring depth; 0 = shape does not fit */
 void jl_decode_mega_set_trace(void* buf /* device u64 [num_sms][L][32] %globaltimer stamps, NULL = off */);
 int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
                    const void* lm_head, const void* attn_norm, const void* ffn_norm, const void* final_norm,
-                   const void* embedding, const int* ids, void* x, void* qkv, void* attn, void* hmlp,
-                   float* logits, void* k_cache, void* v_cache, const float* cos_t, const float* sin_t,
-                   const int* cache_len, const int* pad_left, void* scratch, int M, int L, int H, int F, int V,
-                   int vocab_full, int nh, int nkv, int hd, int T, int max_pos, float eps, float scale,
-                   int num_sms, int tp, int rank, void* const* peer_inbox, void* const* peer_flags,
-                   size_t inbox_parity_stride_floats, int flag_offset, const int* seq_ptr, void* stream);
+                   const void* embedding, const int* ids, float* logits, void* k_cache, void* v_cache,
+                   const float* cos_t, const float* sin_t, const int* cache_len, const int* pad_left, void* scratch,
+                   unsigned int* gen, int M, int L, int H, int F, int V, int vocab_full, int nh, int nkv, int hd,
+                   int T, int max_pos, float eps, float scale, int num_sms, int tp, int rank,
+                   void* const* peer_partials, void* mc_partials, void* const* peer_cand, void* mc_cand,
+                   void* stream);
+/* HF _greedy_search body (generation.py:28-41 with temperature 0) for the step jl_decode_mega just ran on this
+ * stream: merges the num_sms x tp arg-max candidates per row (ties: lower vocabulary index; waits for ranks whose
+ * kernel is still finishing), then the bookkeeping of jl_decode_advance.  `cand` = this rank's candidate packets. */
+int jl_mega_select(const void* cand, const unsigned int* gen, int tp, int rank, int num_sms, int M, int L, int* tok,
+                   int* next_ids, int* finished, int* sequences, int max_len, int eos, int pad, int* cur_len,
+                   int* cache_len, int* step, int* n_unfinished, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Tensor parallelism over NVLink peer memory (partition.py:62-78 names the sharding; XLA/GSPMD inserted NCCL

@@ -122,6 +122,10 @@ class B200Engine:
         self._decode_states: Dict[Tuple[int, int], DecodeState] = {}
         self.warned_slow_prefill = False
         self._mega_fit_cache: Dict[int, bool] = {}
+        # step counter of the whole-step decode kernel: the base of its packet tags (never reset, see decode_mega.cu)
+        self._mega_gen = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._mega_peer: Optional[Tuple] = None
+        self.mega_write_logits = False      # True: the decode kernel also stores the fp32 [B, V] logits (tests, forward-style use)
         if self.device.type == "cuda":
             K.ensure_gemm_workspace(self.device)          # split-K scratch of the small-batch GEMMs (before any capture)
         # Prefill at tp > 1.  Measured on 8xB200, LLaMA-3 8B, 2048 tokens (ms): fused sequence-parallel chain
@@ -146,13 +150,23 @@ class B200Engine:
         return self._mega_fit_cache[batch]
 
     def _mega_tp_args(self) -> Tuple:
-        """(tp, rank, peer inbox table, peer flag table, parity stride in floats, flag offset, epoch counter)."""
+        """(tp, rank, peer table of the partial-sum packets, its multicast address, peer table of the arg-max
+        candidates, its multicast address).  The two buffers live in a symmetric heap (parallel/symm.py) sized for
+        the largest batch the kernel takes; allocated once, before any graph capture."""
         if self.tp == 1:
-            return (1, 0, None, None, 0, 0, None)
-        cm = self.comm
-        grid = K.num_sms(self.device)
-        off = cm.flag_block(("mega", grid), 8 * grid)
-        return (self.tp, self.rank, cm.inbox_ptrs, cm.flag_ptrs, cm.parity_bytes // 4, off, cm.seq.data_ptr())
+            return (1, 0, None, None, None, None)
+        if self._mega_peer is None:
+            import ctypes as C
+            from ..parallel.symm import SymmetricHeap
+            L = _lib.lib()
+            cand_off = C.c_size_t(0)
+            nbytes = int(L.jl_decode_mega_peer_bytes(8, self.config.hidden_size, self.tp, K.num_sms(self.device),
+                                                     C.byref(cand_off)))
+            heap = SymmetricHeap(self.tp, self.rank, self.device, nbytes, group=getattr(self.comm, "group", None))
+            self._mega_peer = (heap, heap.peer_table(0), heap.mc(0), heap.peer_table(cand_off.value),
+                               heap.mc(cand_off.value), heap.local_ptr + cand_off.value)
+        _, p_tab, p_mc, c_tab, c_mc, _ = self._mega_peer
+        return (self.tp, self.rank, p_tab, p_mc or None, c_tab, c_mc or None)
 
     def _stack_weights(self) -> None:
         """Store each op's weights of all layers contiguously ([L·N, K]); the per-layer tensors become views.
@@ -201,23 +215,42 @@ class B200Engine:
 
     @classmethod
     def random_init(cls, config: LLaMAConfig, device: Any = "cuda", seed: int = 0, **kw: Any) -> "B200Engine":
-        """Random weights generated directly in kernel layout on the device (benchmarks; no host copy)."""
+        """Random weights generated directly in kernel layout on the device (benchmarks; no host copy).
+
+        Every rank draws the FULL matrices from the same generator and keeps its Megatron slice (rows of wqkv /
+        w13 / lm_head, columns of wo / w2 — parallel/layout.py), so a tensor-parallel engine and a single-GPU
+        engine built with the same seed are the same model: `bench.py` uses that for its pre-run `tp_check`."""
         dev = torch.device(device)
         tp, rank = int(kw.get("tp", 1)), int(kw.get("rank", 0))
-        g = torch.Generator(device=dev).manual_seed(seed * 1000 + rank)
+        g = torch.Generator(device=dev).manual_seed(seed * 1000)
         std = config.initializer_range
-        h, f, v = config.hidden_size, config.intermediate_size // tp, config.vocab_size // tp
-        nh, nkv, hd = config.num_attention_heads // tp, config.num_key_value_heads // tp, config.head_dim
+        h, F, V = config.hidden_size, config.intermediate_size, config.vocab_size
+        NH, NKV, hd = config.num_attention_heads, config.num_key_value_heads, config.head_dim
+        f, v, nh, nkv = F // tp, V // tp, NH // tp, NKV // tp
 
-        def mat(n: int, k: int) -> torch.Tensor:
-            return (torch.randn(n, k, generator=g, device=dev, dtype=torch.float32) * std).to(torch.bfloat16)
+        def full(n: int, k: int) -> torch.Tensor:
+            return torch.randn(n, k, generator=g, device=dev, dtype=torch.float32) * std
+
+        def rows(t: torch.Tensor, n: int) -> torch.Tensor:
+            return t[rank * n:(rank + 1) * n].to(torch.bfloat16).contiguous()
+
+        def cols(t: torch.Tensor, n: int) -> torch.Tensor:
+            return t[:, rank * n:(rank + 1) * n].to(torch.bfloat16).contiguous()
 
         ones = lambda: torch.ones(h, dtype=torch.bfloat16, device=dev)     # noqa: E731
-        layers = [LayerWeights(ones(), mat((nh + 2 * nkv) * hd, h), mat(h, nh * hd), ones(), mat(2 * f, h),
-                               mat(h, f)) for _ in range(config.num_hidden_layers)]
+        layers = []
+        for _ in range(config.num_hidden_layers):
+            wqkv = full((NH + 2 * NKV) * hd, h)
+            q, k_, v_ = wqkv[:NH * hd], wqkv[NH * hd:(NH + NKV) * hd], wqkv[(NH + NKV) * hd:]
+            wqkv_r = torch.cat([rows(q, nh * hd), rows(k_, nkv * hd), rows(v_, nkv * hd)], 0)
+            del wqkv, q, k_, v_
+            wo = cols(full(h, NH * hd), nh * hd)
+            w13 = rows(full(2 * F, h), 2 * f)                  # (w1_j, w3_j) rows interleaved: a slice of 2f rows is f pairs
+            w2 = cols(full(h, F), f)
+            layers.append(LayerWeights(ones(), wqkv_r, wo, ones(), w13, w2))
         ge = torch.Generator(device=dev).manual_seed(seed * 1000 + 999)      # same table on every rank
-        emb = (torch.randn(config.vocab_size, h, generator=ge, device=dev, dtype=torch.float32) * std).to(torch.bfloat16)
-        head = emb if (config.tie_word_embeddings and tp == 1) else mat(v, h)
+        emb = (torch.randn(V, h, generator=ge, device=dev, dtype=torch.float32) * std).to(torch.bfloat16)
+        head = emb if (config.tie_word_embeddings and tp == 1) else rows(full(V, h), v)
         return cls(config, emb, layers, ones(), head, **kw)
 
     def to_tree(self) -> Tree:
@@ -490,23 +523,38 @@ class B200Engine:
         if self.comm is not None:
             self.comm.begin_sequence()
         if self._mega_fits(st.B):
-            # whole model in one persistent kernel: embedding → L layers → final norm → LM head
+            # whole model in one persistent kernel: embedding → L layers → final norm → LM head (+ running arg-max)
             L = _lib.lib()
+            sms = K.num_sms(self.device)
+            shape = (st.B, c.hidden_size, c.intermediate_size // self.tp, self.nh, self.nkv, sms)
             if getattr(st, "mega_scratch", None) is None:
-                nbytes = int(L.jl_decode_mega_scratch_bytes(st.B, self.nh, self.nkv, K.num_sms(self.device)))
+                nbytes = int(L.jl_decode_mega_scratch_bytes(*shape))
                 st.mega_scratch = torch.zeros((nbytes + 3) // 4, dtype=torch.int32, device=self.device)
+                st.mega_cand = st.mega_scratch.data_ptr() + int(L.jl_decode_mega_cand_offset(*shape))
+            do_sample = bool(sampling[0])
+            want_logits = do_sample or self.mega_write_logits
             _lib.check(L.jl_decode_mega(
                 self.wqkv_all.data_ptr(), self.wo_all.data_ptr(), self.w13_all.data_ptr(), self.w2_all.data_ptr(),
                 self.lm_head.data_ptr(), self.attn_norm_all.data_ptr(), self.ffn_norm_all.data_ptr(),
-                self.final_norm.data_ptr(), self.embedding.data_ptr(), st.ids.data_ptr(), st.x.data_ptr(),
-                st.qkv.data_ptr(), st.attn.data_ptr(), st.mlp.data_ptr(), st.logits.data_ptr(),
+                self.final_norm.data_ptr(), self.embedding.data_ptr(), st.ids.data_ptr(),
+                st.logits.data_ptr() if want_logits else None,
                 cache.k.data_ptr(), cache.v.data_ptr(), self.cos.data_ptr(), self.sin.data_ptr(),
-                cache.len_dev.data_ptr(), cache.pad_left.data_ptr(), st.mega_scratch.data_ptr(), st.B,
+                cache.len_dev.data_ptr(), cache.pad_left.data_ptr(), st.mega_scratch.data_ptr(),
+                self._mega_gen.data_ptr(), st.B,
                 len(self.layers), c.hidden_size, c.intermediate_size // self.tp, self.v_local, c.vocab_size,
                 self.nh, self.nkv, self.hd, cache.capacity, self.cos.shape[0], float(c.rms_norm_eps),
-                1.0 / (self.hd ** 0.5), K.num_sms(self.device), *self._mega_tp_args(), K._stream()), "jl_decode_mega")
-            if self.tp > 1:
-                self.comm.call_index += 2 * len(self.layers)      # the kernel ran 2 all-reduces per layer
+                1.0 / (self.hd ** 0.5), sms, *self._mega_tp_args(), K._stream()), "jl_decode_mega")
+            if not do_sample:
+                # greedy: the kernel left one candidate per CTA (and rank); merge + bookkeeping in one launch
+                cand = st.mega_cand if self.tp == 1 else self._mega_peer[5]
+                _lib.check(L.jl_mega_select(
+                    cand, self._mega_gen.data_ptr(), self.tp, self.rank, sms, st.B, len(self.layers),
+                    st.tok.data_ptr(), st.ids.data_ptr(), st.finished.data_ptr(), st.sequences.data_ptr(), st.max_len,
+                    int(eos), int(pad), st.cur_len.data_ptr(), cache.len_dev.data_ptr(), st.step.data_ptr(),
+                    st.n_unfinished.data_ptr(), K._stream()), "jl_mega_select")
+                if self.comm is not None:
+                    self.comm.end_sequence()
+                return
         else:
             K.embed(st.ids, self.embedding, out=st.x)
             x = self._layers(st.x, st.B, 1, cache, None, ws=st)

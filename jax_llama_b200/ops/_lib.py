@@ -34,9 +34,13 @@ _SIGNATURES = {
     "jl_decode_attn_fused_scratch_bytes": (sz, [i32, i32, i32, i32, i32]),
     "jl_decode_attn_fused_splits": (i32, [i32, i32, i32, i32]),
     "jl_decode_attn_fused": (i32, [vp, vp, vp, fp, fp, ip, ip, vp, vp, i32, i32, i32, i32, i32, i32, f32, i32, vp]),
-    "jl_decode_mega_scratch_bytes": (sz, [i32, i32, i32, i32]),
-    "jl_decode_mega": (i32, [vp] * 9 + [ip] + [vp] * 4 + [fp, vp, vp, fp, fp, ip, ip, vp] + [i32] * 11 +
-                       [f32, f32, i32, i32, i32, vp, vp, sz, i32, ip, vp]),
+    "jl_decode_mega_scratch_bytes": (sz, [i32, i32, i32, i32, i32, i32]),
+    "jl_decode_mega_cand_offset": (sz, [i32, i32, i32, i32, i32, i32]),
+    "jl_decode_mega_peer_bytes": (sz, [i32, i32, i32, i32, vp]),
+    "jl_decode_mega": (i32, [vp] * 9 + [ip, fp, vp, vp, fp, fp, ip, ip, vp, vp] + [i32] * 11 +
+                       [f32, f32, i32, i32, i32, vp, vp, vp, vp, vp]),
+    "jl_mega_select": (i32, [vp, vp] + [i32] * 5 + [ip] * 4 + [i32] * 3 + [ip] * 4 + [vp]),
+    "jl_nvls_selftest": (i32, [vp, vp, vp, i32, i32, C.c_uint, vp]),
     "jl_argmax": (i32, [fp, i32, i32, i32, i32, fp, ip, vp]),
     "jl_topk": (i32, [fp, i32, i32, i32, i32, i32, fp, ip, vp]),
     "jl_sample": (i32, [fp, ip, i32, i32, sz, i32, i32, f32, f32, u64, ip, ip, vp]),

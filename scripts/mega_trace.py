@@ -40,21 +40,27 @@ tall = trace.view(NB, L, EV).cpu().double()
 t = tall[[0, NB - 1]]
 if rank != 0:
     sys.exit(0)
-names = ["stage_qkv", "gemv_qkv", "bar", "attn", "bar(+merge)", "stage_wo", "gemv_wo", "bar", "stage_w13", "gemv_w13",
-         "bar", "stage_w2", "gemv_w2", "bar"]
+names = ["stage_qkv(poll x)", "gemv_qkv", "attn(poll qkv)", "merge(poll parts)", "stage_wo(poll attn)", "gemv_wo(+AR)",
+         "stage_w13(poll x)", "gemv_w13", "stage_w2(poll h)", "gemv_w2(+AR)"]
 lo, hi = 4, L - 4
 for blk in range(2):
-    d = (t[blk, lo:hi, 1:15] - t[blk, lo:hi, 0:14]) / 1e3          # µs
+    d = (t[blk, lo:hi, 1:11] - t[blk, lo:hi, 0:10]) / 1e3          # µs
     print(f"block {'0' if blk == 0 else 'last'}: " + "  ".join(f"{n}={v:.1f}" for n, v in zip(names, d.mean(0).tolist())))
-    print(f"   layer total {((t[blk, lo:hi, 14] - t[blk, lo:hi, 0]) / 1e3).mean():.1f} us; layer-to-layer "
+    print(f"   layer total {((t[blk, lo:hi, 10] - t[blk, lo:hi, 0]) / 1e3).mean():.1f} us; layer-to-layer "
           f"{((t[blk, lo + 1:hi, 0] - t[blk, lo:hi - 1, 0]) / 1e3).mean():.1f} us")
-a = (t[0, lo:hi, 16:21] - t[0, lo:hi, 3:4]) / 1e3
+dall = (tall[:, lo:hi, 1:11] - tall[:, lo:hi, 0:10]) / 1e3         # [blocks, layers, phases]
+print("all blocks, mean over layers, then over blocks (min / p50 / max):")
+for i, n in enumerate(names):
+    m = dall[:, :, i].mean(1)
+    print(f"   {n:22s} {m.min():6.2f} {m.median():6.2f} {m.max():6.2f}")
+print(f"   layer total p50 {((tall[:, lo:hi, 10] - tall[:, lo:hi, 0]) / 1e3).mean(1).median():.1f} us")
+a = (t[0, lo:hi, 16:21] - t[0, lo:hi, 2:3]) / 1e3
 print("block 0 attention internals (µs after the phase starts): " + "  ".join(
     f"{n}={v:.1f}" for n, v in zip(["setup", "q+rope", "kv_loop", "new_tok", "fold+write"], a.mean(0).tolist())))
 
 # spread across blocks: when does each block finish each phase, relative to the earliest block entering it
-ends = {"gemv_qkv": 2, "attn": 4, "gemv_wo": 7, "gemv_w13": 10, "gemv_w2": 13}
-starts = {"gemv_qkv": 1, "attn": 3, "gemv_wo": 6, "gemv_w13": 9, "gemv_w2": 12}
+ends = {"gemv_qkv": 2, "attn": 3, "gemv_wo": 6, "gemv_w13": 8, "gemv_w2": 10}
+starts = {"gemv_qkv": 1, "attn": 2, "gemv_wo": 5, "gemv_w13": 7, "gemv_w2": 9}
 smid = tall[:, lo, 31].long()
 for n in ends:
     begin = tall[:, lo:hi, starts[n]].min(0).values                      # [layers]
