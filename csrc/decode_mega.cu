@@ -5,11 +5,11 @@
 // only ~50% of a 19 µs `wo` GEMV), and programmatic dependent launch does not recover it because the
 // streaming kernels fill the SM.  Here ONE cooperative kernel with one CTA per SM runs the entire step:
 //
-//   * warp 0 is a TMA producer that streams every weight matrix of the model, layer after layer, through a
+//   * warp 0 (of a 4-warp producer group, see MG_PWARPS) is a TMA producer that streams every weight matrix of the model, layer after layer, through a
 //     shared-memory ring: one 16 KB request per stage ([16 k-blocks][8 rows][128 B], 128-byte swizzle).  It
 //     depends on nothing but free ring slots, so it runs ahead across op boundaries: while the consumers poll
 //     for their inputs or do attention, the next op's weights are already landing.
-//   * warps 1..8 are consumers: RMSNorm + tensor-core GEMV (ldmatrix + mma.sync, see decode_mega_mma.cuh),
+//   * warps 4..11 are consumers: RMSNorm + tensor-core GEMV (ldmatrix + mma.sync, see decode_mega_mma.cuh),
 //     residual / SwiGLU epilogues, RoPE + KV append + split-KV GQA attention (one (batch, kv-head, split) item
 //     per CTA, merge spread over the grid), final norm + LM head with a running arg-max.
 //   * rows of each GEMV are cut into 148 contiguous, near-equal ranges (±1 group of 8 rows).
@@ -62,7 +62,18 @@
 namespace jl {
 
 constexpr int MG_CONSUMERS = 8;
-constexpr int MG_THREADS = (MG_CONSUMERS + 1) * 32;
+// Warp roles and registers.  The SM allocates registers per scheduler quarter, so a 9-warp CTA (8 consumers + 1
+// producer) caps EVERY thread at 168 registers (three warps share one quarter) and the consumers spilled inside the
+// GEMV loop.  The CTA is therefore three warpgroups: warps 0-3 = producer group (warp 0 lane 0 issues the TMA
+// stream, the others leave at once), warps 4-11 = consumers; `setmaxnreg` hands the producer group's registers to
+// the consumers right after start-up (56 vs 224 per thread; 56·128 + 224·256 = 64512 of the SM's 65536).
+#ifndef JL_MG_PWARPS
+#define JL_MG_PWARPS 4
+#endif
+constexpr int MG_PWARPS = JL_MG_PWARPS;            // warps of the producer warpgroup (1: no register hand-over)
+constexpr int MG_CT0 = MG_PWARPS * 32;             // first consumer thread
+constexpr int MG_THREADS = (MG_CONSUMERS + MG_PWARPS) * 32;
+constexpr int MG_PRODUCER_REGS = 56, MG_CONSUMER_REGS = 224;
 constexpr int MG_CT = MG_CONSUMERS * 32;           // consumer threads
 constexpr int MG_GROUP = 8;                        // weight rows per stage (one per consumer warp)
 constexpr int MG_KS = 1024;                        // K elements per stage
@@ -113,7 +124,7 @@ struct MegaParams {
 };
 
 enum { MG_PLAIN = 0, MG_RESIDUAL = 1, MG_SWIGLU = 2, MG_LOGITS = 3 };
-enum { MG_W_X = 0, MG_W_QKV = 1, MG_W_PART = 2, MG_W_ATTN = 3, MG_W_H = 4, MG_W_PEER = 5 };      // what a poll waits for
+enum { MG_W_X = 0, MG_W_QKV = 1, MG_W_PART = 2, MG_W_ATTN = 3, MG_W_H = 4, MG_W_PEER = 5, MG_W_X2 = 6 };      // what a poll waits for
 
 __device__ __forceinline__ void mg_consumer_bar() { asm volatile("bar.sync 1, %0;" ::"n"(MG_CT) : "memory"); }
 
@@ -151,7 +162,7 @@ __device__ __forceinline__ uint4 ld_relaxed_sys_v4(const uint4* p) {
 }
 
 __device__ __forceinline__ void mg_stamp(const MegaParams& p, int layer, int ev) {
-  if (p.trace != nullptr && threadIdx.x == 32) {
+  if (p.trace != nullptr && threadIdx.x == MG_CT0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     p.trace[((size_t)blockIdx.x * p.L + layer) * 32 + ev] = t;
@@ -163,10 +174,10 @@ __device__ __forceinline__ void mg_stamp(const MegaParams& p, int layer, int ev)
   }
 }
 
-// contiguous, near-equal split of `n` groups over the grid
+// contiguous, near-equal split of `n` groups over the grid (n * gridDim.x < 2^31 for every matrix here)
 __device__ __forceinline__ void mg_range(int n, int& g0, int& g1) {
-  g0 = (int)(((long long)n * blockIdx.x) / gridDim.x);
-  g1 = (int)(((long long)n * (blockIdx.x + 1)) / gridDim.x);
+  g0 = (int)(((unsigned)n * blockIdx.x) / gridDim.x);
+  g1 = (int)(((unsigned)n * (blockIdx.x + 1u)) / gridDim.x);
 }
 
 struct MegaCtx {
@@ -178,7 +189,16 @@ struct MegaCtx {
   int stage; uint32_t phase;  // ring cursor (producer and consumers keep separate copies)
   const MegaAr* ar;           // tensor-parallel state; ar_tag tags (and its parity places) the current all-reduce
   uint32_t ar_tag;
+  unsigned long long* trace_row;   // tracing: this block's stamp row of the current layer (null: off)
+  bool trace_on;
 };
+__device__ __forceinline__ void mg_stamp_raw(const MegaCtx& c, int ev) {
+  if (threadIdx.x == MG_CT0 && c.trace_row != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    c.trace_row[ev] = t;
+  }
+}
 
 // row-parallel epilogue under tensor parallelism: hand this rank's fp32 partial to every rank (itself included).
 // One 8-byte packet {value, tag}; the receiver polls the slot until the tag matches, so no flag, no fence and a
@@ -261,25 +281,28 @@ struct MegaCursor {
 #include "decode_mega_mma.cuh"
 namespace jl {
 
-// 8 consecutive bf16 of a packet row (4 packets = two 16-byte loads), polled until all four tags match
-struct MgPoll8 {
-  const uint4* src;
-  uint4 a, b;
-  __device__ __forceinline__ void issue(const uint2* pk) {
-    src = reinterpret_cast<const uint4*>(pk);
-    a = ld_relaxed_gpu_v4(src);
-    b = ld_relaxed_gpu_v4(src + 1);
-  }
-  __device__ __forceinline__ uint4 wait(uint32_t tag, int what) {
-    unsigned spins = 0;
-    while (a.y != tag || a.w != tag || b.y != tag || b.w != tag) {
-      a = ld_relaxed_gpu_v4(src);
-      b = ld_relaxed_gpu_v4(src + 1);
-      if (++spins > (1u << 24)) mg_poll_timeout(what, tag, a.y);
+// 8 consecutive bf16 of N packet rows (4 packets = two 16-byte loads each): all loads are issued, then all tags are
+// checked, and everything is fetched again until every tag matches (one L2 round trip once the data is there)
+template <int N>
+__device__ __forceinline__ void mg_poll8(const uint2* const (&pk)[N], uint32_t tag, int what, uint4 (&out)[N]) {
+  unsigned spins = 0;
+  for (;;) {
+    uint4 a[N], b[N];
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      a[i] = ld_relaxed_gpu_v4(reinterpret_cast<const uint4*>(pk[i]));
+      b[i] = ld_relaxed_gpu_v4(reinterpret_cast<const uint4*>(pk[i]) + 1);
     }
-    return make_uint4(a.x, a.z, b.x, b.z);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      ok = ok && a[i].y == tag && a[i].w == tag && b[i].y == tag && b[i].w == tag;
+      out[i] = make_uint4(a[i].x, a[i].z, b[i].x, b[i].z);
+    }
+    if (ok) return;
+    if (++spins > (1u << 22)) mg_poll_timeout(what, tag, a[0].y);
   }
-};
+}
 
 // RoPE + KV append + split-KV attention for one (b, kv head, split) item (8 consumer warps)
 struct MgPos { int len, first; float cs[4], sn[4]; };      // per-step constants of one batch row (this lane's pairs)
@@ -304,7 +327,7 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
   constexpr int HD = MG_HD, LPK = HD / 8, GPW = 32 / LPK, NG = MG_CONSUMERS * GPW;
   constexpr int KEYS_PER_ITER = NG * MG_KPI;
   const int nh = p.nkv * G;
-  const int lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) - 1, ct = threadIdx.x - 32;
+  const int lane = threadIdx.x & 31, warp = (threadIdx.x >> 5) - MG_PWARPS, ct = threadIdx.x - MG_CT0;
   const int lig = lane % LPK, gid = warp * GPW + lane / LPK, group_base = lane - lig;
   const int kidx = ((lig / (LPK / 2)) & 1) * 2 + ((lig / (LPK / 4)) & 1);
   float (*s_o)[G][HD] = reinterpret_cast<float (*)[G][HD]>(c.s_attn);
@@ -322,18 +345,24 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
   // q (all heads of the group) and the new token's k, v arrive as packets from the qkv GEMV of other CTAs
   const uint2* row = p.qkv_pk + (size_t)b * (p.NQKV / 2);
   const bool owns_new = split == 0 && warp == 0;      // consumes the new k, v after the KV loop
-  MgPoll8 pq[G], pk_new, pv_new;
+  uint4 qa[G];
+  {
+    const uint2* src[G];
 #pragma unroll
-  for (int g = 0; g < G; ++g) pq[g].issue(row + ((size_t)(kvh * G + g) * HD + lig * 8) / 2);
+    for (int g = 0; g < G; ++g) src[g] = row + ((size_t)(kvh * G + g) * HD + lig * 8) / 2;
+    mg_poll8<G>(src, tag, MG_W_QKV, qa);
+  }
+  uint4 ka = make_uint4(0, 0, 0, 0), va = ka;
   if (owns_new) {
-    pk_new.issue(row + ((size_t)(nh + kvh) * HD + lig * 8) / 2);
-    pv_new.issue(row + ((size_t)(nh + p.nkv + kvh) * HD + lig * 8) / 2);
+    const uint2* src[2] = {row + ((size_t)(nh + kvh) * HD + lig * 8) / 2, row + ((size_t)(nh + p.nkv + kvh) * HD + lig * 8) / 2};
+    uint4 kv[2];
+    mg_poll8<2>(src, tag, MG_W_QKV, kv);
+    ka = kv[0]; va = kv[1];
   }
   float qf[G][8];
 #pragma unroll
   for (int g = 0; g < G; ++g) {
-    const uint4 a = pq[g].wait(tag, MG_W_QKV);
-    const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+    const uint32_t aw[4] = {qa[g].x, qa[g].y, qa[g].z, qa[g].w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float re = bf16_lo(aw[j]), im = bf16_hi(aw[j]);
@@ -341,11 +370,6 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
       qf[g][2 * j] = bf16_lo(r) * p.scale_log2;
       qf[g][2 * j + 1] = bf16_hi(r) * p.scale_log2;
     }
-  }
-  uint4 ka = make_uint4(0, 0, 0, 0), va = ka;
-  if (owns_new) {
-    ka = pk_new.wait(tag, MG_W_QKV);
-    va = pv_new.wait(tag, MG_W_QKV);
   }
   float m[G], l[G], o[G][8];
 #pragma unroll
@@ -508,56 +532,53 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
   mg_consumer_bar();                 // s_attn is reused by this CTA's next item
 }
 
-// Merge of the split-KV partials, spread over the grid one warp at a time (32 outputs per warp, every CTA's first
-// warp before any CTA's second): a thread polls the partial packets of its output, combines them online in chunks
-// of 8 splits, and publishes the merged attention output as {bf16 pair, tag} packets for the `wo` staging.
-__device__ __forceinline__ void mg_attn_merge(const MegaParams& p, int M, uint32_t tag) {
-  const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
-  const int total = M * p.nh * MG_HD;
+// Merge of the split-KV partials, spread over the grid one warp at a time (32 outputs of one head per warp, every
+// CTA's first warp before any CTA's second).  Splits are taken in chunks of 16: lane s fetches the (max, sum) pair
+// of split s for the whole warp, every lane fetches its own output element of the 16 splits, all of it is issued
+// before anything is checked (one L2 round trip per chunk once the data is there); the softmax weights travel by
+// shuffle.  Indices past the last split are clamped to it and get weight zero, so the code has no tail branches.
+// The merged attention output is published as {bf16 pair, tag} packets for the `wo` staging.
+__device__ __noinline__ void mg_attn_merge(const uint2* part_pk, uint2* attn_pk, int total, int splits, uint32_t tag) {
+  const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - MG_PWARPS;
+#pragma unroll 1
   for (int idx = (cw * gridDim.x + blockIdx.x) * 32 + lane; idx < total; idx += gridDim.x * MG_CT) {
-    const int bh = idx / MG_HD, d = idx - bh * MG_HD;
-    const uint2* base = p.part_pk + (size_t)bh * p.splits * MG_PART;
+    const int bh = idx / MG_HD, d = idx - bh * MG_HD;          // bh is warp-uniform (32 | 128)
+    const uint2* base = part_pk + (size_t)bh * splits * MG_PART;
     float Mx = -INFINITY, acc = 0.f, Ls = 0.f;
-    for (int s0 = 0; s0 < p.splits; s0 += 8) {
-      uint2 ov[8];
-      uint4 ml[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const uint2* q = base + (size_t)(s0 + u < p.splits ? s0 + u : s0) * MG_PART;
-        ov[u] = ld_relaxed_gpu_v2(q + d);
-        ml[u] = ld_relaxed_gpu_v4(reinterpret_cast<const uint4*>(q + MG_HD));
-      }
+#pragma unroll 1
+    for (int s0 = 0; s0 < splits; s0 += 16) {
+      const int ns = splits - s0 < 16 ? splits - s0 : 16;
+      const uint4* mlp = reinterpret_cast<const uint4*>(base + (size_t)(s0 + (lane < ns ? lane : 0)) * MG_PART + MG_HD);
+      uint2 ov[16];
+      uint4 ml;
       unsigned spins = 0;
+      for (;;) {
+        bool ok = true;
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const uint2* q = base + (size_t)(s0 + u < p.splits ? s0 + u : s0) * MG_PART;
-        while (ov[u].y != tag || ml[u].y != tag || ml[u].w != tag) {
-          ov[u] = ld_relaxed_gpu_v2(q + d);
-          ml[u] = ld_relaxed_gpu_v4(reinterpret_cast<const uint4*>(q + MG_HD));
-          if (++spins > (1u << 24)) mg_poll_timeout(MG_W_PART, tag, ov[u].y);
-        }
+        for (int u = 0; u < 16; ++u) ov[u] = ld_relaxed_gpu_v2(base + (size_t)(s0 + (u < ns ? u : ns - 1)) * MG_PART + d);
+        ml = ld_relaxed_gpu_v4(mlp);
+#pragma unroll
+        for (int u = 0; u < 16; ++u) ok = ok && ov[u].y == tag;
+        if (ok && ml.y == tag && ml.w == tag) break;
+        if (++spins > (1u << 22)) mg_poll_timeout(MG_W_PART, tag, ml.y);
       }
-      float cm = Mx;
-#pragma unroll
-      for (int u = 0; u < 8; ++u)
-        if (s0 + u < p.splits) cm = fmaxf(cm, __uint_as_float(ml[u].x));
+      const float my_m = lane < ns ? __uint_as_float(ml.x) : -INFINITY;
+      const float cm = fmaxf(Mx, warp_max(my_m));
       const float Ms = cm == -INFINITY ? 0.f : cm;
-      const float corr = exp2f(Mx - Ms);                 // Mx = -inf on the first chunk: 0
+      const float corr = exp2f(Mx - Ms);                       // first chunk: Mx = -inf → 0
+      const float w = exp2f(my_m - Ms);                        // lanes >= ns: 0
       acc *= corr;
-      Ls *= corr;
+      Ls = Ls * corr + warp_sum(w * (lane < ns ? __uint_as_float(ml.z) : 0.f));
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        if (s0 + u < p.splits) {
-          const float w = exp2f(__uint_as_float(ml[u].x) - Ms);
-          acc += w > 0.f ? w * __uint_as_float(ov[u].x) : 0.f;
-          Ls += w * __uint_as_float(ml[u].z);
-        }
+      for (int u = 0; u < 16; ++u) {
+        const float wu = __shfl_sync(0xffffffffu, w, u);
+        acc += wu > 0.f ? wu * __uint_as_float(ov[u].x) : 0.f;
       }
       Mx = cm;
     }
     const float y = Ls > 0.f ? acc / Ls : 0.f;
     const float y1 = __shfl_down_sync(0xffffffffu, y, 1);
-    if ((d & 1) == 0) st_packet(p.attn_pk + (size_t)bh * (MG_HD / 2) + (d >> 1), pack_bf16(y, y1), tag);
+    if ((d & 1) == 0) st_packet(attn_pk + (size_t)bh * (MG_HD / 2) + (d >> 1), pack_bf16(y, y1), tag);
   }
 }
 
@@ -565,32 +586,35 @@ __device__ __forceinline__ void mg_attn_merge(const MegaParams& p, int M, uint32
 // the same-index CTA of every rank (all ranks cut rows identically), sums them in rank order (bit-identical on
 // all ranks), adds its residual slice and publishes the new residual-stream packets to the CTAs of this GPU.
 template <int M>
-__device__ __forceinline__ void mg_owner_reduce(const MegaParams& p, uint32_t tag, int N, float (*res)[MG_MAX_OWN],
-                                                uint2* r_pk) {
-  const MegaAr& a = p.ar;
-  const int ct = threadIdx.x - 32;
+__device__ __noinline__ void mg_owner_reduce(const uint2* mine, int tp, int rank, uint32_t tag, int N,
+                                             float (*res)[MG_MAX_OWN], uint2* r_pk) {
+  const int ct = threadIdx.x - MG_CT0;
   int g0, g1;
   mg_range(N / MG_GROUP, g0, g1);
   const int row0 = g0 * MG_GROUP, pairs = (g1 - g0) * MG_GROUP / 2;
-  const uint2* mine = a.p_peer[a.rank] + (size_t)(tag & 1) * a.tp * M * N;
+#pragma unroll 1
   for (int i = ct; i < pairs * M; i += MG_CT) {
     const int m = i / pairs, row = row0 + 2 * (i - m * pairs);
     uint4 v[8];
-#pragma unroll
-    for (int src = 0; src < 8; ++src)
-      if (src < a.tp) v[src] = ld_relaxed_sys_v4(reinterpret_cast<const uint4*>(mine + ((size_t)src * M + m) * N + row));
-    float s0 = 0.f, s1 = 0.f;
     unsigned spins = 0;
+    for (;;) {
+      bool ok = true;
+#pragma unroll
+      for (int src = 0; src < 8; ++src)       // sources past the group are clamped to the last rank (re-read, ignored below)
+        v[src] = ld_relaxed_sys_v4(reinterpret_cast<const uint4*>(mine + ((size_t)(src < tp ? src : tp - 1) * M + m) * N + row));
+#pragma unroll
+      for (int src = 0; src < 8; ++src) ok = ok && v[src].y == tag && v[src].w == tag;
+      if (ok) break;
+      if (++spins > (1u << 22)) {
+        int late = 0;
+        for (int src = 0; src < 8; ++src) if (src < tp && (v[src].y != tag || v[src].w != tag)) late = src;
+        mg_peer_timeout(rank, late, tag, v[late].y, 0);
+      }
+    }
+    float s0 = 0.f, s1 = 0.f;
 #pragma unroll
     for (int src = 0; src < 8; ++src) {
-      if (src < a.tp) {
-        while (v[src].y != tag || v[src].w != tag) {
-          v[src] = ld_relaxed_sys_v4(reinterpret_cast<const uint4*>(mine + ((size_t)src * M + m) * N + row));
-          if (++spins > (1u << 24)) mg_peer_timeout(a.rank, src, tag, v[src].y, 0);
-        }
-        s0 += __uint_as_float(v[src].x);
-        s1 += __uint_as_float(v[src].z);
-      }
+      if (src < tp) { s0 += __uint_as_float(v[src].x); s1 += __uint_as_float(v[src].z); }
     }
     const float y0 = __bfloat162float(__float2bfloat16(__bfloat162float(__float2bfloat16(s0)) + res[m][row - row0]));
     const float y1 = __bfloat162float(__float2bfloat16(__bfloat162float(__float2bfloat16(s1)) + res[m][row - row0 + 1]));
@@ -624,6 +648,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   c.xin = reinterpret_cast<uint4*>(after);
   c.stage = 0; c.phase = 0;
   c.ar = &p.ar; c.ar_tag = 0;
+  c.trace_row = nullptr; c.trace_on = p.trace != nullptr;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -637,9 +662,10 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   __syncthreads();
 
   const int qdim = p.nh * MG_HD;
-  if (warp == 0) {
+  if (warp < MG_PWARPS) {
+    if constexpr (MG_PWARPS == 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(MG_PRODUCER_REGS));
     // ===================================================== producer: the whole model's weights, in order
-    if (lane == 0) {
+    if (warp == 0 && lane == 0) {
       // `ld` feeds the ring.  While the consumers are NOT consuming (attention, merge and the polls around
       // them: s_idle is set) and the ring is full, `pf` walks up to p.l2_ahead stages further down the same
       // sequence and only asks the L2 to fetch them, so HBM keeps streaming through the part of a layer in
@@ -680,10 +706,11 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   }
 
   // ===================================================== consumers
+  if constexpr (MG_PWARPS == 4) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(MG_CONSUMER_REGS));
   const unsigned int gen = *reinterpret_cast<volatile unsigned int*>(p.gen);
   const uint32_t base = gen * (uint32_t)(2 * p.L);           // tags of this step: base + 2 l + {1, 2}; base is even
   const MgPos pos0 = mg_pos(p, 0, lane % (MG_HD / 8));      // batch row 0: constant for the whole step
-  const int ct = threadIdx.x - 32;
+  const int ct = threadIdx.x - MG_CT0;
   int own0, own1;
   mg_range(p.H / MG_GROUP, own0, own1);
   own0 *= MG_GROUP; own1 *= MG_GROUP;                        // rows of the residual stream this CTA owns
@@ -697,6 +724,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   }
   // (first read of s_res happens after the consumer barriers of the first staging pass)
 
+  const uint2* ar_mine = p.ar.tp > 1 ? p.ar.p_peer[p.ar.rank] : nullptr;      // this rank's copy of the partial-sum packets
   const size_t r_half = (size_t)M * (p.H / 2);               // packets of one parity half of the residual buffer
   MegaOut o;
   o.res = s_res; o.row0 = own0; o.logits = nullptr; o.best_v = nullptr; o.best_i = nullptr; o.idx_offset = 0;
@@ -706,14 +734,15 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     uint2* r1 = p.r_pk + r_half;                               // residual packets tagged t1 (after wo)
     uint2* r2 = p.r_pk;                                        // residual packets tagged t2 (after w2)
     // ---- fused qkv projection (RMSNorm in the prologue); x comes from the previous layer's w2 epilogues
+    if (c.trace_on) c.trace_row = p.trace + ((size_t)blockIdx.x * p.L + l) * 32;
     mg_stamp(p, l, 0);
-    if (l == 0) mg_stage_embedding<M>(c, p.embedding, p.ids, p.vocab_full, p.H, p.attn_norm, p.eps, red);
-    else mg_stage_packets<M>(c, r2, t1 - 1u, p.H, p.H / 2, p.attn_norm + (size_t)l * p.H, p.eps, red, MG_W_X);
+    if (l == 0) mg_stage_embedding<M>(c.xin, p.embedding, p.ids, p.vocab_full, p.H, p.attn_norm, p.eps, red);
+    else mg_stage_packets<M>(c.xin, r2, t1 - 1u, p.H, p.H / 2, p.attn_norm + (size_t)l * p.H, p.eps, red, MG_W_X, c.trace_row);
     mg_stamp(p, l, 1);
     o.pk = p.qkv_pk; o.tag = t1;
     mg_gemv_mma<M, MG_PLAIN>(c, p.NQKV, p.H, o, s_acc);
     mg_stamp(p, l, 2);
-    if (threadIdx.x == 32) *s_idle = 1;
+    if (threadIdx.x == MG_CT0) *s_idle = 1;
     // ---- attention: each item polls the q / k / v packets it needs
     {
       const int items = M * p.nkv * p.splits;
@@ -724,19 +753,19 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
       }
     }
     mg_stamp(p, l, 3);
-    if (p.splits > 1) mg_attn_merge(p, M, t1);
+    if (p.splits > 1) mg_attn_merge(p.part_pk, p.attn_pk, M * p.nh * MG_HD, p.splits, t1);
     mg_stamp(p, l, 4);
     // ---- wo + residual
-    mg_stage_packets<M>(c, p.attn_pk, t1, qdim, qdim / 2, nullptr, p.eps, red, MG_W_ATTN);
+    mg_stage_packets<M>(c.xin, p.attn_pk, t1, qdim, qdim / 2, nullptr, p.eps, red, MG_W_ATTN, c.trace_row);
     mg_stamp(p, l, 5);
-    if (threadIdx.x == 32) *s_idle = 0;
+    if (threadIdx.x == MG_CT0) *s_idle = 0;
     c.ar_tag = t1;
     o.r_pk = r1; o.tag = t1;
     mg_gemv_mma<M, MG_RESIDUAL>(c, p.H, qdim, o, s_acc);
-    if (p.ar.tp > 1) mg_owner_reduce<M>(p, t1, p.H, s_res, r1);
+    if (p.ar.tp > 1) mg_owner_reduce<M>(ar_mine + (size_t)(t1 & 1) * p.ar.tp * M * p.H, p.ar.tp, p.ar.rank, t1, p.H, s_res, r1);
     mg_stamp(p, l, 6);
     // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
-    mg_stage_packets<M>(c, r1, t1, p.H, p.H / 2, p.ffn_norm + (size_t)l * p.H, p.eps, red, MG_W_X);
+    mg_stage_packets<M>(c.xin, r1, t1, p.H, p.H / 2, p.ffn_norm + (size_t)l * p.H, p.eps, red, MG_W_X2, c.trace_row);
     mg_stamp(p, l, 7);
     o.pk = p.h_pk; o.tag = t2;
     mg_gemv_mma<M, MG_SWIGLU>(c, 2 * p.F, p.H, o, s_acc);
@@ -748,25 +777,26 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     if constexpr (M > 4) {
       if (p.w2_passes == 2) {
         const int ka = ((p.F + MG_KS - 1) / MG_KS + 1) / 2 * MG_KS;       // first K range: whole k-stages
-        mg_stage_packets<M>(c, p.h_pk, t2, ka, p.F / 2, nullptr, p.eps, red, MG_W_H);
+        mg_stage_packets<M>(c.xin, p.h_pk, t2, ka, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
         mg_stamp(p, l, 9);
         mg_gemv_mma<M, MG_RESIDUAL, 1>(c, p.H, ka, o, s_acc, s_carry);
-        mg_stage_packets<M>(c, p.h_pk + ka / 2, t2, p.F - ka, p.F / 2, nullptr, p.eps, red, MG_W_H);
+        mg_stage_packets<M>(c.xin, p.h_pk + ka / 2, t2, p.F - ka, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
         mg_gemv_mma<M, MG_RESIDUAL, 2>(c, p.H, p.F - ka, o, s_acc, s_carry);
         w2_done = true;
       }
     }
     if (!w2_done) {
-      mg_stage_packets<M>(c, p.h_pk, t2, p.F, p.F / 2, nullptr, p.eps, red, MG_W_H);
+      mg_stage_packets<M>(c.xin, p.h_pk, t2, p.F, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
       mg_stamp(p, l, 9);
       mg_gemv_mma<M, MG_RESIDUAL>(c, p.H, p.F, o, s_acc);
     }
-    if (p.ar.tp > 1) mg_owner_reduce<M>(p, t2, p.H, s_res, r2);
+    if (p.ar.tp > 1) mg_owner_reduce<M>(ar_mine + (size_t)(t2 & 1) * p.ar.tp * M * p.H, p.ar.tp, p.ar.rank, t2, p.H, s_res, r2);
     mg_stamp(p, l, 10);
   }
   // ---- final norm + LM head with a running arg-max per (batch row, weight-row lane)
   const uint32_t t_last = base + 2u * p.L;
-  mg_stage_packets<M>(c, p.r_pk, t_last, p.H, p.H / 2, p.final_norm, p.eps, red, MG_W_X);
+  c.trace_row = nullptr;
+  mg_stage_packets<M>(c.xin, p.r_pk, t_last, p.H, p.H / 2, p.final_norm, p.eps, red, MG_W_X, c.trace_row);
   float best_v = -INFINITY;
   int best_i = 0x7fffffff;
   o.logits = p.logits; o.best_v = &best_v; o.best_i = &best_i; o.idx_offset = p.ar.rank * p.V;
@@ -798,7 +828,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   }
   // every block read `gen` before it produced anything, and block 0 got here only after consuming packets of the
   // last layer from every block: nobody can still be about to read the old value
-  if (blockIdx.x == 0 && threadIdx.x == 32) *p.gen = gen + 1u;
+  if (blockIdx.x == 0 && threadIdx.x == MG_CT0) *p.gen = gen + 1u;
 }
 
 // Greedy selection + sequence bookkeeping after the decode kernel: merges the grid x tp arg-max candidates of every

@@ -45,15 +45,22 @@ __device__ __forceinline__ int mg_xperm_word(int m, int n_ks, int k) {
   return ((((m * n_ks + ks) * 8 + w) * 4 + t) << 4) + s * 2 + half;
 }
 
+// ---- staging of a GEMV input into the permuted shared-memory layout.
+// The two staging functions are deliberately NOT inlined: the layer body calls them six times, and the decode
+// kernel must stay small — measured on B200: at 129 KB / 178 KB of code per instance the step ran 2.84 / 2.95 ms,
+// at 238 KB and 280 KB 5.0 ms (every GEMV phase twice as slow: the instruction stream no longer stays cached).
+constexpr int MG_NPRE = 4;                                 // norm-weight chunks per thread: K <= 8192
+
 // second half of a staging pass: RMSNorm scale of what pass one left in shared memory (ss = this thread's partial
-// sums of squares per batch row), then the barrier that publishes the staged activations to all consumer warps
+// sums of squares per batch row; gpre = this thread's chunks of the norm weights, fetched before the poll so that
+// their L2 round trip hides behind it), then the barrier that publishes the staged activations to all consumer warps
 template <int M>
-__device__ __forceinline__ void mg_stage_finish(MegaCtx& c, int K, const __nv_bfloat16* norm_w, float eps,
-                                                float (*red)[MG_CONSUMERS], float (&ss)[M]) {
-  const int ct = threadIdx.x - 32, lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1;
+__device__ __forceinline__ void mg_stage_finish(uint4* xin, int K, bool norm, float eps, float (*red)[MG_CONSUMERS],
+                                                float (&ss)[M], const uint4 (&gpre)[MG_NPRE]) {
+  const int ct = threadIdx.x - MG_CT0, lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - MG_PWARPS;
   const int K8 = K >> 3, n_ks = (K + MG_KS - 1) / MG_KS;
-  uint32_t* xw = reinterpret_cast<uint32_t*>(c.xin);
-  if (norm_w != nullptr) {
+  uint32_t* xw = reinterpret_cast<uint32_t*>(xin);
+  if (norm) {
 #pragma unroll
     for (int m = 0; m < M; ++m) {
       const float t = warp_sum(ss[m]);
@@ -67,44 +74,53 @@ __device__ __forceinline__ void mg_stage_finish(MegaCtx& c, int K, const __nv_bf
       t = warp_sum(t);
       rinv[m] = rsqrtf(t / (float)K + eps);
     }
-    for (int i = ct; i < K8; i += MG_CT) {
-      const uint4 g = __ldg(reinterpret_cast<const uint4*>(norm_w) + i);
-      const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
 #pragma unroll
-      for (int m = 0; m < M; ++m) {
-        const int base = mg_xperm_word(m, n_ks, i * 8);
+    for (int j = 0; j < MG_NPRE; ++j) {
+      const int i = ct + j * MG_CT;
+      if (i < K8) {
+        const uint32_t gw[4] = {gpre[j].x, gpre[j].y, gpre[j].z, gpre[j].w};
+#pragma unroll 1
+        for (int m = 0; m < M; ++m) {
+          const int base = mg_xperm_word(m, n_ks, i * 8);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint32_t a = xw[base + j * 16];
-          xw[base + j * 16] = pack_bf16(bf16_lo(a) * rinv[m] * bf16_lo(gw[j]), bf16_hi(a) * rinv[m] * bf16_hi(gw[j]));
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t a = xw[base + q * 16];
+            xw[base + q * 16] = pack_bf16(bf16_lo(a) * rinv[m] * bf16_lo(gw[q]), bf16_hi(a) * rinv[m] * bf16_hi(gw[q]));
+          }
         }
       }
     }
   }
   mg_consumer_bar();
 }
+__device__ __forceinline__ void mg_norm_prefetch(const __nv_bfloat16* norm_w, int K, uint4 (&gpre)[MG_NPRE]) {
+  const int ct = threadIdx.x - MG_CT0, K8 = K >> 3;
+#pragma unroll
+  for (int j = 0; j < MG_NPRE; ++j) {
+    const int i = ct + j * MG_CT;
+    gpre[j] = (norm_w != nullptr && i < K8) ? __ldg(reinterpret_cast<const uint4*>(norm_w) + i) : make_uint4(0, 0, 0, 0);
+  }
+}
 
 // stage the embedding rows of this step's tokens (first layer only; optional RMSNorm); positions k >= K are zero
 template <int M>
-__device__ __forceinline__ void mg_stage_embedding(MegaCtx& c, const __nv_bfloat16* table, const int* ids, int vocab,
-                                                   int K, const __nv_bfloat16* norm_w, float eps,
-                                                   float (*red)[MG_CONSUMERS]) {
-  const int ct = threadIdx.x - 32;
+__device__ __noinline__ void mg_stage_embedding(uint4* xin, const __nv_bfloat16* table, const int* ids, int vocab,
+                                                int K, const __nv_bfloat16* norm_w, float eps,
+                                                float (*red)[MG_CONSUMERS]) {
+  const int ct = threadIdx.x - MG_CT0;
   const int K8 = K >> 3, n_ks = (K + MG_KS - 1) / MG_KS;
-  uint32_t* xw = reinterpret_cast<uint32_t*>(c.xin);
+  uint32_t* xw = reinterpret_cast<uint32_t*>(xin);
   float ss[M];
-  const uint4* rows[M];
+  uint4 gpre[MG_NPRE];
+  mg_norm_prefetch(norm_w, K, gpre);
 #pragma unroll
-  for (int m = 0; m < M; ++m) {
-    ss[m] = 0.f;
-    int id = ids[m];
-    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
-    rows[m] = reinterpret_cast<const uint4*>(table) + (size_t)id * K8;
-  }
+  for (int m = 0; m < M; ++m) ss[m] = 0.f;
   for (int i = ct; i < n_ks * (MG_KS / 8); i += MG_CT) {
 #pragma unroll
     for (int m = 0; m < M; ++m) {
-      const uint4 a = i < K8 ? __ldg(rows[m] + i) : make_uint4(0, 0, 0, 0);
+      int id = ids[m];
+      id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+      const uint4 a = i < K8 ? __ldg(reinterpret_cast<const uint4*>(table) + (size_t)id * K8 + i) : make_uint4(0, 0, 0, 0);
       const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
       const int base = mg_xperm_word(m, n_ks, i * 8);
 #pragma unroll
@@ -115,46 +131,48 @@ __device__ __forceinline__ void mg_stage_embedding(MegaCtx& c, const __nv_bfloat
       }
     }
   }
-  mg_stage_finish<M>(c, K, norm_w, eps, red, ss);
+  mg_stage_finish<M>(xin, K, norm_w != nullptr, eps, red, ss, gpre);
 }
 
 // Stage [M, K] activations that arrive as tagged packets {bf16 pair, tag} (row pitch `ldp` packets): every thread
 // polls the packets it stages until their tag is `tag` — this poll IS the synchronisation with the producers of
-// the previous op (all CTAs of this GPU), there is no grid barrier.  Up to 4 16-byte loads (8 packets) are in
-// flight per thread.  Optional RMSNorm; positions k >= K are zero.
+// the previous op (all CTAs of this GPU), there is no grid barrier.  Up to 8 16-byte loads (16 packets) are in
+// flight per thread (one L2 round trip per batch once the data is there); the norm weights are fetched before the
+// poll.  Optional RMSNorm; positions k >= K are zero.
 template <int M>
-__device__ __forceinline__ void mg_stage_packets(MegaCtx& c, const uint2* pk, uint32_t tag, int K, int ldp,
-                                                 const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS],
-                                                 int what) {
-  const int ct = threadIdx.x - 32;
+__device__ __noinline__ void mg_stage_packets(uint4* xin, const uint2* pk, uint32_t tag, int K, int ldp,
+                                              const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS],
+                                              int what, unsigned long long* trace_row) {
+  constexpr int NB = 8;                                    // 16-byte loads in flight per thread
+  const int ct = threadIdx.x - MG_CT0;
   const int n_ks = (K + MG_KS - 1) / MG_KS, K4 = K >> 2;
-  uint32_t* xw = reinterpret_cast<uint32_t*>(c.xin);
+  uint32_t* xw = reinterpret_cast<uint32_t*>(xin);
   float ss[M];
 #pragma unroll
   for (int m = 0; m < M; ++m) ss[m] = 0.f;
+  uint4 gpre[MG_NPRE];
+  mg_norm_prefetch(norm_w, K, gpre);
   // item q = it * M + m covers values k = 4 i .. 4 i + 3 of row m, i = ct + it * MG_CT (exactly n_ks items per row)
   const int items = n_ks * M;
-  for (int q0 = 0; q0 < items; q0 += 4) {
-    uint4 v[4];
-    const uint4* src[4];
-    bool need[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int q = q0 + u, it = q / M, m = q - it * M, i = ct + it * MG_CT;
-      need[u] = q < items && i < K4;
-      src[u] = reinterpret_cast<const uint4*>(pk + (size_t)m * ldp) + i;
-      v[u] = need[u] ? ld_relaxed_gpu_v4(src[u]) : make_uint4(0, tag, 0, tag);
-    }
+#pragma unroll 1
+  for (int q0 = 0; q0 < items; q0 += NB) {
+    uint4 v[NB];
     unsigned spins = 0;
+    for (;;) {
+      bool ok = true;
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      while (v[u].y != tag || v[u].w != tag) {
-        v[u] = ld_relaxed_gpu_v4(src[u]);
-        if (++spins > (1u << 24)) mg_poll_timeout(what, tag, v[u].y);
+      for (int u = 0; u < NB; ++u) {
+        const int q = q0 + u, it = q / M, m = q - it * M, i = ct + it * MG_CT;
+        v[u] = (q < items && i < K4) ? ld_relaxed_gpu_v4(reinterpret_cast<const uint4*>(pk + (size_t)m * ldp) + i)
+                                     : make_uint4(0, tag, 0, tag);
       }
+#pragma unroll
+      for (int u = 0; u < NB; ++u) ok = ok && v[u].y == tag && v[u].w == tag;
+      if (ok) break;
+      if (++spins > (1u << 22)) mg_poll_timeout(what, tag, v[0].y);
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < NB; ++u) {
       const int q = q0 + u, it = q / M, m = q - it * M, i = ct + it * MG_CT;
       if (q < items) {
         xw[mg_xperm_word(m, n_ks, i * 4)] = v[u].x;
@@ -164,7 +182,12 @@ __device__ __forceinline__ void mg_stage_packets(MegaCtx& c, const uint2* pk, ui
       }
     }
   }
-  mg_stage_finish<M>(c, K, norm_w, eps, red, ss);
+  if (trace_row != nullptr && threadIdx.x == MG_CT0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    trace_row[21 + what] = t;
+  }
+  mg_stage_finish<M>(xin, K, norm_w != nullptr, eps, red, ss, gpre);
 }
 
 // What the epilogue of a GEMV does with a finished 8-row group (see decode_mega.cu for the packet buffers)
@@ -187,7 +210,7 @@ template <int M, int MODE, int CARRY = 0>
 __device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, const MegaOut& o,
                                             float (*s_acc)[MG_CONSUMERS][MG_MMA_MAX_M][8], float (*carry)[64] = nullptr) {
   static_assert(M <= MG_MMA_MAX_M, "batch rows ride in the first 8 rows of the MMA M dimension");
-  const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - 1, ct = threadIdx.x - 32;
+  const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - MG_PWARPS, ct = threadIdx.x - MG_CT0;
   const int g = lane >> 2, t = lane & 3;                   // MMA fragment coordinates: batch row g, quad lane t
   const int n_ks = (K + MG_KS - 1) / MG_KS;
   int g0, g1;

@@ -58,6 +58,22 @@ a = (t[0, lo:hi, 16:21] - t[0, lo:hi, 2:3]) / 1e3
 print("block 0 attention internals (µs after the phase starts): " + "  ".join(
     f"{n}={v:.1f}" for n, v in zip(["setup", "q+rope", "kv_loop", "new_tok", "fold+write"], a.mean(0).tolist())))
 
+# data-flow waits: per layer, how long after the LAST block finished producing does the FIRST / median block finish
+# consuming (stamps: 6 = wo GEMV + all-reduce done, 7 = x staged for w13; 10 = w2 + all-reduce done, next layer's 1)
+def tail(prod, cons, shift=0):
+    tp_ = tall[:, lo:hi, prod]                                  # [blocks, layers]
+    tc_ = tall[:, lo + shift:hi + shift, cons]
+    last = tp_.max(0).values
+    return (((last - tp_.median(0).values) / 1e3).mean().item(), ((tc_.min(0).values - last) / 1e3).mean().item(),
+            ((tc_.median(0).values - last) / 1e3).mean().item())
+for name, pr, co, sh in (("qkv→attn(q+rope)", 2, 17, 0), ("attn→merge", 3, 4, 0), ("merge→stage_wo", 4, 5, 0),
+                         ("wo(+AR)→stage_w13", 6, 7, 0), ("w13→stage_w2", 8, 9, 0), ("w2(+AR)→stage_qkv", 10, 1, 1)):
+    a_, b_, c_ = tail(pr, co, sh)
+    print(f"{name:22s} producer tail (last - median) {a_:5.2f} us | first consumer done {b_:5.2f} us after the last producer, median {c_:5.2f}")
+for name, ev, start in (("poll x (qkv)", 21, 0), ("poll x (w13)", 27, 6), ("poll attn", 24, 4), ("poll h", 25, 8)):
+    d_ = (tall[:, lo:hi, ev] - tall[:, lo:hi, start]) / 1e3
+    print(f"{name:14s} poll finished after phase start: min {d_.mean(1).min():5.2f} p50 {d_.mean(1).median():5.2f} max {d_.mean(1).max():5.2f}")
+
 # spread across blocks: when does each block finish each phase, relative to the earliest block entering it
 ends = {"gemv_qkv": 2, "attn": 3, "gemv_wo": 6, "gemv_w13": 8, "gemv_w2": 10}
 starts = {"gemv_qkv": 1, "attn": 2, "gemv_wo": 5, "gemv_w13": 7, "gemv_w2": 9}
