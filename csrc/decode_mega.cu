@@ -323,7 +323,8 @@ __device__ __forceinline__ MgPos mg_pos(const MegaParams& p, int b, int lig) {
 
 template <int G>
 __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const MegaCtx& c, int layer, int M, int b,
-                                                  int kvh, int split, uint32_t tag, const MgPos& pp) {
+                                                  int kvh, int split, uint32_t tag, const uint2* qkv_pk, uint2* part_pk,
+                                                  uint2* attn_pk, const MgPos& pp) {
   constexpr int HD = MG_HD, LPK = HD / 8, GPW = 32 / LPK, NG = MG_CONSUMERS * GPW;
   constexpr int KEYS_PER_ITER = NG * MG_KPI;
   const int nh = p.nkv * G;
@@ -343,8 +344,29 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
   mg_stamp(p, layer, 16);
   const float cs[4] = {pp.cs[0], pp.cs[1], pp.cs[2], pp.cs[3]}, sn[4] = {pp.sn[0], pp.sn[1], pp.sn[2], pp.sn[3]};
   // q (all heads of the group) and the new token's k, v arrive as packets from the qkv GEMV of other CTAs
-  const uint2* row = p.qkv_pk + (size_t)b * (p.NQKV / 2);
+  const uint2* row = qkv_pk + (size_t)b * (p.NQKV / 2);
   const bool owns_new = split == 0 && warp == 0;      // consumes the new k, v after the KV loop
+  // The K/V cache rows of this item's first load batch do not depend on q: request them BEFORE polling for q, so the
+  // HBM round trip of the cache overlaps the wait for the qkv GEMV of the other CTAs (needs the 224-register
+  // consumers: at 168 registers the held rows spilled and this lost, round 1).
+  constexpr int UNR = G <= 4 ? 2 : 1;
+  const size_t head_off = (((size_t)layer * M + b) * p.nkv + kvh) * (size_t)p.T * HD;
+  const __nv_bfloat16* kbase = p.kc + head_off + lig * 8;
+  const __nv_bfloat16* vbase = p.vc + head_off + lig * 8;
+  uint4 kr[UNR][MG_KPI], vr[UNR][MG_KPI];
+  auto load_batch = [&](int base) {
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const int key0 = base + u * KEYS_PER_ITER + gid * MG_KPI;
+#pragma unroll
+      for (int i = 0; i < MG_KPI; ++i) {
+        const bool ok = key0 + i < hi;
+        kr[u][i] = ok ? ldg_stream(kbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
+        vr[u][i] = ok ? ldg_stream(vbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
+      }
+    }
+  };
+  load_batch(lo);
   uint4 qa[G];
   {
     const uint2* src[G];
@@ -378,10 +400,6 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
 #pragma unroll
     for (int e = 0; e < 8; ++e) o[g][e] = 0.f;
   }
-  const size_t head_off = (((size_t)layer * M + b) * p.nkv + kvh) * (size_t)p.T * HD;
-  const __nv_bfloat16* kbase = p.kc + head_off + lig * 8;
-  const __nv_bfloat16* vbase = p.vc + head_off + lig * 8;
-
   auto process = [&](const uint4 (&kr)[MG_KPI], const uint4 (&vr)[MG_KPI], const int key0) {
     float part[G][MG_KPI];
 #pragma unroll
@@ -440,19 +458,9 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
   };
 
   mg_stamp(p, layer, 17);
-  constexpr int UNR = G <= 4 ? 2 : 1;
+#pragma unroll 1
   for (int base = lo; base < hi; base += UNR * KEYS_PER_ITER) {
-    uint4 kr[UNR][MG_KPI], vr[UNR][MG_KPI];
-#pragma unroll
-    for (int u = 0; u < UNR; ++u) {
-      const int key0 = base + u * KEYS_PER_ITER + gid * MG_KPI;
-#pragma unroll
-      for (int i = 0; i < MG_KPI; ++i) {
-        const bool ok = key0 + i < hi;
-        kr[u][i] = ok ? ldg_stream(kbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
-        vr[u][i] = ok ? ldg_stream(vbase + (size_t)(key0 + i) * HD) : make_uint4(0, 0, 0, 0);
-      }
-    }
+    if (base != lo) load_batch(base);
 #pragma unroll
     for (int u = 0; u < UNR; ++u) process(kr[u], vr[u], base + u * KEYS_PER_ITER + gid * MG_KPI);
   }
@@ -521,9 +529,9 @@ __device__ __forceinline__ void mg_attention_item(const MegaParams& p, const Meg
     if (p.splits == 1) {
       const float y = Ls > 0.f ? acc / Ls : 0.f;
       const float y1 = __shfl_down_sync(0xffffffffu, y, 1);
-      if ((d & 1) == 0) st_packet(p.attn_pk + ((size_t)b * nh + h) * (HD / 2) + (d >> 1), pack_bf16(y, y1), tag);
+      if ((d & 1) == 0) st_packet(attn_pk + ((size_t)b * nh + h) * (HD / 2) + (d >> 1), pack_bf16(y, y1), tag);
     } else {
-      uint2* dst = p.part_pk + (((size_t)b * nh + h) * p.splits + split) * MG_PART;
+      uint2* dst = part_pk + (((size_t)b * nh + h) * p.splits + split) * MG_PART;
       st_packet(dst + d, __float_as_uint(acc), tag);
       if (d == 0) { st_packet(dst + HD, __float_as_uint(Mx), tag); st_packet(dst + HD + 1, __float_as_uint(Ls), tag); }
     }
@@ -733,13 +741,21 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     const uint32_t t1 = base + 2u * l + 1u, t2 = t1 + 1u;      // t1 odd, t2 even
     uint2* r1 = p.r_pk + r_half;                               // residual packets tagged t1 (after wo)
     uint2* r2 = p.r_pk;                                        // residual packets tagged t2 (after w2)
+    // qkv / partials / attention output / SwiGLU output alternate between two buffers by layer parity: a CTA whose
+    // row range of some GEMV is empty (tiny models) may trail the grid by most of a layer, and must never find
+    // the packets it is still polling overwritten by the next layer's
+    const int lp = l & 1;
+    uint2* qkv_pk = p.qkv_pk + (size_t)lp * M * (p.NQKV / 2);
+    uint2* part_pk = p.part_pk + (size_t)lp * M * p.nh * p.splits * MG_PART;
+    uint2* attn_pk = p.attn_pk + (size_t)lp * M * (qdim / 2);
+    uint2* h_pk = p.h_pk + (size_t)lp * M * (p.F / 2);
     // ---- fused qkv projection (RMSNorm in the prologue); x comes from the previous layer's w2 epilogues
     if (c.trace_on) c.trace_row = p.trace + ((size_t)blockIdx.x * p.L + l) * 32;
     mg_stamp(p, l, 0);
     if (l == 0) mg_stage_embedding<M>(c.xin, p.embedding, p.ids, p.vocab_full, p.H, p.attn_norm, p.eps, red);
     else mg_stage_packets<M>(c.xin, r2, t1 - 1u, p.H, p.H / 2, p.attn_norm + (size_t)l * p.H, p.eps, red, MG_W_X, c.trace_row);
     mg_stamp(p, l, 1);
-    o.pk = p.qkv_pk; o.tag = t1;
+    o.pk = qkv_pk; o.tag = t1;
     mg_gemv_mma<M, MG_PLAIN>(c, p.NQKV, p.H, o, s_acc);
     mg_stamp(p, l, 2);
     if (threadIdx.x == MG_CT0) *s_idle = 1;
@@ -749,14 +765,14 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
         const int split = it % p.splits, bk = it / p.splits;
         const int bb = bk / p.nkv;
-        mg_attention_item<G>(p, c, l, M, bb, bk % p.nkv, split, t1, M == 1 ? pos0 : mg_pos(p, bb, lane % (MG_HD / 8)));
+        mg_attention_item<G>(p, c, l, M, bb, bk % p.nkv, split, t1, qkv_pk, part_pk, attn_pk, M == 1 ? pos0 : mg_pos(p, bb, lane % (MG_HD / 8)));
       }
     }
     mg_stamp(p, l, 3);
-    if (p.splits > 1) mg_attn_merge(p.part_pk, p.attn_pk, M * p.nh * MG_HD, p.splits, t1);
+    if (p.splits > 1) mg_attn_merge(part_pk, attn_pk, M * p.nh * MG_HD, p.splits, t1);
     mg_stamp(p, l, 4);
     // ---- wo + residual
-    mg_stage_packets<M>(c.xin, p.attn_pk, t1, qdim, qdim / 2, nullptr, p.eps, red, MG_W_ATTN, c.trace_row);
+    mg_stage_packets<M>(c.xin, attn_pk, t1, qdim, qdim / 2, nullptr, p.eps, red, MG_W_ATTN, c.trace_row);
     mg_stamp(p, l, 5);
     if (threadIdx.x == MG_CT0) *s_idle = 0;
     c.ar_tag = t1;
@@ -767,7 +783,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
     mg_stage_packets<M>(c.xin, r1, t1, p.H, p.H / 2, p.ffn_norm + (size_t)l * p.H, p.eps, red, MG_W_X2, c.trace_row);
     mg_stamp(p, l, 7);
-    o.pk = p.h_pk; o.tag = t2;
+    o.pk = h_pk; o.tag = t2;
     mg_gemv_mma<M, MG_SWIGLU>(c, 2 * p.F, p.H, o, s_acc);
     mg_stamp(p, l, 8);
     // ---- w2 + residual
@@ -777,16 +793,16 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     if constexpr (M > 4) {
       if (p.w2_passes == 2) {
         const int ka = ((p.F + MG_KS - 1) / MG_KS + 1) / 2 * MG_KS;       // first K range: whole k-stages
-        mg_stage_packets<M>(c.xin, p.h_pk, t2, ka, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
+        mg_stage_packets<M>(c.xin, h_pk, t2, ka, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
         mg_stamp(p, l, 9);
         mg_gemv_mma<M, MG_RESIDUAL, 1>(c, p.H, ka, o, s_acc, s_carry);
-        mg_stage_packets<M>(c.xin, p.h_pk + ka / 2, t2, p.F - ka, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
+        mg_stage_packets<M>(c.xin, h_pk + ka / 2, t2, p.F - ka, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
         mg_gemv_mma<M, MG_RESIDUAL, 2>(c, p.H, p.F - ka, o, s_acc, s_carry);
         w2_done = true;
       }
     }
     if (!w2_done) {
-      mg_stage_packets<M>(c.xin, p.h_pk, t2, p.F, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
+      mg_stage_packets<M>(c.xin, h_pk, t2, p.F, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
       mg_stamp(p, l, 9);
       mg_gemv_mma<M, MG_RESIDUAL>(c, p.H, p.F, o, s_acc);
     }
@@ -929,10 +945,10 @@ static MegaLayout mega_layout(int M, int H, int F, int nh, int nkv, int num_sms)
   size_t at = 0;
   auto take = [&](size_t packets) { const size_t off = at; at += (packets * 8 + 255) / 256 * 256; return off; };
   o.r = take((size_t)2 * M * (H / 2));
-  o.qkv = take((size_t)M * ((nh + 2 * nkv) * MG_HD / 2));
-  o.part = take((size_t)M * nh * splits * MG_PART);
-  o.attn = take((size_t)M * (nh * MG_HD / 2));
-  o.h = take((size_t)M * (F / 2));
+  o.qkv = take((size_t)2 * M * ((nh + 2 * nkv) * MG_HD / 2));          // x2: buffers alternate by layer parity
+  o.part = take((size_t)2 * M * nh * splits * MG_PART);
+  o.attn = take((size_t)2 * M * (nh * MG_HD / 2));
+  o.h = take((size_t)2 * M * (F / 2));
   o.cand = take((size_t)2 * num_sms * M * 2);
   o.total = at;
   return o;

@@ -649,7 +649,11 @@ class B200Engine:
                                           eos: int, pad: int) -> None:
         # the prefill already advanced cache.len_dev by S; `advance` adds one more for the *next* token's
         # slot only after that token is written, so compensate here
+        if self.comm is not None:
+            self.comm.begin_sequence()
         self._select_and_advance(st, cache, sampling, eos, pad)
+        if self.comm is not None:
+            self.comm.end_sequence()          # the candidate exchange used an epoch: advance the counter past it
         cache.len_dev.sub_(1)
 
     # ------------------------------------------------------------------ streaming (token-at-a-time) API

@@ -82,7 +82,7 @@ def main():
                      top_p=0.9, seed=3, eos_token_id=-7)
     b = eng.generate(ids.to(dev), mask.to(dev), max_length=32, do_sample=True, temperature=0.9, top_k=20,
                      top_p=0.9, seed=3, eos_token_id=-7)
-    assert torch.equal(a, b)
+    assert torch.equal(a, b), (a[:, 21:].tolist(), b[:, 21:].tolist())
     ga = [torch.empty_like(a) for _ in range(world)]
     dist.all_gather(ga, a)
     assert all(torch.equal(ga[0], t) for t in ga)
