@@ -736,7 +736,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   const size_t r_half = (size_t)M * (p.H / 2);               // packets of one parity half of the residual buffer
   MegaOut o;
   o.res = s_res; o.row0 = own0; o.logits = nullptr; o.best_v = nullptr; o.best_i = nullptr; o.idx_offset = 0;
-  o.pk = nullptr; o.r_pk = nullptr; o.tag = 0;
+  o.pk = nullptr; o.r_pk = nullptr; o.tag = 0; o.red = nullptr; o.inv_k = 0.f; o.eps = p.eps;
   for (int l = 0; l < p.L; ++l) {
     const uint32_t t1 = base + 2u * l + 1u, t2 = t1 + 1u;      // t1 odd, t2 even
     uint2* r1 = p.r_pk + r_half;                               // residual packets tagged t1 (after wo)
@@ -752,10 +752,10 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     // ---- fused qkv projection (RMSNorm in the prologue); x comes from the previous layer's w2 epilogues
     if (c.trace_on) c.trace_row = p.trace + ((size_t)blockIdx.x * p.L + l) * 32;
     mg_stamp(p, l, 0);
-    if (l == 0) mg_stage_embedding<M>(c.xin, p.embedding, p.ids, p.vocab_full, p.H, p.attn_norm, p.eps, red);
-    else mg_stage_packets<M>(c.xin, r2, t1 - 1u, p.H, p.H / 2, p.attn_norm + (size_t)l * p.H, p.eps, red, MG_W_X, c.trace_row);
+    if (l == 0) mg_stage_embedding<M>(c.xin, p.embedding, p.ids, p.vocab_full, p.H, p.attn_norm, red);
+    else mg_stage_packets<M>(c.xin, r2, t1 - 1u, p.H, p.H / 2, p.attn_norm + (size_t)l * p.H, red, MG_W_X, c.trace_row);
     mg_stamp(p, l, 1);
-    o.pk = qkv_pk; o.tag = t1;
+    o.pk = qkv_pk; o.tag = t1; o.red = red; o.inv_k = 1.f / (float)p.H;
     mg_gemv_mma<M, MG_PLAIN>(c, p.NQKV, p.H, o, s_acc);
     mg_stamp(p, l, 2);
     if (threadIdx.x == MG_CT0) *s_idle = 1;
@@ -772,37 +772,37 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
     if (p.splits > 1) mg_attn_merge(part_pk, attn_pk, M * p.nh * MG_HD, p.splits, t1);
     mg_stamp(p, l, 4);
     // ---- wo + residual
-    mg_stage_packets<M>(c.xin, attn_pk, t1, qdim, qdim / 2, nullptr, p.eps, red, MG_W_ATTN, c.trace_row);
+    mg_stage_packets<M>(c.xin, attn_pk, t1, qdim, qdim / 2, nullptr, red, MG_W_ATTN, c.trace_row);
     mg_stamp(p, l, 5);
     if (threadIdx.x == MG_CT0) *s_idle = 0;
     c.ar_tag = t1;
-    o.r_pk = r1; o.tag = t1;
+    o.r_pk = r1; o.tag = t1; o.red = nullptr;
     mg_gemv_mma<M, MG_RESIDUAL>(c, p.H, qdim, o, s_acc);
     if (p.ar.tp > 1) mg_owner_reduce<M>(ar_mine + (size_t)(t1 & 1) * p.ar.tp * M * p.H, p.ar.tp, p.ar.rank, t1, p.H, s_res, r1);
     mg_stamp(p, l, 6);
     // ---- w1/w3 + SwiGLU (RMSNorm in the prologue)
-    mg_stage_packets<M>(c.xin, r1, t1, p.H, p.H / 2, p.ffn_norm + (size_t)l * p.H, p.eps, red, MG_W_X2, c.trace_row);
+    mg_stage_packets<M>(c.xin, r1, t1, p.H, p.H / 2, p.ffn_norm + (size_t)l * p.H, red, MG_W_X2, c.trace_row);
     mg_stamp(p, l, 7);
-    o.pk = h_pk; o.tag = t2;
+    o.pk = h_pk; o.tag = t2; o.red = red; o.inv_k = 1.f / (float)p.H;
     mg_gemv_mma<M, MG_SWIGLU>(c, 2 * p.F, p.H, o, s_acc);
     mg_stamp(p, l, 8);
     // ---- w2 + residual
     c.ar_tag = t2;
-    o.r_pk = r2; o.tag = t2;
+    o.r_pk = r2; o.tag = t2; o.red = nullptr;
     bool w2_done = false;
     if constexpr (M > 4) {
       if (p.w2_passes == 2) {
         const int ka = ((p.F + MG_KS - 1) / MG_KS + 1) / 2 * MG_KS;       // first K range: whole k-stages
-        mg_stage_packets<M>(c.xin, h_pk, t2, ka, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
+        mg_stage_packets<M>(c.xin, h_pk, t2, ka, p.F / 2, nullptr, red, MG_W_H, c.trace_row);
         mg_stamp(p, l, 9);
         mg_gemv_mma<M, MG_RESIDUAL, 1>(c, p.H, ka, o, s_acc, s_carry);
-        mg_stage_packets<M>(c.xin, h_pk + ka / 2, t2, p.F - ka, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
+        mg_stage_packets<M>(c.xin, h_pk + ka / 2, t2, p.F - ka, p.F / 2, nullptr, red, MG_W_H, c.trace_row);
         mg_gemv_mma<M, MG_RESIDUAL, 2>(c, p.H, p.F - ka, o, s_acc, s_carry);
         w2_done = true;
       }
     }
     if (!w2_done) {
-      mg_stage_packets<M>(c.xin, h_pk, t2, p.F, p.F / 2, nullptr, p.eps, red, MG_W_H, c.trace_row);
+      mg_stage_packets<M>(c.xin, h_pk, t2, p.F, p.F / 2, nullptr, red, MG_W_H, c.trace_row);
       mg_stamp(p, l, 9);
       mg_gemv_mma<M, MG_RESIDUAL>(c, p.H, p.F, o, s_acc);
     }
@@ -812,10 +812,11 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   // ---- final norm + LM head with a running arg-max per (batch row, weight-row lane)
   const uint32_t t_last = base + 2u * p.L;
   c.trace_row = nullptr;
-  mg_stage_packets<M>(c.xin, p.r_pk, t_last, p.H, p.H / 2, p.final_norm, p.eps, red, MG_W_X, c.trace_row);
+  mg_stage_packets<M>(c.xin, p.r_pk, t_last, p.H, p.H / 2, p.final_norm, red, MG_W_X, c.trace_row);
   float best_v = -INFINITY;
   int best_i = 0x7fffffff;
   o.logits = p.logits; o.best_v = &best_v; o.best_i = &best_i; o.idx_offset = p.ar.rank * p.V;
+  o.red = red; o.inv_k = 1.f / (float)p.H;
   mg_gemv_mma<M, MG_LOGITS>(c, p.V, p.H, o, s_acc);
   if (ct < 64) {                                             // thread (m, n): fold the 8 weight-row lanes of a batch row
 #pragma unroll

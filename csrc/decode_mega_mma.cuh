@@ -49,73 +49,41 @@ __device__ __forceinline__ int mg_xperm_word(int m, int n_ks, int k) {
 // The two staging functions are deliberately NOT inlined: the layer body calls them six times, and the decode
 // kernel must stay small — measured on B200: at 129 KB / 178 KB of code per instance the step ran 2.84 / 2.95 ms,
 // at 238 KB and 280 KB 5.0 ms (every GEMV phase twice as slow: the instruction stream no longer stays cached).
-constexpr int MG_NPRE = 4;                                 // norm-weight chunks per thread: K <= 8192
+//
+// RMSNorm is split around the GEMV: staging writes x ⊙ g (the norm weights, fetched before the poll) and leaves the
+// per-warp sums of squares of x in `red`; the GEMV epilogue multiplies its outputs by rsqrt(mean x² + eps).  The
+// scale is a per-row scalar, so W·(x ⊙ g)·r = W·(x·r ⊙ g); this takes a barrier, a second pass over shared memory
+// and the rsqrt out of the critical path between two GEMVs.
 
-// second half of a staging pass: RMSNorm scale of what pass one left in shared memory (ss = this thread's partial
-// sums of squares per batch row; gpre = this thread's chunks of the norm weights, fetched before the poll so that
-// their L2 round trip hides behind it), then the barrier that publishes the staged activations to all consumer warps
+// end of a staging pass: per-warp sums of squares → red, then the barrier that publishes the staged activations
+// (and red) to all consumer warps
 template <int M>
-__device__ __forceinline__ void mg_stage_finish(uint4* xin, int K, bool norm, float eps, float (*red)[MG_CONSUMERS],
-                                                float (&ss)[M], const uint4 (&gpre)[MG_NPRE]) {
-  const int ct = threadIdx.x - MG_CT0, lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - MG_PWARPS;
-  const int K8 = K >> 3, n_ks = (K + MG_KS - 1) / MG_KS;
-  uint32_t* xw = reinterpret_cast<uint32_t*>(xin);
+__device__ __forceinline__ void mg_stage_finish(bool norm, float (*red)[MG_CONSUMERS], float (&ss)[M]) {
+  const int lane = threadIdx.x & 31, cw = (threadIdx.x >> 5) - MG_PWARPS;
   if (norm) {
 #pragma unroll
     for (int m = 0; m < M; ++m) {
       const float t = warp_sum(ss[m]);
       if (lane == 0) red[m][cw] = t;
     }
-    mg_consumer_bar();
-    float rinv[M];
-#pragma unroll
-    for (int m = 0; m < M; ++m) {
-      float t = lane < MG_CONSUMERS ? red[m][lane] : 0.f;
-      t = warp_sum(t);
-      rinv[m] = rsqrtf(t / (float)K + eps);
-    }
-#pragma unroll
-    for (int j = 0; j < MG_NPRE; ++j) {
-      const int i = ct + j * MG_CT;
-      if (i < K8) {
-        const uint32_t gw[4] = {gpre[j].x, gpre[j].y, gpre[j].z, gpre[j].w};
-#pragma unroll 1
-        for (int m = 0; m < M; ++m) {
-          const int base = mg_xperm_word(m, n_ks, i * 8);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const uint32_t a = xw[base + q * 16];
-            xw[base + q * 16] = pack_bf16(bf16_lo(a) * rinv[m] * bf16_lo(gw[q]), bf16_hi(a) * rinv[m] * bf16_hi(gw[q]));
-          }
-        }
-      }
-    }
   }
   mg_consumer_bar();
-}
-__device__ __forceinline__ void mg_norm_prefetch(const __nv_bfloat16* norm_w, int K, uint4 (&gpre)[MG_NPRE]) {
-  const int ct = threadIdx.x - MG_CT0, K8 = K >> 3;
-#pragma unroll
-  for (int j = 0; j < MG_NPRE; ++j) {
-    const int i = ct + j * MG_CT;
-    gpre[j] = (norm_w != nullptr && i < K8) ? __ldg(reinterpret_cast<const uint4*>(norm_w) + i) : make_uint4(0, 0, 0, 0);
-  }
 }
 
 // stage the embedding rows of this step's tokens (first layer only; optional RMSNorm); positions k >= K are zero
 template <int M>
 __device__ __noinline__ void mg_stage_embedding(uint4* xin, const __nv_bfloat16* table, const int* ids, int vocab,
-                                                int K, const __nv_bfloat16* norm_w, float eps,
-                                                float (*red)[MG_CONSUMERS]) {
+                                                int K, const __nv_bfloat16* norm_w, float (*red)[MG_CONSUMERS]) {
   const int ct = threadIdx.x - MG_CT0;
   const int K8 = K >> 3, n_ks = (K + MG_KS - 1) / MG_KS;
   uint32_t* xw = reinterpret_cast<uint32_t*>(xin);
   float ss[M];
-  uint4 gpre[MG_NPRE];
-  mg_norm_prefetch(norm_w, K, gpre);
 #pragma unroll
   for (int m = 0; m < M; ++m) ss[m] = 0.f;
   for (int i = ct; i < n_ks * (MG_KS / 8); i += MG_CT) {
+    const uint4 g = (norm_w != nullptr && i < K8) ? __ldg(reinterpret_cast<const uint4*>(norm_w) + i)
+                                                  : make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
+    const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
 #pragma unroll
     for (int m = 0; m < M; ++m) {
       int id = ids[m];
@@ -125,24 +93,24 @@ __device__ __noinline__ void mg_stage_embedding(uint4* xin, const __nv_bfloat16*
       const int base = mg_xperm_word(m, n_ks, i * 8);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        xw[base + j * 16] = aw[j];                       // pair j of the chunk belongs to quad lane t = j
         const float lo = bf16_lo(aw[j]), hi = bf16_hi(aw[j]);
+        xw[base + j * 16] = pack_bf16(lo * bf16_lo(gw[j]), hi * bf16_hi(gw[j]));      // pair j of the chunk belongs to quad lane t = j
         ss[m] += lo * lo + hi * hi;
       }
     }
   }
-  mg_stage_finish<M>(xin, K, norm_w != nullptr, eps, red, ss, gpre);
+  mg_stage_finish<M>(norm_w != nullptr, red, ss);
 }
 
 // Stage [M, K] activations that arrive as tagged packets {bf16 pair, tag} (row pitch `ldp` packets): every thread
 // polls the packets it stages until their tag is `tag` — this poll IS the synchronisation with the producers of
 // the previous op (all CTAs of this GPU), there is no grid barrier.  Up to 8 16-byte loads (16 packets) are in
-// flight per thread (one L2 round trip per batch once the data is there); the norm weights are fetched before the
-// poll.  Optional RMSNorm; positions k >= K are zero.
+// flight per thread (one L2 round trip per batch once the data is there); the norm weights of a batch are requested
+// before its poll.  Optional RMSNorm (see above); positions k >= K are zero.
 template <int M>
 __device__ __noinline__ void mg_stage_packets(uint4* xin, const uint2* pk, uint32_t tag, int K, int ldp,
-                                              const __nv_bfloat16* norm_w, float eps, float (*red)[MG_CONSUMERS],
-                                              int what, unsigned long long* trace_row) {
+                                              const __nv_bfloat16* norm_w, float (*red)[MG_CONSUMERS], int what,
+                                              unsigned long long* trace_row) {
   constexpr int NB = 8;                                    // 16-byte loads in flight per thread
   const int ct = threadIdx.x - MG_CT0;
   const int n_ks = (K + MG_KS - 1) / MG_KS, K4 = K >> 2;
@@ -150,13 +118,18 @@ __device__ __noinline__ void mg_stage_packets(uint4* xin, const uint2* pk, uint3
   float ss[M];
 #pragma unroll
   for (int m = 0; m < M; ++m) ss[m] = 0.f;
-  uint4 gpre[MG_NPRE];
-  mg_norm_prefetch(norm_w, K, gpre);
   // item q = it * M + m covers values k = 4 i .. 4 i + 3 of row m, i = ct + it * MG_CT (exactly n_ks items per row)
   const int items = n_ks * M;
 #pragma unroll 1
   for (int q0 = 0; q0 < items; q0 += NB) {
     uint4 v[NB];
+    uint2 g[NB];
+#pragma unroll
+    for (int u = 0; u < NB; ++u) {
+      const int q = q0 + u, it = q / M, i = ct + it * MG_CT;
+      g[u] = (norm_w != nullptr && q < items && i < K4) ? __ldg(reinterpret_cast<const uint2*>(norm_w) + i)
+                                                        : make_uint2(0x3f803f80u, 0x3f803f80u);      // bf16 1.0 pairs
+    }
     unsigned spins = 0;
     for (;;) {
       bool ok = true;
@@ -175,9 +148,9 @@ __device__ __noinline__ void mg_stage_packets(uint4* xin, const uint2* pk, uint3
     for (int u = 0; u < NB; ++u) {
       const int q = q0 + u, it = q / M, m = q - it * M, i = ct + it * MG_CT;
       if (q < items) {
-        xw[mg_xperm_word(m, n_ks, i * 4)] = v[u].x;
-        xw[mg_xperm_word(m, n_ks, i * 4 + 2)] = v[u].z;
         const float a = bf16_lo(v[u].x), b = bf16_hi(v[u].x), d = bf16_lo(v[u].z), e = bf16_hi(v[u].z);
+        xw[mg_xperm_word(m, n_ks, i * 4)] = pack_bf16(a * bf16_lo(g[u].x), b * bf16_hi(g[u].x));
+        xw[mg_xperm_word(m, n_ks, i * 4 + 2)] = pack_bf16(d * bf16_lo(g[u].y), e * bf16_hi(g[u].y));
         ss[m] += a * a + b * b + d * d + e * e;
       }
     }
@@ -187,7 +160,7 @@ __device__ __noinline__ void mg_stage_packets(uint4* xin, const uint2* pk, uint3
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     trace_row[21 + what] = t;
   }
-  mg_stage_finish<M>(xin, K, norm_w != nullptr, eps, red, ss, gpre);
+  mg_stage_finish<M>(norm_w != nullptr, red, ss);
 }
 
 // What the epilogue of a GEMV does with a finished 8-row group (see decode_mega.cu for the packet buffers)
@@ -198,6 +171,8 @@ struct MegaOut {
   float (*res)[64];         // MG_RESIDUAL: this CTA's rows of the residual stream (shared memory, bf16-exact values)
   float* best_v;            // MG_LOGITS: running (max, argmax) of this thread's rows
   int* best_i;
+  const float (*red)[MG_CONSUMERS];   // non-null: the input was staged with RMSNorm, scale outputs by rsqrt(mean x² + eps)
+  float inv_k, eps;         // 1 / K of the normalised input
   uint32_t tag;
   int row0;                 // first row of this CTA's range (index base of `res`)
   int idx_offset;           // MG_LOGITS: global vocabulary index of local row 0
@@ -227,6 +202,17 @@ __device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, const Mega
     }
   }
   const bool has_row = g < M;
+  // epilogue threads (see below) scale their outputs by the RMSNorm factor of their batch row
+  float rs = 1.f;
+  if (o.red != nullptr) {
+    const int em = MODE == MG_SWIGLU ? (ct >> 2) : (ct >> 3);
+    if (em < M) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < MG_CONSUMERS; ++w) t += o.red[em][w];
+      rs = rsqrtf(t * o.inv_k + o.eps);
+    }
+  }
   const uint4* xq = c.xin + ((size_t)((g * n_ks) * 8 + cw) * 4 + t) * 4;      // + ks * 128 uint4 per k-stage
 
   for (int grp = g0; grp < g1; ++grp) {
@@ -262,8 +248,8 @@ __device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, const Mega
           float gate = 0.f, up = 0.f;
 #pragma unroll
           for (int w = 0; w < MG_CONSUMERS; ++w) { gate += buf[w][m][2 * pp]; up += buf[w][m][2 * pp + 1]; }
-          gate = __bfloat162float(__float2bfloat16(gate));
-          up = __bfloat162float(__float2bfloat16(up));
+          gate = __bfloat162float(__float2bfloat16(gate * rs));
+          up = __bfloat162float(__float2bfloat16(up * rs));
           h = silu(gate) * up;
         }
         const float h1 = __shfl_down_sync(0xffffffffu, h, 1);
@@ -278,6 +264,7 @@ __device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, const Mega
         if (valid) {
 #pragma unroll
           for (int w = 0; w < MG_CONSUMERS; ++w) v += buf[w][m][n];
+          v *= rs;
         }
         const int row = grp * MG_GROUP + n;
         if constexpr (CARRY == 1) {

@@ -81,14 +81,18 @@ class LLaMAConfig:
     # ------------------------------------------------------------------ derived
     @property
     def head_dim(self) -> int:
-        return self.hidden_size // self.num_attention_heads
+        """hidden_size // num_attention_heads as in the reference (model.py:115), unless the config carries an
+        explicit ``head_dim`` key (newer HF Llama configs do): then q/o project to ``num_attention_heads * head_dim``
+        columns, which need not equal hidden_size — e.g. the per-rank slice of a tensor-parallel model as a model."""
+        hd = self.extra.get("head_dim") if hasattr(self, "extra") else None
+        return int(hd) if hd else self.hidden_size // self.num_attention_heads
 
     @property
     def n_rep(self) -> int:
         return self.num_attention_heads // self.num_key_value_heads
 
     def validate(self) -> None:
-        if self.hidden_size % self.num_attention_heads:
+        if not self.extra.get("head_dim") and self.hidden_size % self.num_attention_heads:
             raise ValueError("hidden_size must be divisible by num_attention_heads")
         if self.num_attention_heads % self.num_key_value_heads:
             raise ValueError("num_attention_heads must be divisible by num_key_value_heads")
@@ -98,7 +102,7 @@ class LLaMAConfig:
     def num_params(self) -> int:
         h, f, v, l = self.hidden_size, self.intermediate_size, self.vocab_size, self.num_hidden_layers
         kv = self.num_key_value_heads * self.head_dim
-        per_layer = h * h * 2 + 2 * h * kv + 3 * h * f + 2 * h
+        per_layer = h * self.num_attention_heads * self.head_dim * 2 + 2 * h * kv + 3 * h * f + 2 * h
         head = 0 if self.tie_word_embeddings else v * h
         return v * h + l * per_layer + h + head
 

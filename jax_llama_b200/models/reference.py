@@ -233,12 +233,13 @@ def init_params(config: LLaMAConfig, seed: int = 0, dtype: torch.dtype = torch.f
 
     h, f, v = config.hidden_size, config.intermediate_size, config.vocab_size
     kv = config.num_key_value_heads * config.head_dim
+    qd = config.num_attention_heads * config.head_dim          # == h unless the config sets head_dim explicitly
     ones = lambda: torch.ones(h, dtype=dtype, device=device)  # noqa: E731
     layers = {}
     for i in range(config.num_hidden_layers):
         layers[str(i)] = {
-            "attention": {"wq": {"kernel": mat(h, h)}, "wk": {"kernel": mat(h, kv)},
-                          "wv": {"kernel": mat(h, kv)}, "wo": {"kernel": mat(h, h)}},
+            "attention": {"wq": {"kernel": mat(h, qd)}, "wk": {"kernel": mat(h, kv)},
+                          "wv": {"kernel": mat(h, kv)}, "wo": {"kernel": mat(qd, h)}},
             "feed_forward": {"w1": {"kernel": mat(h, f)}, "w2": {"kernel": mat(f, h)},
                              "w3": {"kernel": mat(h, f)}},
             "attention_norm": {"kernel": ones()}, "ffn_norm": {"kernel": ones()},

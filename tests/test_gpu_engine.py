@@ -159,34 +159,88 @@ def test_public_generate_api_on_gpu():
 
 @pytest.mark.parametrize("B", [1, 2, 4, 7, 8, -6, -8])
 def test_megakernel_step_matches_unfused_step(B, monkeypatch):
-    """The persistent whole-model decode kernel against the per-op kernels, several consecutive steps."""
+    """The persistent whole-model decode kernel against the per-op kernels, several consecutive steps.  Both paths
+    are fed the SAME tokens (the per-op engine's choices): with free-running greedy decoding one near-tie that flips
+    under bf16 rounding sends the two runs down different sequences and the comparison means nothing."""
     if B < 0:          # batch > 4 with w2 walked in two K passes (what a wide FFN forces; forced here at a small shape)
         monkeypatch.setenv("JLLAMA_MEGA_W2_PASSES", "2")
         B = -B
     cfg = LLaMAConfig(vocab_size=1000, hidden_size=512, intermediate_size=1536, num_hidden_layers=3,
                       num_attention_heads=4, num_key_value_heads=2, max_sequence_length=256, initializer_range=0.05)
     tree = tree_to(ref.init_params(cfg, seed=2), dtype=torch.bfloat16, device="cuda")
-    engines = [B200Engine.from_tree(cfg, tree, use_cuda_graph=False, use_megakernel=flag) for flag in (True, False)]
-    assert engines[0].use_megakernel and not engines[1].use_megakernel
-    engines[0].mega_write_logits = True          # the greedy path keeps only arg-max candidates unless asked
+    engines = [B200Engine.from_tree(cfg, tree, use_cuda_graph=False, use_megakernel=flag) for flag in (False, True)]
+    assert engines[1].use_megakernel and not engines[0].use_megakernel
+    engines[1].mega_write_logits = True          # the greedy path keeps only arg-max candidates unless asked
     ids = torch.randint(3, cfg.vocab_size, (B, 37), generator=torch.Generator().manual_seed(7)).cuda()
     mask = torch.ones(B, 37, dtype=torch.int32, device="cuda")
     if B > 1:
         mask[1, :6] = 0
-    outs = []
-    for eng in engines:
+    outs, fed = [], []
+    for which, eng in enumerate(engines):
         st = eng._decode_state(B, 64)
         cache = eng.prepare(st, ids, mask, 0)
         sampling = (False, 1.0, 0, 1.0, 0)
         eng._select_and_advance_after_prefill(st, cache, sampling, -7, 0)
         logits = []
-        for _ in range(5):
+        for i in range(5):
+            if which == 0:
+                fed.append(st.ids.clone())
+            else:
+                st.ids.copy_(fed[i])
             eng._decode_step(st, cache, sampling, -7, 0)
             logits.append(st.logits.clone())
         outs.append((torch.stack(logits), cache.k[:, :, :, :43].clone(), st.sequences.clone()))
-    assert rel(outs[0][0], outs[1][0]) < 2e-2
-    assert rel(outs[0][1], outs[1][1]) < 2e-2
+    assert rel(outs[0][0], outs[1][0]) < 2.5e-2
+    assert rel(outs[0][1], outs[1][1]) < 2.5e-2
     # the token the fused arg-max picked is the arg-max of the logits the same kernel wrote (ties: lower index)
-    seqs = outs[0][2]
+    seqs = outs[1][2]
     for i in range(5):
-        assert torch.equal(seqs[:, 38 + i].long(), outs[0][0][i].argmax(-1)), i
+        assert torch.equal(seqs[:, 38 + i].long(), outs[1][0][i].argmax(-1)), i
+
+
+# The shapes the benchmarks run, two layers each (SURVEY §2.6 table): 8B on one GPU (GQA group 4), the per-rank
+# slice of 8B at TP=8 (one KV head, group 4), of 13B at TP=2 (MHA, group 1) and of 70B at TP=8 (group 8, H = 8192).
+MEGA_SHAPES = {
+    "8b_tp1": dict(hidden_size=4096, intermediate_size=14336, num_attention_heads=32, num_key_value_heads=8),
+    "8b_tp8_slice": dict(hidden_size=4096, intermediate_size=1792, num_attention_heads=4, num_key_value_heads=1),
+    "13b_tp2_slice": dict(hidden_size=5120, intermediate_size=6912, num_attention_heads=20, num_key_value_heads=20),
+    "70b_tp8_slice": dict(hidden_size=8192, intermediate_size=3584, num_attention_heads=8, num_key_value_heads=1),
+}
+
+
+@pytest.mark.parametrize("shape", list(MEGA_SHAPES))
+@pytest.mark.parametrize("B,ctx", [(1, 40), (4, 40), (8, 40), (1, 300)])
+def test_megakernel_matches_fp32_oracle_at_benchmark_shapes(shape, B, ctx):
+    """Decode-kernel logits against the fp32 reference model (not against other kernels), teacher-forced, for the
+    GQA groups / hidden sizes / FFN widths of the benchmarked configurations; ctx = 300 exercises more than one
+    split-KV chunk per head and the split merge.  Reference: last-token logits within tolerance, as
+    /root/reference/jax_test.py:427-490 does for the real checkpoints."""
+    kw = MEGA_SHAPES[shape]
+    cfg = LLaMAConfig(vocab_size=2048, num_hidden_layers=2, max_sequence_length=512, initializer_range=0.02,
+                      head_dim=128, **kw)
+    assert cfg.head_dim == 128
+    tree = tree_to(ref.init_params(cfg, seed=3), dtype=torch.bfloat16)
+    tree32 = tree_to(tree, dtype=torch.float32)
+    eng = B200Engine.from_tree(cfg, tree_to(tree, device="cuda"), use_cuda_graph=False)
+    if not eng._mega_fits(B):
+        pytest.skip("batch does not fit the whole-step kernel at this shape")
+    eng.mega_write_logits = True
+    g = torch.Generator().manual_seed(11)
+    ids = torch.randint(3, cfg.vocab_size, (B, ctx), generator=g)
+    nxt = torch.randint(3, cfg.vocab_size, (3, B), generator=g)
+    st = eng._decode_state(B, ctx + 8)
+    cache = eng.prepare(st, ids.cuda(), None, 0)
+    samp = (False, 1.0, 0, 1.0, 0)
+    eng._select_and_advance_after_prefill(st, cache, samp, -7, 0)
+    got = []
+    for i in range(3):
+        st.ids.copy_(nxt[i].to(torch.int32))
+        eng._decode_step(st, cache, samp, -7, 0)
+        got.append(st.logits.clone().cpu())
+    seq = torch.cat([ids, nxt.t()], dim=1)
+    want = ref.forward(tree32, cfg, seq).logits
+    for i in range(3):
+        w = want[:, ctx + i]
+        scale = float(w.abs().max())
+        assert rel(got[i], w) < 3e-2, (i, rel(got[i], w))
+        assert torch.allclose(got[i], w, rtol=5e-2, atol=3e-2 * scale), i
