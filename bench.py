@@ -125,7 +125,7 @@ def tp_check(args, cfg, eng, dev, rank: int, world: int) -> dict:
         eng_tp = B200Engine.random_init(ccfg, dev, seed=0, tp=world, rank=rank, comm=eng.comm)
         own = True
     full = B200Engine.random_init(ccfg, dev, seed=0)
-    P, n_new, B = 256, 16, 1
+    P, n_new, B = 1024, 16, 1
     g = torch.Generator().manual_seed(4321)
     ids = torch.randint(0, ccfg.vocab_size, (B, P), generator=g).to(dev)
     want = full.forward(ids, last_only=True).logits[:, 0].float()
@@ -256,26 +256,37 @@ def main() -> None:
         if i > 0:
             prefill_ms.append(max_over_ranks(e0.elapsed_time(e1)))
     prefill_best = min(prefill_ms)
-    # the fused sequence-parallel chain (all-gather→GEMM / GEMM→reduce-scatter over peer memory), timed for the
-    # record next to the default path (tcgen05 GEMM + NCCL all-reduce), whichever of the two is the default
+    # the other prefill paths of the same engine, timed for the record: GEMM + in-switch all-reduce kernel, and the
+    # same with the all-reduce done by NCCL (the baseline arm; nothing in the engine calls NCCL by itself)
+    PATH_NAMES = {"single": "single GPU", "sequence_parallel": "fused sequence-parallel (NVLS reduce-scatter / all-gather)",
+                  "allreduce": "GEMM + in-switch all-reduce kernel (multimem.ld_reduce)",
+                  "nccl": "GEMM + NCCL all-reduce (baseline arm)"}
+    default_path = ("single" if world == 1 else
+                    "sequence_parallel" if (eng.sequence_parallel_prefill and (B * P) % (128 * world) == 0) else "allreduce")
     prefill_alt = None
-    if world > 1 and (B * P) % (128 * world) == 0:
-        was = eng.sequence_parallel_prefill
-        eng.sequence_parallel_prefill = not was
-        alt = []
-        for i in range(1 + args.prefill_reps):
-            barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            eng.prepare(st, ids_dev, None, 0)
-            e1.record()
-            torch.cuda.synchronize()
-            if i > 0:
-                alt.append(max_over_ranks(e0.elapsed_time(e1)))
-        eng.sequence_parallel_prefill = was
+    if world > 1:
+        prefill_alt = []
+        for path in ("sequence_parallel", "allreduce", "nccl"):
+            if path == default_path or (path == "sequence_parallel" and (B * P) % (128 * world)):
+                continue
+            eng.set_prefill_path("allreduce" if path == "nccl" else path)
+            nv = eng.comm.nvls_state(B * P, cfg.hidden_size)
+            nv.use_nccl_baseline = path == "nccl"
+            alt = []
+            for i in range(1 + args.prefill_reps):
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                eng.prepare(st, ids_dev, None, 0)
+                e1.record()
+                torch.cuda.synchronize()
+                if i > 0:
+                    alt.append(max_over_ranks(e0.elapsed_time(e1)))
+            nv.use_nccl_baseline = False
+            prefill_alt.append({"path": PATH_NAMES[path], "ms": round(min(alt), 3),
+                                "tokens_per_sec": round(B * P / (min(alt) / 1e3), 1)})
+        eng.set_prefill_path(None)
         eng.prepare(st, ids_dev, None, 0)
-        prefill_alt = {"path": "fused sequence-parallel" if not was else "GEMM + NCCL all-reduce",
-                       "ms": round(min(alt), 3), "tokens_per_sec": round(B * P / (min(alt) / 1e3), 1)}
 
     # ---------------------------------------------------------------- device-timed decode steps
     stream = llama.stream(prompt, mask, max_gen_len=max_len - P, temperature=0.0, top_p=1.0)
@@ -368,8 +379,7 @@ def main() -> None:
             "hbm_roofline_frac_of_measured": round((weight_bytes / (ms_per_step / 1e3)) / (hbm * 1e9), 4),
             "prefill": {"tokens_per_sec": round(B * P / (prefill_best / 1e3), 1), "ms": round(prefill_best, 3),
                         "prompt_len": P, "includes": "embedding..lm_head(last token) of the prompt",
-                        "path": ("single GPU" if world == 1 else
-                                 "fused sequence-parallel" if eng.sequence_parallel_prefill else "GEMM + NCCL all-reduce"),
+                        "path": PATH_NAMES[default_path],
                         "other_path": prefill_alt},
             "e2e": {"value": round(B * args.steps / (e2e_ms / 1e3), 2), "unit": "tokens/s",
                     "h2d_bytes_per_step": stream2.h2d_bytes, "d2h_bytes_per_step": stream2.d2h_bytes,

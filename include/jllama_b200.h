@@ -186,6 +186,8 @@ int jl_allgather_small(const void* src, void* out, int n_bytes, int slot_bytes, 
                        void* const* peer_inbox, void* const* peer_flags, size_t parity_stride_bytes,
                        int flag_offset, const int* seq_ptr, int call_index, void* stream);
 int jl_comm_bump(int* seq_ptr, int n, void* stream);
+/* one warp waits (on the stream) until flags[0..tp) >= epoch: later kernels may read what the peers published first */
+int jl_wait_flags(const int* flags, int epoch, int tp, int rank, void* stream);
 int jl_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream);
 
 /* Sequence-parallel prefill (M % (128*tp) == 0).  The residual stream is sharded by rows; per layer:
@@ -207,6 +209,17 @@ int jl_gemm_rs(const void* x, const void* w, void* const* peer_rs_buf, int M, in
 int jl_rs_reduce(void* x, const void* partials, const void* norm_w, void* const* xn_peers, int xn_row0, int mloc,
                  int H, int n_src, int tp, int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off,
                  int gemm_epoch, int ready_epoch, int* ticket, float eps, void* stream);
+
+/* NVLS form of the owner-side step of the sequence-parallel prefill, and the all-reduce of a row-parallel GEMM for any
+ * token count (partition.py:67,70 is what GSPMD all-reduced there).  The GEMM before it stored this rank's bf16 partial
+ * product into its own copy of a symmetric buffer; `part_mc` is the multicast address of that buffer at the first of
+ * the `rows` rows this call owns: x[rows, H] += sum over ranks (multimem.ld_reduce, fp32 in the switch).  With `xn_mc`
+ * (multicast address of the gathered-activation buffer at the same first row) the updated rows are RMS-normalised and
+ * stored into every rank's copy with multimem.st, then the "rows ready" flag is published; without it the call is a
+ * plain all-reduce into a replicated residual stream (rows = all tokens). */
+int jl_rs_reduce_mm(void* x, const void* part_mc, const void* norm_w, void* xn_mc, int rows, int H, int has_partials,
+                    int tp, int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off, int gemm_epoch,
+                    int ready_epoch, int* ticket, float eps, void* stream);
 
 /* NVLS self-test over a multicast mapping of a symmetric buffer (parallel/symm.py): `mc` is the multicast
  * address.  op 0: out[i] = sum over ranks of fp32 buf[i] (multimem.ld_reduce); 1: 8-byte packets {src[i], tag}

@@ -128,11 +128,9 @@ class B200Engine:
         self.mega_write_logits = False      # True: the decode kernel also stores the fp32 [B, V] logits (tests, forward-style use)
         if self.device.type == "cuda":
             K.ensure_gemm_workspace(self.device)          # split-K scratch of the small-batch GEMMs (before any capture)
-        # Prefill at tp > 1.  Measured on 8xB200, LLaMA-3 8B, 2048 tokens (ms): fused sequence-parallel chain
-        # (rows pushed by their owners, tiles scattered from the GEMM epilogue) 18.0 / 15.3 at tp = 2 / 8, the
-        # earlier pull-gather 17.3 / 17.9, tcgen05 GEMM + NCCL all-reduce (NVLS in-switch reduction) 16.7 / 13.0.
-        # The fastest path is the default; JLLAMA_SP=1 selects the fused chain (tested in tests/tp_worker.py).
-        self.sequence_parallel_prefill = os.environ.get("JLLAMA_SP", "0") == "1"
+        # Prefill at tp > 1 runs over NVLS (parallel/comm.py `NvlsPrefill`): sequence-parallel when the token count is a
+        # multiple of 128·tp, otherwise tcgen05 GEMM + in-switch all-reduce kernel.  JLLAMA_SP=0 forces the latter.
+        self.sequence_parallel_prefill = os.environ.get("JLLAMA_SP", "1") != "0"
         self.use_megakernel = use_megakernel and self.hd == 128 \
             and config.hidden_size % 256 == 0 and (config.intermediate_size // self.tp) % 256 == 0 \
             and (self.nh * self.hd) % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
@@ -333,21 +331,23 @@ class B200Engine:
     def _prefill_sp(self, input_ids: torch.Tensor, cache: DeviceKVCache, B: int, S: int) -> torch.Tensor:
         """Megatron-style sequence-parallel prefill (a capability the reference does not have).
 
-        The residual stream lives sharded by token rows ([M/tp, H] per rank).  Column-parallel GEMMs
-        (wqkv, w1·w3) gather the normalised shards of all ranks inside the kernel; row-parallel GEMMs (wo, w2)
-        scatter their partial output tiles to the row owners from the epilogue; the owner sums, adds the
-        residual and normalises for the next GEMM (`SPState.rs_reduce`).  Returns this rank's vocabulary slice
-        of the last-position logits, [B, V/tp] fp32."""
+        The residual stream lives sharded by token rows ([M/tp, H] per rank).  Row-parallel GEMMs (wo, w2) keep
+        their partial product on the rank that computed it; the owner of a row pulls the sum over ranks with
+        `multimem.ld_reduce` (reduced inside the NVSwitch), adds the residual, normalises and stores the row into
+        every rank's copy of the gathered activations with `multimem.st` (`NvlsPrefill.rs_reduce`); column-parallel
+        GEMMs (wqkv, w1·w3) read that local copy, their TMA producer waiting per row owner for its flag
+        (`NvlsPrefill.ag_gemm`).  No NCCL call.  Returns this rank's vocabulary slice of the last-position logits,
+        [B, V/tp] fp32."""
         c = self.config
         eps = c.rms_norm_eps
         nh, nkv, hd = self.nh, self.nkv, self.hd
         M = B * S
-        sp = self.comm.sp_state(M, c.hidden_size, c.hidden_size)
+        sp = self.comm.nvls_state(M, c.hidden_size)
         mloc, r = sp.mloc, self.rank
         start = cache.index
         ids = input_ids.reshape(-1)
         x = K.embed(ids[r * mloc:(r + 1) * mloc], self.embedding)                 # this rank's rows of the stream
-        sp.rs_reduce(x, self.layers[0].attn_norm, eps, n_src=0)                  # starts the chain: norm + publish
+        sp.rs_reduce(x, self.layers[0].attn_norm, eps, has_partials=False)       # starts the chain: norm + broadcast
         for i, l in enumerate(self.layers):
             kc, vc = cache.k[i], cache.v[i]
             qkv = sp.ag_gemm(l.wqkv, K.PLAIN)                                    # [M, (nh+2nkv)·hd] local heads, all tokens
@@ -355,20 +355,15 @@ class B200Engine:
             K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
                             pad_left=cache.pad_left, q_out=q_rot)
             attn = self._prefill_attn(q_rot.view(B, S, nh, hd), kc, vc, start, S, cache).view(M, nh * hd)
-            sp.gemm_rs(attn, l.wo)
-            sp.rs_reduce(x, l.ffn_norm, eps, n_src=self.tp)
+            K.linear(attn, l.wo, out=sp.next_part())                             # partial product stays on this rank
+            sp.rs_reduce(x, l.ffn_norm, eps, has_partials=True)                  # in-switch reduce-scatter + norm + all-gather
             h = sp.ag_gemm(l.w13, K.SWIGLU)
-            sp.gemm_rs(h, l.w2)
+            K.linear(h, l.w2, out=sp.next_part())
             nxt = self.layers[i + 1].attn_norm if i + 1 < len(self.layers) else self.final_norm
-            sp.rs_reduce(x, nxt, eps, n_src=self.tp)
-        # last position of every batch row, already final-normed, lives on the rank that owns that row
-        import torch.distributed as dist
+            sp.rs_reduce(x, nxt, eps, has_partials=True)
+        # last position of every batch row, already final-normed: its owner stored it into every rank's copy
         last = torch.arange(B, device=self.device) * S + (S - 1)
-        mine = (last // mloc) == r
-        xl = torch.zeros((B, c.hidden_size), dtype=torch.bfloat16, device=self.device)
-        if bool(mine.any()):
-            xl[mine] = sp.read_rows(last[mine])
-        dist.all_reduce(xl, group=self.comm.group)                                # B rows: off the hot path
+        xl = sp.read_rows(last).contiguous()
         return K.linear(xl, self.lm_head, out_f32=True)
 
     def _row_parallel(self, a: torch.Tensor, w: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
@@ -379,10 +374,18 @@ class B200Engine:
         if m <= 8:
             # decode: GEMV + one-shot all-reduce over NVLink peer memory + residual, one kernel
             return self.comm.gemv_allreduce(a, w, x, out=x)
-        # larger M: tcgen05 GEMM, then the NCCL baseline all-reduce (fused GEMM→reduce-scatter: see parallel/)
-        y = K.linear(a, w)
-        self.comm.allreduce_nccl(y)
-        return x.add_(y)
+        # larger M: tcgen05 GEMM into this rank's copy of a symmetric buffer, then one kernel in which every rank
+        # pulls the in-switch sum (multimem.ld_reduce) and adds it to its replicated residual stream
+        st = self.comm.nvls_state(m, w.shape[0])
+        K.linear(a, w, out=st.next_part())
+        return st.allreduce_add(x)
+
+    def prefill_paths(self) -> List[str]:
+        return ["single"] if self.tp == 1 else ["sequence_parallel", "allreduce"]
+
+    def set_prefill_path(self, name: Optional[str]) -> None:
+        """`sequence_parallel` (default when the token count allows), `allreduce`, or None = the default."""
+        self.sequence_parallel_prefill = name in (None, "sequence_parallel") and os.environ.get("JLLAMA_SP", "1") != "0"
 
     def _prefill_attn(self, q: torch.Tensor, kc: torch.Tensor, vc: torch.Tensor, start: int, S: int,
                       cache: DeviceKVCache) -> torch.Tensor:

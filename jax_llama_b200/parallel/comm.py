@@ -39,11 +39,15 @@ _EXTRA_SIGNATURES = {
     "jl_allgather_small": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "jl_comm_bump": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "jl_wait_flags": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "jl_memcpy_d2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "jl_ag_gemm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                              C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "jl_gemm_rs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                              C.c_void_p]),
+    "jl_rs_reduce_mm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                  C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
+                                  C.c_void_p]),
     "jl_rs_reduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
                                C.c_void_p]),
@@ -222,6 +226,14 @@ class PeerComm:
             states[key] = SPState(self, M, H, kmax)
         return states[key]
 
+    def nvls_state(self, M: int, H: int) -> "NvlsPrefill":
+        """Symmetric (multicast-mapped) buffers of the prefill collectives for one (tokens, hidden) shape."""
+        key = (M, H)
+        states = self.__dict__.setdefault("_nvls_states", {})
+        if key not in states:
+            states[key] = NvlsPrefill(self, M, H)
+        return states[key]
+
     # ------------------------------------------------------------------ NCCL baseline (measured, not the product)
     def allreduce_nccl(self, t: torch.Tensor) -> torch.Tensor:
         if self.tp > 1:
@@ -302,3 +314,94 @@ class SPState:
         _lib.check(_L().jl_memcpy_d2d(out.data_ptr(), src, out.numel() * 2, K._stream()),
                    "jl_memcpy_d2d")
         return out[rows - self.comm.rank * self.mloc]
+
+
+class NvlsPrefill:
+    """Prefill collectives over an NVLS multicast mapping (csrc/sp_prefill.cu, `rs_reduce_mm_kernel`).
+
+    part[2]    [M][H] bf16   this rank's partial product of a row-parallel GEMM (wo / w2 alternate between the two);
+                             the GEMM stores it locally, peers read it only through ``multimem.ld_reduce``
+    a_full[2]  [M][H] bf16   gathered, normalised activations, double-buffered by parity; row owners fill every rank's
+                             copy with ``multimem.st``
+
+    Two ways to use it, both without NCCL:
+    * sequence parallel (token count a multiple of 128·tp): `rs_reduce` on the rank's row shard, `ag_gemm`;
+    * `allreduce_add` for any token count: every rank pulls the in-switch sum of all rows into its replicated stream.
+    """
+
+    def __init__(self, comm: PeerComm, M: int, H: int):
+        from .symm import SymmetricHeap
+        self.comm, self.M, self.H = comm, M, H
+        tp = comm.tp
+        self.sp_ok = M % (tp * 128) == 0
+        self.mloc = M // tp if self.sp_ok else 0
+        one = (M * H * 2 + 1023) // 1024 * 1024
+        self.heap = SymmetricHeap(tp, comm.rank, comm.device, 4 * one + 4096, group=comm.group)
+        if tp > 1 and not self.heap.has_multicast:
+            raise RuntimeError("this platform gave the symmetric heap no NVLS multicast address")
+        self.part_off = [self.heap.alloc(one), self.heap.alloc(one)]
+        self.a_off = [self.heap.alloc(one), self.heap.alloc(one)]
+        self.part = [self.heap.view(o, (M, H), torch.bfloat16) for o in self.part_off]
+        self.counters = torch.zeros(max(1, M // 128), dtype=torch.int32, device=comm.device)
+        self.ticket = torch.zeros(1, dtype=torch.int32, device=comm.device)
+        self.gemm_off = comm.flag_block(("nvls_gemm",), MAX_TP)
+        self.ready_off = comm.flag_block(("nvls_ready",), MAX_TP)
+        self.parity = 0
+        self.slot = 0
+        self.use_nccl_baseline = False          # bench only: time the NCCL all-reduce in place of the in-switch pull
+        comm.__dict__.setdefault("_nvls_epochs", {"gemm": 0, "ready": 0})
+        self.ep = comm._nvls_epochs            # epochs persist across forwards and shapes (flags are never reset)
+
+    def next_part(self) -> torch.Tensor:
+        """Output buffer of the next row-parallel GEMM (its partial product stays on this rank)."""
+        self.slot ^= 1
+        return self.part[self.slot]
+
+    def allreduce_add(self, x: torch.Tensor) -> torch.Tensor:
+        """x += Σ_ranks part (the buffer handed out by the last `next_part`), all rows, replicated result."""
+        cm = self.comm
+        if self.use_nccl_baseline:
+            y = self.part[self.slot].clone()
+            dist.all_reduce(y, group=cm.group)
+            return x.add_(y)
+        self.ep["gemm"] += 1
+        _lib.check(_L().jl_rs_reduce_mm(x.data_ptr(), self.heap.mc(self.part_off[self.slot]), None, None, self.M, self.H,
+                                        1, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off, self.ready_off,
+                                        self.ep["gemm"], 0, self.ticket.data_ptr(), 0.0, K._stream()), "jl_rs_reduce_mm")
+        return x
+
+    def rs_reduce(self, x_shard: torch.Tensor, norm_w: torch.Tensor, eps: float, has_partials: bool) -> None:
+        """Owner step: x_shard += in-switch Σ of this rank's rows; RMSNorm → every rank's a_full[next parity]; publish."""
+        cm = self.comm
+        self.parity ^= 1
+        self.ep["ready"] += 1
+        if has_partials:
+            self.ep["gemm"] += 1
+        row0 = cm.rank * self.mloc * self.H * 2
+        part_mc = self.heap.mc(self.part_off[self.slot] + row0) if has_partials else None
+        _lib.check(_L().jl_rs_reduce_mm(x_shard.data_ptr(), part_mc, norm_w.data_ptr(),
+                                        self.heap.mc(self.a_off[self.parity] + row0), self.mloc, self.H,
+                                        1 if has_partials else 0, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off,
+                                        self.ready_off, self.ep["gemm"], self.ep["ready"], self.ticket.data_ptr(),
+                                        float(eps), K._stream()), "jl_rs_reduce_mm")
+
+    def ag_gemm(self, w: torch.Tensor, mode: int) -> torch.Tensor:
+        """y = (gathered normalised rows) · wᵀ; the GEMM's TMA producer waits per row owner for its "ready" flag."""
+        cm = self.comm
+        n, k = w.shape
+        odim = n // 2 if mode == K.SWIGLU else n
+        out = torch.empty((self.M, odim), dtype=torch.bfloat16, device=cm.device)
+        flags_local = cm._own_flags + 4 * self.ready_off
+        _lib.check(_L().jl_ag_gemm(None, self.heap.local_ptr + self.a_off[self.parity], w.data_ptr(), out.data_ptr(),
+                                   self.M, n, k, mode, cm.tp, cm.rank, flags_local, self.ep["ready"],
+                                   self.counters.data_ptr(), K.num_sms(cm.device), K._stream()), "jl_ag_gemm")
+        return out
+
+    def read_rows(self, rows: torch.Tensor) -> torch.Tensor:
+        """Rows (global token indices) of the current gathered, normalised activations.  Every rank holds all rows
+        (their owners stored them into every copy); a one-warp kernel first waits for the owners' "ready" flags."""
+        cm = self.comm
+        _lib.check(_L().jl_wait_flags(cm._own_flags + 4 * self.ready_off, self.ep["ready"], cm.tp, cm.rank, K._stream()),
+                   "jl_wait_flags")
+        a = self.heap.view(self.a_off[self.parity], (self.M, self.H), torch.bfloat16)
+        return a[rows]

@@ -91,15 +91,22 @@ def main():
     ids_sp = torch.randint(3, cfg.vocab_size, (2, S), generator=torch.Generator().manual_seed(9))
     assert (2 * S) % (128 * world) == 0
     want_sp = ref.forward(full32, cfg, ids_sp).logits[:, -1]
-    eng.sequence_parallel_prefill = True                # the fused chain is opt-in (JLLAMA_SP=1): see engine.py
+    eng.set_prefill_path("sequence_parallel")           # NVLS reduce-scatter + all-gather around the GEMMs (the default)
     for _ in range(2):                                  # twice: epochs, parities and counters must re-arm
         cache = eng.new_cache(2, S + 8)
         got_sp = eng.forward(ids_sp.to(dev), cache=cache, last_only=True).logits[:, 0]
         assert got_sp.shape == want_sp.shape and rel(got_sp, want_sp) < 3e-2, rel(got_sp, want_sp)
-    eng.sequence_parallel_prefill = False               # same prefill through the NCCL-all-reduce path
+    eng.set_prefill_path("allreduce")                   # same prefill through GEMM + in-switch all-reduce kernel
     cache2 = eng.new_cache(2, S + 8)
-    got_nccl = eng.forward(ids_sp.to(dev), cache=cache2, last_only=True).logits[:, 0]
-    assert rel(got_sp, got_nccl) < 3e-2 and rel(cache.k, cache2.k) < 2e-2
+    got_ar = eng.forward(ids_sp.to(dev), cache=cache2, last_only=True).logits[:, 0]
+    assert rel(got_ar, want_sp) < 3e-2, rel(got_ar, want_sp)
+    assert rel(got_sp, got_ar) < 3e-2 and rel(cache.k, cache2.k) < 2e-2
+    eng.set_prefill_path(None)
+    # a token count that is not a multiple of 128·tp takes the all-reduce path on its own
+    ids_odd = ids_sp[:, :S - 3]
+    want_odd = ref.forward(full32, cfg, ids_odd).logits[:, -1]
+    got_odd = eng.forward(ids_odd.to(dev), last_only=True).logits[:, 0]
+    assert rel(got_odd, want_odd) < 3e-2, rel(got_odd, want_odd)
     # ---- 4. flag / epoch protocol stress: ranks enter every collective at random, different times
     # (a device-side sleep of up to ~200 us per rank per call) for many back-to-back calls; payloads change
     # every iteration so that a stale inbox slot, a reused flag or a parity mix-up shows up as a wrong sum.
