@@ -173,10 +173,10 @@ __global__ void __launch_bounds__(256) allgather_small_kernel(const GatherParams
 }
 
 // stream-side wait: later kernels on this stream may read what the peers published before raising their flags
-__global__ void wait_flags_kernel(const int* flags, int epoch, int tp, int rank) {
+__global__ void wait_flags_kernel(const int* flags, int epoch, const int* seq_ptr, int tp, int rank) {
   pdl_wait();
   pdl_launch_dependents();
-  if (threadIdx.x < tp) wait_flag(flags + threadIdx.x, epoch, rank, threadIdx.x, 6);
+  if (threadIdx.x < tp) wait_flag(flags + threadIdx.x, epoch + (seq_ptr ? *seq_ptr : 0), rank, threadIdx.x, 6);
 }
 
 __global__ void bump_kernel(int* seq, int n) {
@@ -269,9 +269,9 @@ extern "C" JL_API int jl_allgather_small(const void* src, void* out, int n_bytes
   return JL_OK;
 }
 
-extern "C" JL_API int jl_wait_flags(const int* flags, int epoch, int tp, int rank, void* stream) {
+extern "C" JL_API int jl_wait_flags(const int* flags, int epoch, const int* seq_ptr, int tp, int rank, void* stream) {
   JL_CHECK_ARG(flags && tp >= 1 && tp <= MAX_TP, "jl_wait_flags: bad arguments");
-  JL_CUDA(launch_pdl(wait_flags_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, flags, epoch, tp, rank));
+  JL_CUDA(launch_pdl(wait_flags_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, flags, epoch, seq_ptr, tp, rank));
   return JL_OK;
 }
 

@@ -110,7 +110,8 @@ struct MegaParams {
   uint2* part_pk;                    // [M·nh][splits][130]   split-KV partials ({fp32, tag})
   uint2* attn_pk;                    // [M][nh·hd/2]
   uint2* h_pk;                       // [M][F/2]
-  float* logits;                     // [M, V] or null
+  float* logits;                     // [M, logits_ld] or null; this rank's V columns start at logits_col0
+  int logits_ld, logits_col0, logits_mc;     // logits_mc: `logits` is a multicast address (every rank gets every shard)
   __nv_bfloat16* kc;                 // [L][M][nkv][T][hd]
   __nv_bfloat16* vc;
   const float* cos_t;
@@ -736,6 +737,7 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   const size_t r_half = (size_t)M * (p.H / 2);               // packets of one parity half of the residual buffer
   MegaOut o;
   o.res = s_res; o.row0 = own0; o.logits = nullptr; o.best_v = nullptr; o.best_i = nullptr; o.idx_offset = 0;
+  o.logits_ld = 0; o.logits_col0 = 0; o.logits_mc = false;
   o.pk = nullptr; o.r_pk = nullptr; o.tag = 0; o.red = nullptr; o.inv_k = 0.f; o.eps = p.eps;
   for (int l = 0; l < p.L; ++l) {
     const uint32_t t1 = base + 2u * l + 1u, t2 = t1 + 1u;      // t1 odd, t2 even
@@ -815,10 +817,14 @@ decode_mega_kernel(const __grid_constant__ MegaTmaps tm, const MegaParams p) {
   mg_stage_packets<M>(c.xin, p.r_pk, t_last, p.H, p.H / 2, p.final_norm, red, MG_W_X, c.trace_row);
   float best_v = -INFINITY;
   int best_i = 0x7fffffff;
-  o.logits = p.logits; o.best_v = &best_v; o.best_i = &best_i; o.idx_offset = p.ar.rank * p.V;
+  o.logits = p.logits; o.logits_ld = p.logits_ld; o.logits_col0 = p.logits_col0; o.logits_mc = p.logits_mc != 0;
+  o.best_v = &best_v; o.best_i = &best_i; o.idx_offset = p.ar.rank * p.V;
   o.red = red; o.inv_k = 1.f / (float)p.H;
   mg_gemv_mma<M, MG_LOGITS>(c, p.V, p.H, o, s_acc);
   if (ct < 64) {                                             // thread (m, n): fold the 8 weight-row lanes of a batch row
+    // logits stored into the other ranks' buffers must be there before the candidate packet that announces them
+    if (p.logits != nullptr && p.logits_mc) __threadfence_system();
+    __syncwarp();
 #pragma unroll
     for (int off = 1; off < 8; off <<= 1) {
       const float ov = __shfl_xor_sync(0xffffffffu, best_v, off);
@@ -1004,7 +1010,7 @@ extern "C" JL_API int jl_decode_mega_stages(int M, int H, int F, int nh, int nkv
 extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
                                      const void* lm_head, const void* attn_norm, const void* ffn_norm,
                                      const void* final_norm, const void* embedding, const int* ids, float* logits,
-                                     void* k_cache, void* v_cache, const float* cos_t, const float* sin_t,
+                                     int logits_ld, int logits_col0, int logits_multicast, void* k_cache, void* v_cache, const float* cos_t, const float* sin_t,
                                      const int* cache_len, const int* pad_left, void* scratch, unsigned int* gen, int M,
                                      int L, int H, int F, int V, int vocab_full, int nh, int nkv, int hd, int T,
                                      int max_pos, float eps, float scale, int num_sms, int tp, int rank,
@@ -1035,7 +1041,8 @@ extern "C" JL_API int jl_decode_mega(const void* wqkv_all, const void* wo_all, c
   p.eps = eps; p.scale_log2 = scale * 1.4426950408889634f;
   p.attn_norm = (const __nv_bfloat16*)attn_norm; p.ffn_norm = (const __nv_bfloat16*)ffn_norm;
   p.final_norm = (const __nv_bfloat16*)final_norm; p.embedding = (const __nv_bfloat16*)embedding;
-  p.ids = ids; p.logits = logits; p.kc = (__nv_bfloat16*)k_cache; p.vc = (__nv_bfloat16*)v_cache;
+  p.ids = ids; p.logits = logits; p.logits_ld = logits_ld > 0 ? logits_ld : V; p.logits_col0 = logits_col0;
+  p.logits_mc = logits_multicast; p.kc = (__nv_bfloat16*)k_cache; p.vc = (__nv_bfloat16*)v_cache;
   p.cos_t = cos_t; p.sin_t = sin_t; p.cache_len = cache_len; p.pad_left = pad_left; p.gen = gen;
   p.splits = mega_splits(M, nh, nkv, T, num_sms);
   const MegaLayout lay = mega_layout(M, H, F, nh, nkv, num_sms);

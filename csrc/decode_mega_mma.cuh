@@ -167,7 +167,9 @@ __device__ __noinline__ void mg_stage_packets(uint4* xin, const uint2* pk, uint3
 struct MegaOut {
   uint2* pk;                // MG_PLAIN / MG_SWIGLU: packet buffer [M][N/2] ({bf16 pair, tag})
   uint2* r_pk;              // MG_RESIDUAL: packets of the new residual stream [M][H/2]
-  float* logits;            // MG_LOGITS: optional fp32 [M][N] (may be null: candidates only)
+  float* logits;            // MG_LOGITS: optional fp32 logits (may be null: candidates only): row pitch logits_ld, this
+  int logits_ld, logits_col0;   // rank's shard starts at column logits_col0; logits_mc: the pointer is an NVLS multicast
+  bool logits_mc;               // address (the store lands in every rank's [M, V] buffer)
   float (*res)[64];         // MG_RESIDUAL: this CTA's rows of the residual stream (shared memory, bf16-exact values)
   float* best_v;            // MG_LOGITS: running (max, argmax) of this thread's rows
   int* best_i;
@@ -271,7 +273,10 @@ __device__ __forceinline__ void mg_gemv_mma(MegaCtx& c, int N, int K, const Mega
           if (valid) carry[m][(grp - g0) * MG_GROUP + n] = v;       // read back by this same thread in the second pass
         } else if constexpr (MODE == MG_LOGITS) {
           if (valid) {
-            if (o.logits != nullptr) o.logits[(size_t)m * N + row] = v;
+            if (o.logits != nullptr) {
+              float* dst = o.logits + (size_t)m * o.logits_ld + o.logits_col0 + row;
+              if (o.logits_mc) mm::st_f32(dst, v); else *dst = v;
+            }
             if (v > *o.best_v) { *o.best_v = v; *o.best_i = row + o.idx_offset; }      // rows ascend: ties keep the lower index
           }
         } else if constexpr (MODE == MG_RESIDUAL) {

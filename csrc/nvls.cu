@@ -37,6 +37,41 @@ __global__ void nvls_selftest_kernel(void* mc, const void* src, void* out, int n
   }
 }
 
+
+// Every rank's [rows, cols] fp32 block → columns [col0, col0 + cols) of every rank's [rows, dst_ld] buffer: one
+// multimem.st per 16 bytes (the switch replicates it), then the last CTA publishes this rank's "done" flag to all
+// ranks.  Used to assemble the vocabulary-sharded prefill logits on every rank for the exact sampler.
+struct BcastParams {
+  const float* src; float* dst_mc;
+  int rows, cols, src_ld, dst_ld, col0, tp, rank, flag_off, epoch;
+  const int* seq_ptr;        // non-null: the flag value is *seq_ptr + epoch (device epoch counter, CUDA-graph safe)
+  int* flags[8];
+  int* ticket;
+};
+__global__ void __launch_bounds__(256) nvls_bcast_f32_kernel(const BcastParams p) {
+  pdl_wait();
+  pdl_launch_dependents();
+  __shared__ int s_last;
+  const int c4 = p.cols / 4, total = p.rows * c4;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int r = i / c4, c = (i - r * c4) * 4;
+    const float4 v = *reinterpret_cast<const float4*>(p.src + (size_t)r * p.src_ld + c);
+    mm::st_v4f32(p.dst_mc + (size_t)r * p.dst_ld + p.col0 + c, v);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int prev = atomicAdd(p.ticket, 1);
+    s_last = prev == (int)gridDim.x - 1;
+    if (s_last) *p.ticket = 0;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x < p.tp) {
+    __threadfence_system();
+    st_release_sys(p.flags[threadIdx.x] + p.flag_off + p.rank, p.epoch + (p.seq_ptr ? *p.seq_ptr : 0));
+  }
+}
+
 }  // namespace jl
 
 using namespace jl;
@@ -48,5 +83,22 @@ extern "C" JL_API int jl_nvls_selftest(void* mc, const void* src, void* out, int
   count_launch();
   nvls_selftest_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(mc, src, out, n, op, tag);
   JL_CUDA(cudaGetLastError());
+  return JL_OK;
+}
+
+extern "C" JL_API int jl_nvls_bcast_f32(const float* src, float* dst_mc, int rows, int cols, int src_ld, int dst_ld, int col0,
+                                        int tp, int rank, void* const* peer_flags, int flag_off, int epoch, const int* seq_ptr,
+                                        int* ticket, void* stream) {
+  JL_CHECK_ARG(src && dst_mc && ticket && cols % 4 == 0 && col0 % 4 == 0 && src_ld % 4 == 0 && dst_ld % 4 == 0,
+               "jl_nvls_bcast_f32: columns, offsets and pitches must be multiples of 4");
+  JL_CHECK_ARG(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "jl_nvls_bcast_f32: bad tp/rank");
+  BcastParams p{};
+  p.src = src; p.dst_mc = dst_mc; p.rows = rows; p.cols = cols; p.src_ld = src_ld; p.dst_ld = dst_ld; p.col0 = col0;
+  p.tp = tp; p.rank = rank; p.flag_off = flag_off; p.epoch = epoch; p.seq_ptr = seq_ptr; p.ticket = ticket;
+  for (int i = 0; i < tp; ++i) p.flags[i] = (int*)peer_flags[i];
+  int blocks = (rows * (cols / 4) + 255) / 256;
+  if (blocks > 148) blocks = 148;
+  if (blocks < 1) blocks = 1;
+  JL_CUDA(launch_pdl(nvls_bcast_f32_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, p));
   return JL_OK;
 }

@@ -17,6 +17,9 @@ __device__ __forceinline__ void st_b64(void* mc, uint32_t lo, uint32_t hi) {
   const uint64_t v = ((uint64_t)hi << 32) | lo;
   asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(mc), "l"(v) : "memory");
 }
+__device__ __forceinline__ void st_f32(void* mc, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
 __device__ __forceinline__ void st_v4f32(void* mc, float4 v) {
   asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
                "f"(v.w)

@@ -136,7 +136,9 @@ int jl_decode_advance(const int* tok, int* next_ids, int* finished, int* sequenc
  * counter of the steps this engine has run (zero at start; the kernel advances it; it is the tag base, so every
  * scratch / peer buffer ever used with it must only be used with it).  `logits` fp32 [M, V] (V = this rank's
  * vocab shard, vocab_full the whole vocabulary) may be NULL: then only the per-CTA arg-max candidates are
- * produced (read by jl_mega_select).  Needs a cooperative launch of one CTA per SM (num_sms CTAs co-resident).
+ * produced (read by jl_mega_select).  Row pitch `logits_ld` (0 = V), this rank's columns start at `logits_col0`;
+ * with `logits_multicast` the pointer is the NVLS multicast address of a symmetric [M, vocab_full] buffer and every
+ * rank receives every shard (input of jl_sample_full under tensor parallelism).  Needs a cooperative launch of one CTA per SM (num_sms CTAs co-resident).
  * With tp > 1 the wo / w2 outputs are all-reduced inside the kernel (partition.py:67,70 is what GSPMD
  * all-reduced there): fp32 partial packets go to every rank with one multimem.st on `mc_partials` (the NVLS
  * multicast address of the symmetric buffer whose per-rank mappings are `peer_partials`; NULL = one unicast
@@ -148,7 +150,8 @@ int jl_decode_mega_stages(int M, int H, int F, int nh, int nkv, int hd); /* weig
 void jl_decode_mega_set_trace(void* buf /* device u64 [num_sms][L][32] %globaltimer stamps, NULL = off */);
 int jl_decode_mega(const void* wqkv_all, const void* wo_all, const void* w13_all, const void* w2_all,
                    const void* lm_head, const void* attn_norm, const void* ffn_norm, const void* final_norm,
-                   const void* embedding, const int* ids, float* logits, void* k_cache, void* v_cache,
+                   const void* embedding, const int* ids, float* logits, int logits_ld, int logits_col0,
+                   int logits_multicast, void* k_cache, void* v_cache,
                    const float* cos_t, const float* sin_t, const int* cache_len, const int* pad_left, void* scratch,
                    unsigned int* gen, int M, int L, int H, int F, int V, int vocab_full, int nh, int nkv, int hd,
                    int T, int max_pos, float eps, float scale, int num_sms, int tp, int rank,
@@ -186,8 +189,9 @@ int jl_allgather_small(const void* src, void* out, int n_bytes, int slot_bytes, 
                        void* const* peer_inbox, void* const* peer_flags, size_t parity_stride_bytes,
                        int flag_offset, const int* seq_ptr, int call_index, void* stream);
 int jl_comm_bump(int* seq_ptr, int n, void* stream);
-/* one warp waits (on the stream) until flags[0..tp) >= epoch: later kernels may read what the peers published first */
-int jl_wait_flags(const int* flags, int epoch, int tp, int rank, void* stream);
+/* one warp waits (on the stream) until flags[0..tp) >= epoch (+ *seq_ptr if given: device epoch counter, graph safe):
+ * later kernels may read what the peers published first */
+int jl_wait_flags(const int* flags, int epoch, const int* seq_ptr, int tp, int rank, void* stream);
 int jl_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream);
 
 /* Sequence-parallel prefill (M % (128*tp) == 0).  The residual stream is sharded by rows; per layer:
@@ -209,6 +213,24 @@ int jl_gemm_rs(const void* x, const void* w, void* const* peer_rs_buf, int M, in
 int jl_rs_reduce(void* x, const void* partials, const void* norm_w, void* const* xn_peers, int xn_row0, int mloc,
                  int H, int n_src, int tp, int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off,
                  int gemm_epoch, int ready_epoch, int* ticket, float eps, void* stream);
+
+/* HF Flax warpers + categorical sampling + `_sample` bookkeeping (generation.py:28-41) over the WHOLE vocabulary, exact
+ * for any top_k / top_p (no candidate budget), deterministic ties (lower index), identical on every rank: see
+ * csrc/sample_full.cu.  logits fp32 [B, ld] with V valid columns; temperature 0 = arg-max; top_k <= 0 or >= V and
+ * top_p >= 1 disable the filters.  `cand`/`gen` (may be NULL) = candidate packets / step counter of jl_decode_mega: wait
+ * for every rank's logits shard first.  `next_ids` == NULL: selection only (tok[B]).  `ticket` = one zero int. */
+int jl_sample_full(const float* logits, int B, int V, int ld, float temperature, int top_k, float top_p,
+                   unsigned long long seed, const int* step, int* tok, const void* cand, const unsigned int* gen, int tp,
+                   int rank, int num_sms, int L, int* ticket, int* next_ids, int* finished, int* sequences, int max_len,
+                   int eos, int pad, int* cur_len, int* cache_len, int* step_rw, int* n_unfinished, void* stream);
+
+/* All-gather of a column-sharded fp32 block over NVLS: this rank's [rows, cols] goes to columns [col0, col0+cols) of
+ * every rank's [rows, dst_ld] buffer (`dst_mc` = its multicast address) with multimem.st; flags[r][flag_off + rank] =
+ * epoch (+ *seq_ptr if given) on every rank afterwards (pair with jl_wait_flags).  The reference gathers the vocab-sharded logits with the
+ * all-gather GSPMD derives from partition.py:77. */
+int jl_nvls_bcast_f32(const float* src, float* dst_mc, int rows, int cols, int src_ld, int dst_ld, int col0, int tp,
+                      int rank, void* const* peer_flags, int flag_off, int epoch, const int* seq_ptr, int* ticket,
+                      void* stream);
 
 /* NVLS form of the owner-side step of the sequence-parallel prefill, and the all-reduce of a row-parallel GEMM for any
  * token count (partition.py:67,70 is what GSPMD all-reduced there).  The GEMM before it stored this rank's bf16 partial

@@ -160,9 +160,15 @@ class B200Engine:
             cand_off = C.c_size_t(0)
             nbytes = int(L.jl_decode_mega_peer_bytes(8, self.config.hidden_size, self.tp, K.num_sms(self.device),
                                                      C.byref(cand_off)))
+            logits_off = (nbytes + 1023) // 1024 * 1024          # [8][V] fp32: every rank's shard of the logits, gathered
+            nbytes = logits_off + 8 * self.config.vocab_size * 4
             heap = SymmetricHeap(self.tp, self.rank, self.device, nbytes, group=getattr(self.comm, "group", None))
             self._mega_peer = (heap, heap.peer_table(0), heap.mc(0), heap.peer_table(cand_off.value),
                                heap.mc(cand_off.value), heap.local_ptr + cand_off.value)
+            self._logits_full = heap.view(logits_off, (8, self.config.vocab_size), torch.float32)
+            self._logits_full_mc = heap.mc(logits_off)
+            self._bcast_ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._bcast_flag_off = self.comm.flag_block(("logits_bcast",), 8)
         _, p_tab, p_mc, c_tab, c_mc, _ = self._mega_peer
         return (self.tp, self.rank, p_tab, p_mc or None, c_tab, c_mc or None)
 
@@ -486,35 +492,69 @@ class B200Engine:
         self._decode_states[key] = st
         return st
 
-    def _select_and_advance(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int) -> None:
-        """logits → token (greedy or temperature/top-k/top-p) → sequences / finished / counters, on device."""
+    def _sample_full(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int,
+                     logits: torch.Tensor, wait_mega: bool) -> None:
+        """Exact selection over the whole vocabulary + bookkeeping, one launch (csrc/sample_full.cu).  `logits` is a
+        [B, V] fp32 view (any row pitch).  wait_mega: the rows are being filled by the decode kernels of all ranks
+        (multicast stores) — the kernel waits for their candidate packets before it reads."""
         do_sample, temperature, top_k, top_p, seed = sampling
-        if self.tp > 1:
-            # vocab-parallel head: each rank extracts its local top-k (value, global index) pairs, the pairs
-            # are exchanged through peer memory, and every rank runs the identical final selection — the
-            # [B, V] logits are never gathered (SURVEY §2.6 O17)
-            B = st.B
-            k = 2 if not do_sample else (MAX_TOPK if not top_k or top_k > MAX_TOPK else max(2, int(top_k)))
-            n = B * k
-            vals = st.cand_local[:n].view(torch.float32).view(B, k)
-            idx = st.cand_local[n:2 * n].view(B, k)
-            K.topk_candidates(st.logits, k, idx_offset=self.rank * self.v_local, out=(vals, idx))
-            gathered = st.cand_all[:self.tp * 2 * n]
-            self.comm.allgather_small(st.cand_local[:2 * n], gathered)
-            K.sample_candidates(gathered[:n].view(torch.float32).view(B, k), gathered[n:2 * n].view(B, k),
-                                n_lists=self.tp, list_stride=2 * n, top_k=(top_k if do_sample else 1) or k,
-                                top_p=top_p, temperature=temperature if do_sample else 0.0, seed=seed,
-                                step=st.step, out=st.tok)
-        elif not do_sample:
-            K.argmax(st.logits, out=st.tok)
-        else:
-            k = MAX_TOPK if not top_k or top_k > MAX_TOPK else int(top_k)
-            vals, idx = st.cand_val[:, :k], st.cand_idx[:, :k]
-            if k != MAX_TOPK:
-                vals, idx = st.cand_val.view(-1)[:st.B * k].view(st.B, k), st.cand_idx.view(-1)[:st.B * k].view(st.B, k)
-            K.topk_candidates(st.logits, k, out=(vals, idx))
-            K.sample_candidates(vals, idx, top_k=k, top_p=top_p, temperature=temperature, seed=seed,
-                                step=st.step, out=st.tok)
+        if getattr(st, "ticket", None) is None:
+            st.ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
+        cand = self._mega_peer[5] if (wait_mega and self.tp > 1) else None
+        _lib.check(_lib.lib().jl_sample_full(
+            logits.data_ptr(), st.B, self.config.vocab_size, logits.stride(0),
+            float(temperature) if do_sample else 0.0, int(top_k or 0), float(top_p), int(seed), st.step.data_ptr(),
+            st.tok.data_ptr(), cand, self._mega_gen.data_ptr(), self.tp, self.rank, K.num_sms(self.device),
+            len(self.layers), st.ticket.data_ptr(), st.ids.data_ptr(), st.finished.data_ptr(), st.sequences.data_ptr(),
+            st.max_len, int(eos), int(pad), st.cur_len.data_ptr(), cache.len_dev.data_ptr(), st.step.data_ptr(),
+            st.n_unfinished.data_ptr(), K._stream()), "jl_sample_full")
+
+    def _gather_logits(self, st: DecodeState) -> torch.Tensor:
+        """tp > 1: this rank's [B, V/tp] logits shard → every rank's [B, V] buffer over NVLS (multimem.st), then a
+        stream-side wait for all ranks' shards.  Returns the local [B, V] view."""
+        self._mega_tp_args()                       # the symmetric buffers exist
+        L = _lib.lib()
+        from ..parallel.comm import _L as comm_lib
+        comm_lib()
+        cm = self.comm
+        # flag value = device epoch counter + position of this collective in the step: the same captured launch stays
+        # correct on every CUDA-graph replay (the counter is advanced at the end of the step, `end_sequence`)
+        epoch_rel = cm.call_index + 1
+        cm.call_index += 1
+        _lib.check(L.jl_nvls_bcast_f32(st.logits.data_ptr(), self._logits_full_mc, st.B, self.v_local, self.v_local,
+                                       self.config.vocab_size, self.rank * self.v_local, self.tp, self.rank, cm.flag_ptrs,
+                                       self._bcast_flag_off, epoch_rel, cm.seq.data_ptr(), self._bcast_ticket.data_ptr(),
+                                       K._stream()), "jl_nvls_bcast_f32")
+        _lib.check(L.jl_wait_flags(cm._own_flags + 4 * self._bcast_flag_off, epoch_rel, cm.seq.data_ptr(), self.tp,
+                                   self.rank, K._stream()), "jl_wait_flags")
+        return self._logits_full[:st.B]
+
+    def _select_and_advance(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int) -> None:
+        """st.logits (this rank's vocabulary shard) → token (greedy or temperature/top-k/top-p) → sequences / finished /
+        counters, on device.  Batches up to 8 rows: exact full-vocabulary kernel (at tp > 1 after an NVLS gather of
+        the shards).  Larger batches at tp > 1: per-rank top-k candidates exchanged through peer memory (top_k <= 64)."""
+        do_sample, temperature, top_k, top_p, seed = sampling
+        if self.tp == 1:
+            return self._sample_full(st, cache, sampling, eos, pad, st.logits, wait_mega=False)
+        if st.B <= 8:
+            return self._sample_full(st, cache, sampling, eos, pad, self._gather_logits(st), wait_mega=False)
+        if do_sample and (not top_k or top_k > MAX_TOPK):
+            raise NotImplementedError(f"tensor-parallel sampling at batch > 8 exchanges at most {MAX_TOPK} candidates per "
+                                      f"rank: pass 1 <= top_k <= {MAX_TOPK} (got {top_k})")
+        # vocab-parallel head: each rank extracts its local top-k (value, global index) pairs, the pairs are exchanged
+        # through peer memory, and every rank runs the identical final selection (SURVEY §2.6 O17)
+        B = st.B
+        k = 2 if not do_sample else max(2, int(top_k))
+        n = B * k
+        vals = st.cand_local[:n].view(torch.float32).view(B, k)
+        idx = st.cand_local[n:2 * n].view(B, k)
+        K.topk_candidates(st.logits, k, idx_offset=self.rank * self.v_local, out=(vals, idx))
+        gathered = st.cand_all[:self.tp * 2 * n]
+        self.comm.allgather_small(st.cand_local[:2 * n], gathered)
+        K.sample_candidates(gathered[:n].view(torch.float32).view(B, k), gathered[n:2 * n].view(B, k),
+                            n_lists=self.tp, list_stride=2 * n, top_k=(top_k if do_sample else 1) or k,
+                            top_p=top_p, temperature=temperature if do_sample else 0.0, seed=seed,
+                            step=st.step, out=st.tok)
         _lib.check(_lib.lib().jl_decode_advance(
             st.tok.data_ptr(), st.ids.data_ptr(), st.finished.data_ptr(), st.sequences.data_ptr(), st.B,
             st.max_len, int(eos), int(pad), st.cur_len.data_ptr(), cache.len_dev.data_ptr(), st.step.data_ptr(),
@@ -535,18 +575,25 @@ class B200Engine:
                 st.mega_scratch = torch.zeros((nbytes + 3) // 4, dtype=torch.int32, device=self.device)
                 st.mega_cand = st.mega_scratch.data_ptr() + int(L.jl_decode_mega_cand_offset(*shape))
             do_sample = bool(sampling[0])
-            want_logits = do_sample or self.mega_write_logits
+            tp_args = self._mega_tp_args()
+            if do_sample and self.tp > 1:
+                # sampling under tensor parallelism: every rank's shard goes into every rank's [B, V] buffer (multimem.st)
+                logits_args = (self._logits_full_mc, c.vocab_size, self.rank * self.v_local, 1)
+            elif do_sample or self.mega_write_logits:
+                logits_args = (st.logits.data_ptr(), self.v_local, 0, 0)
+            else:
+                logits_args = (None, 0, 0, 0)
             _lib.check(L.jl_decode_mega(
                 self.wqkv_all.data_ptr(), self.wo_all.data_ptr(), self.w13_all.data_ptr(), self.w2_all.data_ptr(),
                 self.lm_head.data_ptr(), self.attn_norm_all.data_ptr(), self.ffn_norm_all.data_ptr(),
                 self.final_norm.data_ptr(), self.embedding.data_ptr(), st.ids.data_ptr(),
-                st.logits.data_ptr() if want_logits else None,
+                *logits_args,
                 cache.k.data_ptr(), cache.v.data_ptr(), self.cos.data_ptr(), self.sin.data_ptr(),
                 cache.len_dev.data_ptr(), cache.pad_left.data_ptr(), st.mega_scratch.data_ptr(),
                 self._mega_gen.data_ptr(), st.B,
                 len(self.layers), c.hidden_size, c.intermediate_size // self.tp, self.v_local, c.vocab_size,
                 self.nh, self.nkv, self.hd, cache.capacity, self.cos.shape[0], float(c.rms_norm_eps),
-                1.0 / (self.hd ** 0.5), sms, *self._mega_tp_args(), K._stream()), "jl_decode_mega")
+                1.0 / (self.hd ** 0.5), sms, *tp_args, K._stream()), "jl_decode_mega")
             if not do_sample:
                 # greedy: the kernel left one candidate per CTA (and rank); merge + bookkeeping in one launch
                 cand = st.mega_cand if self.tp == 1 else self._mega_peer[5]
@@ -558,6 +605,12 @@ class B200Engine:
                 if self.comm is not None:
                     self.comm.end_sequence()
                 return
+            # sampling: exact full-vocabulary kernel on the logits the decode kernel just wrote (second and last launch)
+            full = st.logits if self.tp == 1 else self._logits_full[:st.B]
+            self._sample_full(st, cache, sampling, eos, pad, full, wait_mega=True)
+            if self.comm is not None:
+                self.comm.end_sequence()
+            return
         else:
             K.embed(st.ids, self.embedding, out=st.x)
             x = self._layers(st.x, st.B, 1, cache, None, ws=st)

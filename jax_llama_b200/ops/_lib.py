@@ -37,7 +37,10 @@ _SIGNATURES = {
     "jl_decode_mega_scratch_bytes": (sz, [i32, i32, i32, i32, i32, i32]),
     "jl_decode_mega_cand_offset": (sz, [i32, i32, i32, i32, i32, i32]),
     "jl_decode_mega_peer_bytes": (sz, [i32, i32, i32, i32, vp]),
-    "jl_decode_mega": (i32, [vp] * 9 + [ip, fp, vp, vp, fp, fp, ip, ip, vp, vp] + [i32] * 11 +
+    "jl_nvls_bcast_f32": (i32, [fp, fp, i32, i32, i32, i32, i32, i32, i32, vp, i32, i32, ip, ip, vp]),
+    "jl_sample_full": (i32, [fp, i32, i32, i32, f32, i32, f32, u64, ip, ip, vp, vp, i32, i32, i32, i32, ip, ip, ip, ip,
+                             i32, i32, i32, ip, ip, ip, ip, vp]),
+    "jl_decode_mega": (i32, [vp] * 9 + [ip, fp, i32, i32, i32, vp, vp, fp, fp, ip, ip, vp, vp] + [i32] * 11 +
                        [f32, f32, i32, i32, i32, vp, vp, vp, vp, vp]),
     "jl_mega_select": (i32, [vp, vp] + [i32] * 5 + [ip] * 4 + [i32] * 3 + [ip] * 4 + [vp]),
     "jl_nvls_selftest": (i32, [vp, vp, vp, i32, i32, C.c_uint, vp]),

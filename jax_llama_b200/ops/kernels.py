@@ -363,3 +363,23 @@ def sample_candidates(vals: torch.Tensor, idx: torch.Tensor, *, n_lists: int = 1
                                     float(top_p), float(temperature), int(seed), _p(step), out.data_ptr(),
                                     _stream()), "jl_sample")
     return out
+
+
+# --------------------------------------------------------------------------- exact full-vocabulary selection
+def sample_full(logits: torch.Tensor, *, temperature: float, top_k: int = 0, top_p: float = 1.0, seed: int = 0,
+                step: Optional[torch.Tensor] = None, rows: Optional[int] = None) -> torch.Tensor:
+    """Tokens [B] from fp32 logits [B, V] (or [V] read by `rows` independent draws): temperature → top-k → top-p →
+    categorical over the whole vocabulary, exact and deterministic (csrc/sample_full.cu).  temperature 0 = arg-max."""
+    if not logits.is_cuda or logits.dtype != torch.float32:
+        raise ValueError("sample_full needs CUDA fp32 logits")
+    if logits.dim() == 1:
+        B, V, ld = int(rows or 1), logits.shape[0], 0
+    else:
+        B, V, ld = logits.shape[0], logits.shape[1], logits.stride(0)
+    tok = torch.empty(B, dtype=torch.int32, device=logits.device)
+    ticket = torch.zeros(1, dtype=torch.int32, device=logits.device)
+    _lib.check(_lib.lib().jl_sample_full(
+        logits.data_ptr(), B, V, ld, float(temperature), int(top_k or 0), float(top_p), int(seed), _p(step), tok.data_ptr(),
+        None, None, 1, 0, 0, 0, ticket.data_ptr(), None, None, None, 0, 0, 0, None, None, None, None, _stream()),
+        "jl_sample_full")
+    return tok

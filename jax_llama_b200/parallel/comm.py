@@ -39,7 +39,7 @@ _EXTRA_SIGNATURES = {
     "jl_allgather_small": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "jl_comm_bump": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
-    "jl_wait_flags": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "jl_wait_flags": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "jl_memcpy_d2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "jl_ag_gemm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                              C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
@@ -401,7 +401,7 @@ class NvlsPrefill:
         """Rows (global token indices) of the current gathered, normalised activations.  Every rank holds all rows
         (their owners stored them into every copy); a one-warp kernel first waits for the owners' "ready" flags."""
         cm = self.comm
-        _lib.check(_L().jl_wait_flags(cm._own_flags + 4 * self.ready_off, self.ep["ready"], cm.tp, cm.rank, K._stream()),
+        _lib.check(_L().jl_wait_flags(cm._own_flags + 4 * self.ready_off, self.ep["ready"], None, cm.tp, cm.rank, K._stream()),
                    "jl_wait_flags")
         a = self.heap.view(self.a_off[self.parity], (self.M, self.H), torch.bfloat16)
         return a[rows]

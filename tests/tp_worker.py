@@ -86,6 +86,15 @@ def main():
     ga = [torch.empty_like(a) for _ in range(world)]
     dist.all_gather(ga, a)
     assert all(torch.equal(ga[0], t) for t in ga)
+    # pure nucleus sampling (top-k disabled): exact over the whole vocabulary, still identical on every rank
+    c1 = eng.generate(ids.to(dev), mask.to(dev), max_length=32, do_sample=True, temperature=1.0, top_k=None,
+                      top_p=0.95, seed=11, eos_token_id=-7)
+    c2 = eng.generate(ids.to(dev), mask.to(dev), max_length=32, do_sample=True, temperature=1.0, top_k=None,
+                      top_p=0.95, seed=11, eos_token_id=-7)
+    assert torch.equal(c1, c2) and not torch.equal(c1, a)
+    gc = [torch.empty_like(c1) for _ in range(world)]
+    dist.all_gather(gc, c1)
+    assert all(torch.equal(gc[0], t) for t in gc), "ranks sampled different tokens with top_k=None"
     # ---- 3. sequence-parallel prefill (all-gather→GEMM, GEMM→reduce-scatter fused over peer memory)
     S = 64 * world if world > 2 else 128
     ids_sp = torch.randint(3, cfg.vocab_size, (2, S), generator=torch.Generator().manual_seed(9))
