@@ -32,17 +32,12 @@ BASELINE_PUBLISHED = None      # the reference publishes no perform
 
 
 def reference_arm(args) -> None:
-    """The reference (JAX/Flax) cannot be imported on this image: jax, flax and fire are not installed and
-    transformers 5.x ships no Flax generation mixin ("Reference arm")."""
-    why = "jax/flax not installed in this image (no index access); transformers 5.5 has no Flax classes"
-    try:
-        sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline", "_ref"))
-        import jax_llama  # noqa: F401
-        why = "reference imported unexpectedly; no runner implemented for it"
-    except Exception as e:  # noqa: BLE001
-        why = f"reference import fails: {type(e).__name__}: {str(e)[:120]}"
-    if int(os.environ.get("RANK", "0")) == 0:
-        print(json.dumps({"impl": "reference", "unavailable": why}))
+    """`--impl reference`: the unmodified reference from baseline/_ref through its own API (baseline/reference_runner.py).
+    On this image the import fails (no jax / flax; transformers 5.x ships no Flax generation mixin — DESIGN.md,
+    "Reference arm"), and the line says so."""
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline"))
+    import reference_runner
+    reference_runner.main(args)
 
 
 class ClockSampler(threading.Thread):

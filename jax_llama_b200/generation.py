@@ -54,6 +54,14 @@ class LLaMA:
             pad_token_id=self.tokenizer.eos_id, eos_token_id=self.tokenizer.eos_id, seed=seed)
         return with_named_sharding_constraint(out.sequences, self.mesh, P("dp", None))
 
+    def last_generation_stats(self) -> Optional[Any]:
+        """`GenerationStats` of the most recent `generate` call on the B200 engine (prefill ms, ms per token, tokens/s,
+        fraction of the HBM roofline when a peak is set); None on the reference backend."""
+        dev = next(iter(_leaves(self.params))).device if isinstance(self.params, dict) else None
+        if dev is None or getattr(dev, "type", "cpu") != "cuda":
+            return None
+        return getattr(self.model._engine_for(self.params), "last_stats", None)
+
     def stream(self, tokens: torch.Tensor, attention_mask: torch.Tensor, max_gen_len: int,
                temperature: float = 0.8, top_p: float = 0.95, top_k: Optional[int] = 50, seed: int = 0) -> Any:
         """Token-at-a-time variant of `generate` for interactive serving (CUDA parameters only).

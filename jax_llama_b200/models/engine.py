@@ -395,13 +395,12 @@ class B200Engine:
 
     def _prefill_attn(self, q: torch.Tensor, kc: torch.Tensor, vc: torch.Tensor, start: int, S: int,
                       cache: DeviceKVCache) -> torch.Tensor:
-        if _lib.has("jl_flash_prefill") and self.hd == 128:
-            return K.prefill_attn(q, kc, vc, start, S, cache.pad_left, cache.len_dev)
-        if not self.warned_slow_prefill:
-            logger.warning("flash prefill kernel unavailable for head_dim=%d: using the dense PyTorch "
-                           "statement (correct, O(S^2) memory)", self.hd)
-            self.warned_slow_prefill = True
-        return K.prefill_attn_ref(q, kc, vc, start, S, cache.pad_left)
+        if self.hd != 128:
+            # the flash kernel is built for the head size of every LLaMA (128); a dense O(S^2) PyTorch statement on the
+            # GPU path would be a silent library fallback — use the reference backend (CPU tensors) for other head sizes
+            raise NotImplementedError(f"the B200 prefill kernel is built for head_dim 128, got {self.hd}: run this model "
+                                      "through the reference backend (parameters on the CPU)")
+        return K.prefill_attn(q, kc, vc, start, S, cache.pad_left, cache.len_dev)
 
     # ------------------------------------------------------------------ public forward
     @torch.no_grad()
@@ -661,26 +660,41 @@ class B200Engine:
         B, S = input_ids.shape
         if max_length > 2 * self.config.max_sequence_length:
             raise ValueError(f"max_length {max_length} exceeds the rotary table (2 x max_sequence_length)")
+        from ..utils.stats import CudaTimer, GenerationStats, nvtx_range
         st = self._decode_state(B, max_length)
-        cache = self.prepare(st, input_ids, attention_mask, pad_token_id)
+        stats = GenerationStats(batch=B, prompt_len=S, weight_bytes_per_step=self.weight_bytes_per_step())
+        with nvtx_range("prefill"), CudaTimer() as t_prefill:
+            cache = self.prepare(st, input_ids, attention_mask, pad_token_id)
         sampling = (bool(do_sample), float(temperature), int(top_k or 0), float(top_p), int(seed))
         # first new token comes from the prefill logits
         self._select_and_advance_after_prefill(st, cache, sampling, eos_token_id, pad_token_id)
         remaining = max_length - S - 1
         graph = self._graph_for(st, cache, sampling, eos_token_id, pad_token_id) if remaining > 0 else None
         done = 0
+        windows = []
         while done < remaining:
             n = min(check_every, remaining - done)
-            for _ in range(n):
-                if graph is not None:
-                    graph.replay()
-                else:
-                    self._decode_step(st, cache, sampling, eos_token_id, pad_token_id)
+            with nvtx_range("decode"), CudaTimer() as t_win:
+                for _ in range(n):
+                    if graph is not None:
+                        graph.replay()
+                    else:
+                        self._decode_step(st, cache, sampling, eos_token_id, pad_token_id)
+            windows.append((t_win, n))
             done += n
             if done < remaining and int(st.n_unfinished.item()) == 0:      # one sync per `check_every` tokens
                 break
         cache.index = int(cache.len_dev.item())
+        # what this call cost (device time, CUDA events): prefill, ms per token of every window of `check_every` steps
+        stats.prefill_ms = t_prefill.elapsed_ms()
+        stats.new_tokens = 1 + done
+        stats.decode_ms_per_token = [t.elapsed_ms() / n for t, n in windows]
+        self.last_stats = stats
         return st.sequences.to(torch.long)
+
+    def weight_bytes_per_step(self) -> int:
+        """Bytes of weights one decode step streams on this rank (the HBM-roofline numerator)."""
+        return sum(t.numel() * 2 for t in (self.wqkv_all, self.wo_all, self.w13_all, self.w2_all, self.lm_head))
 
     def prepare(self, st: DecodeState, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor],
                 pad: int) -> DeviceKVCache:

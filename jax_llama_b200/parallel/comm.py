@@ -176,8 +176,9 @@ class PeerComm:
             out = torch.empty((m, n), dtype=x.dtype, device=x.device)
         L = _L()
         need = self.tp * m * n * 4
-        if need > self.parity_bytes:
-            raise ValueError(f"inbox too small for a {m}x{n} all-reduce ({need} > {self.parity_bytes} bytes)")
+        usable = self.parity_bytes - self.gather_region      # the top of each parity half belongs to allgather_small
+        if need > usable:
+            raise ValueError(f"inbox too small for a {m}x{n} all-reduce ({need} > {usable} bytes)")
         off = self.flag_block(("gemv_ar", n), int(L.jl_gemv_allreduce_flags(n)))
         _lib.check(L.jl_gemv_allreduce(x.data_ptr(), w.data_ptr(), residual.data_ptr(), out.data_ptr(), m, n, k,
                                        self.tp, self.rank, self.inbox_ptrs, self.flag_ptrs, self.parity_bytes // 4,

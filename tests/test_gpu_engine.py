@@ -13,9 +13,9 @@ CFGS = {
     "gqa128": LLaMAConfig(vocab_size=1000, hidden_size=512, intermediate_size=1024, num_hidden_layers=2,
                           num_attention_heads=4, num_key_value_heads=2, max_sequence_length=256,
                           initializer_range=0.05),
-    "mha64": LLaMAConfig(vocab_size=512, hidden_size=256, intermediate_size=768, num_hidden_layers=2,
-                         num_attention_heads=4, num_key_value_heads=4, max_sequence_length=256,
-                         initializer_range=0.05),
+    "mha128": LLaMAConfig(vocab_size=512, hidden_size=512, intermediate_size=768, num_hidden_layers=2,
+                          num_attention_heads=4, num_key_value_heads=4, max_sequence_length=256,
+                          initializer_range=0.05),
 }
 
 
@@ -147,6 +147,25 @@ def test_engine_cache_follows_the_parameter_tree():
     e2 = model._engine_for(gp)
     assert e2 is not e1
     assert torch.equal(e2.final_norm.float(), gp["transformer"]["ln_f"]["kernel"].float())
+
+
+def test_other_head_sizes_are_refused_not_run_through_pytorch():
+    """head_dim != 128 has no prefill kernel: the engine says so instead of running a dense PyTorch statement on the GPU."""
+    cfg = LLaMAConfig(vocab_size=512, hidden_size=256, intermediate_size=768, num_hidden_layers=1,
+                      num_attention_heads=4, num_key_value_heads=4, max_sequence_length=64)
+    tree = tree_to(ref.init_params(cfg, seed=1), dtype=torch.bfloat16, device="cuda")
+    eng = B200Engine.from_tree(cfg, tree)
+    with pytest.raises(NotImplementedError, match="head_dim 128"):
+        eng.forward(torch.randint(0, 512, (1, 5), device="cuda"))
+
+
+def test_generate_reports_what_it_cost():
+    cfg, tree, _ = make("gqa128")
+    eng = B200Engine.from_tree(cfg, tree_to(tree, device="cuda"))
+    ids = torch.randint(3, cfg.vocab_size, (2, 12), generator=torch.Generator().manual_seed(5)).cuda()
+    eng.generate(ids, None, max_length=40, eos_token_id=-7)
+    s = eng.last_stats.summary()
+    assert s["new_tokens"] == 28 and s["prefill_ms"] > 0 and s["p50_ms_per_token"] > 0 and s["decode_tok_s"] > 0
 
 
 def test_public_generate_api_on_gpu():

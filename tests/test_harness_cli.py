@@ -86,3 +86,80 @@ def test_example_cli_end_to_end_on_cpu(tmp_path, spm_model):
         assert r.returncode == 0, r.stderr[-1500:]
         assert r.stdout.count("==================================") == 2
         assert "the capital of germany is" in r.stdout.lower()
+
+
+def test_reference_arm_runner_with_a_stubbed_reference(tmp_path, monkeypatch):
+    """The runner drives the reference's own API (mesh → FlaxLLaMAForCausalLM(_do_init=False) → partition spec →
+    LLaMA.generate, /root/reference/jax_example.py:10-31).  jax and flax are not installable here, so the API is stubbed:
+    the test pins the call sequence and the JSON contract, and that decode time is the difference of two generate calls."""
+    import textwrap
+    import types
+
+    pkg = tmp_path / "stubs"
+    (pkg / "jax" / "experimental").mkdir(parents=True)
+    (pkg / "jax_llama").mkdir()
+    (pkg / "jax" / "__init__.py").write_text(textwrap.dedent("""
+        import types
+        def devices(): return ["gpu0", "gpu1"]
+        class _R:
+            @staticmethod
+            def PRNGKey(s): return s
+        random = _R()
+        class tree_util:
+            @staticmethod
+            def tree_map(f, *trees):
+                t0 = trees[0]
+                if isinstance(t0, dict):
+                    return {k: tree_util.tree_map(f, *[t[k] for t in trees]) for k in t0}
+                return f(*trees)
+        def device_put(p, s): return p
+        def block_until_ready(x): return x
+    """))
+    (pkg / "jax" / "numpy.py").write_text("import numpy as _np\nint32 = _np.int32\nbfloat16 = _np.float32\nasarray = _np.asarray\nones = _np.ones\n")
+    (pkg / "jax" / "experimental" / "__init__.py").write_text("")
+    (pkg / "jax" / "experimental" / "mesh_utils.py").write_text("def create_device_mesh(shape, devices=None): return [list(devices)]\n")
+    (pkg / "jax" / "sharding.py").write_text(textwrap.dedent("""
+        class Mesh:
+            def __init__(self, devs, axis_names): self.devs, self.axis_names = devs, axis_names
+        class NamedSharding:
+            def __init__(self, mesh, spec): self.mesh, self.spec = mesh, spec
+    """))
+    (pkg / "jax_llama" / "__init__.py").write_text(textwrap.dedent("""
+        import time, numpy as np
+        CALLS = []
+        class LLaMAConfig:
+            def __init__(self, **kw): self.__dict__.update(kw)
+        class FlaxLLaMAForCausalLM:
+            def __init__(self, config, _do_init=True, dtype=None): CALLS.append(("model", _do_init)); self.config = config
+            def init_weights(self, key, shape): CALLS.append(("init", shape)); return {"lm_head": {"kernel": np.zeros((2, 2))}}
+        def get_llama_param_partition_spec(params, fsdp=False):
+            CALLS.append(("spec", fsdp)); return {"lm_head": {"kernel": ("mp",)}}
+        class LLaMA:
+            def __init__(self, params, model, tokenizer, mesh=None): self.mesh = mesh; CALLS.append(("llama", len(mesh.devs[0])))
+            def generate(self, tokens, mask, max_gen_len, temperature=0.8, top_p=0.95):
+                CALLS.append(("generate", max_gen_len, temperature)); time.sleep(0.002 * max_gen_len)
+                return np.zeros((tokens.shape[0], tokens.shape[1] + max_gen_len), dtype=np.int32)
+    """))
+    for name in [m for m in list(sys.modules) if m == "jax" or m.startswith("jax.") or m == "jax_llama"]:
+        monkeypatch.delitem(sys.modules, name)
+    monkeypatch.syspath_prepend(str(pkg))
+    monkeypatch.syspath_prepend(os.path.join(ROOT, "baseline"))
+    monkeypatch.setenv("RANK", "0")
+    import importlib
+
+    import reference_runner
+    importlib.reload(reference_runner)
+    # the stub must win over a real install directory of the reference
+    monkeypatch.setattr(reference_runner, "HERE", str(tmp_path))
+    args = types.SimpleNamespace(gpus=2, steps=20, warmup=3, model="llama3-8b", batch=1, prompt_len=64)
+    line = reference_runner.run(args)
+    import jax_llama
+    assert line["impl"] == "reference" and "unavailable" not in line, line
+    assert line["metric"] == "decode_tokens_per_sec" and line["n_gpus"] == 2 and line["config"]["model"] == "llama3-8b"
+    assert 250 < line["value"] < 1000            # 20 tokens in ~40 ms of stubbed decode
+    kinds = [c[0] for c in jax_llama.CALLS]
+    assert kinds[:4] == ["model", "init", "spec", "llama"] and kinds.count("generate") == 6
+    assert ("model", False) in jax_llama.CALLS and ("spec", False) in jax_llama.CALLS
+    assert all(c[2] == 0.0 for c in jax_llama.CALLS if c[0] == "generate")
+    for name in [m for m in list(sys.modules) if m == "jax" or m.startswith("jax.") or m == "jax_llama"]:
+        sys.modules.pop(name, None)
