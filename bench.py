@@ -361,6 +361,16 @@ def main() -> None:
         except OSError:
             pass
         hbm = peaks.get("hbm_gbs", 6650.0)
+        # prefill roofline: the slower of (FLOPs of this rank at the measured sustained cuBLAS bf16 rate) and (bytes
+        # this rank must move over NVLink at the measured 770 GB/s per direction), assuming perfect overlap
+        M_tok = B * P
+        layer_w = sum(t.numel() for l in eng.layers[:1] for t in (l.wqkv, l.wo, l.w13, l.w2)) * len(eng.layers)
+        flops = 2.0 * M_tok * layer_w + 2.0 * 2.0 * B * (P * (P + 1) / 2) * eng.nh * eng.hd * len(eng.layers)
+        t_compute = flops / (peaks.get("bf16_tflops_sustained", 1400.0) * 1e12) * 1e3
+        nvl_bytes = 0.0 if world == 1 else 4.0 * len(eng.layers) * (world - 1) / world * M_tok * cfg.hidden_size * 2
+        t_nvlink = nvl_bytes / 770e9 * 1e3
+        prefill_roofline = {"compute_ms_at_sustained_peak": round(t_compute, 3), "nvlink_ms_at_770GBs": round(t_nvlink, 3),
+                            "frac_of_measured": round(max(t_compute, t_nvlink) / prefill_best, 4)}
         line = {
             "metric": "decode_tokens_per_sec", "value": round(value, 2), "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
@@ -374,6 +384,7 @@ def main() -> None:
             "hbm_roofline_frac_of_measured": round((weight_bytes / (ms_per_step / 1e3)) / (hbm * 1e9), 4),
             "prefill": {"tokens_per_sec": round(B * P / (prefill_best / 1e3), 1), "ms": round(prefill_best, 3),
                         "prompt_len": P, "includes": "embedding..lm_head(last token) of the prompt",
+                        "roofline": prefill_roofline,
                         "path": PATH_NAMES[default_path],
                         "other_path": prefill_alt},
             "e2e": {"value": round(B * args.steps / (e2e_ms / 1e3), 2), "unit": "tokens/s",

@@ -179,6 +179,19 @@ __global__ void wait_flags_kernel(const int* flags, int epoch, const int* seq_pt
   if (threadIdx.x < tp) wait_flag(flags + threadIdx.x, epoch + (seq_ptr ? *seq_ptr : 0), rank, threadIdx.x, 6);
 }
 
+// publish this rank's flag to every rank, then wait for everybody's: one warp.  Kernels that move data never spin on
+// a peer themselves (a kernel that fills the SMs while it waits could keep the very kernel it waits for — on another
+// stream of a peer — from being scheduled); the waiting is done by these one-warp kernels between them.
+__global__ void flag_exchange_kernel(PeerTable peers, int flag_off, int epoch, int tp, int rank) {
+  pdl_wait();
+  pdl_launch_dependents();
+  if (threadIdx.x < tp) {
+    __threadfence_system();
+    st_release_sys(peers.flags[threadIdx.x] + flag_off + rank, epoch);
+    wait_flag(peers.flags[rank] + flag_off + threadIdx.x, epoch, rank, threadIdx.x, 7);
+  }
+}
+
 __global__ void bump_kernel(int* seq, int n) {
   pdl_wait();
   pdl_launch_dependents();
@@ -272,6 +285,14 @@ extern "C" JL_API int jl_allgather_small(const void* src, void* out, int n_bytes
 extern "C" JL_API int jl_wait_flags(const int* flags, int epoch, const int* seq_ptr, int tp, int rank, void* stream) {
   JL_CHECK_ARG(flags && tp >= 1 && tp <= MAX_TP, "jl_wait_flags: bad arguments");
   JL_CUDA(launch_pdl(wait_flags_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, flags, epoch, seq_ptr, tp, rank));
+  return JL_OK;
+}
+
+extern "C" JL_API int jl_flag_exchange(void* const* peer_flags, int flag_off, int epoch, int tp, int rank, void* stream) {
+  JL_CHECK_ARG(peer_flags && tp >= 1 && tp <= MAX_TP && rank >= 0 && rank < tp, "jl_flag_exchange: bad arguments");
+  PeerTable t{};
+  for (int i = 0; i < tp; ++i) t.flags[i] = (int*)peer_flags[i];
+  JL_CUDA(launch_pdl(flag_exchange_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, t, flag_off, epoch, tp, rank));
   return JL_OK;
 }
 

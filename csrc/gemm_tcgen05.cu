@@ -15,6 +15,8 @@
 //
 // Replaces the cuBLAS GEMMs XLA emitted for /root/reference/jax_llama/model.py:119-150 (wq/wk/wv/wo),
 // :311-338 (w1/w2/w3) and :699-706 (lm_head).
+#include <stdlib.h>
+
 #include "jllama_b200.h"
 #include "tcgen05.cuh"
 
@@ -490,6 +492,13 @@ extern "C" JL_API int jl_gemm(const void* x, const void* w, const void* residual
   p.K = K;
   p.ldo = mode == EPI_SWIGLU ? N / 2 : N;
   auto s = (cudaStream_t)stream;
+  // token-major tiles of the prefill shapes go to the CTA-pair kernel (cta_group::2, gemm_2cta.cu); JLLAMA_GEMM_2CTA=0
+  // keeps everything on the single-CTA kernel below (A/B measurements)
+  static const bool pair_on = [] { const char* e = getenv("JLLAMA_GEMM_2CTA"); return !(e && e[0] == '0'); }();
+  if (pair_on && !out_f32 && M >= 256) {
+    const int rc = jl_gemm_2cta(x, w, residual, out, M, N, K, mode, num_sms, stream);
+    if (rc != JL_ERR_UNSUPPORTED) return rc;
+  }
   if (mode == EPI_PLAIN && out_f32) return dispatch_gemm<EPI_PLAIN, true>(x, w, p, M, N, K, num_sms, s);
   if (mode == EPI_PLAIN) return dispatch_gemm<EPI_PLAIN, false>(x, w, p, M, N, K, num_sms, s);
   if (mode == EPI_RESIDUAL) return dispatch_gemm<EPI_RESIDUAL, false>(x, w, p, M, N, K, num_sms, s);

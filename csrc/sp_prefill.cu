@@ -153,8 +153,9 @@ __global__ void __launch_bounds__(512) rs_reduce_mm_kernel(const RsMmParams p) {
   __shared__ float red[16];
   __shared__ int s_last;
   const size_t row = (size_t)blockIdx.x * p.H8;
-  if (p.has_partials) {
+  if (p.has_partials == 1) {
     // every rank's GEMM (the previous kernel on its stream) has written its partial product
+    // (has_partials == 2: the caller already ran jl_flag_exchange — this kernel then never waits for a peer)
     if (blockIdx.x == 0 && threadIdx.x < p.tp)
       st_release_sys(p.flags[threadIdx.x] + p.gemm_flag_off + p.rank, p.gemm_epoch);
     if (threadIdx.x < p.tp)

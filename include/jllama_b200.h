@@ -189,6 +189,9 @@ int jl_allgather_small(const void* src, void* out, int n_bytes, int slot_bytes, 
                        void* const* peer_inbox, void* const* peer_flags, size_t parity_stride_bytes,
                        int flag_offset, const int* seq_ptr, int call_index, void* stream);
 int jl_comm_bump(int* seq_ptr, int n, void* stream);
+/* one warp: flags[r][flag_off + rank] = epoch on every rank r, then wait until this rank's flags[flag_off + 0..tp) >= epoch
+ * ("every rank has finished the kernel before this one on its stream") */
+int jl_flag_exchange(void* const* peer_flags, int flag_off, int epoch, int tp, int rank, void* stream);
 /* one warp waits (on the stream) until flags[0..tp) >= epoch (+ *seq_ptr if given: device epoch counter, graph safe):
  * later kernels may read what the peers published first */
 int jl_wait_flags(const int* flags, int epoch, const int* seq_ptr, int tp, int rank, void* stream);
@@ -231,6 +234,12 @@ int jl_sample_full(const float* logits, int B, int V, int ld, float temperature,
 int jl_nvls_bcast_f32(const float* src, float* dst_mc, int rows, int cols, int src_ld, int dst_ld, int col0, int tp,
                       int rank, void* const* peer_flags, int flag_off, int epoch, const int* seq_ptr, int* ticket,
                       void* stream);
+
+/* The same linear layers on CTA PAIRS (2-CTA clusters, tcgen05.mma.cta_group::2, 256 x 256 tiles, TMA-store epilogue):
+ * token-major GEMMs with M >= 256, N % 256 == 0, K % 64 == 0 (every prefill GEMM of model.py:119-150, 311-338).
+ * Returns 3 (nothing launched) for other shapes; jl_gemm tries this first and falls back to its single-CTA kernel. */
+int jl_gemm_2cta(const void* x, const void* w, const void* residual, void* out, int M, int N, int K, int mode,
+                 int num_sms, void* stream);
 
 /* NVLS form of the owner-side step of the sequence-parallel prefill, and the all-reduce of a row-parallel GEMM for any
  * token count (partition.py:67,70 is what GSPMD all-reduced there).  The GEMM before it stored this rank's bf16 partial

@@ -341,35 +341,67 @@ class B200Engine:
         their partial product on the rank that computed it; the owner of a row pulls the sum over ranks with
         `multimem.ld_reduce` (reduced inside the NVSwitch), adds the residual, normalises and stores the row into
         every rank's copy of the gathered activations with `multimem.st` (`NvlsPrefill.rs_reduce`); column-parallel
-        GEMMs (wqkv, w1·w3) read that local copy, their TMA producer waiting per row owner for its flag
-        (`NvlsPrefill.ag_gemm`).  No NCCL call.  Returns this rank's vocabulary slice of the last-position logits,
-        [B, V/tp] fp32."""
+        GEMMs (wqkv, w1·w3) read that local copy after a one-warp wait for the owners' flags (`NvlsPrefill.ag_gemm`).
+        No NCCL call.
+
+        A single prompt whose length allows it is cut into two halves that run the same chain on two streams, the
+        second half one step behind the first: while one half's rows cross NVLink (reduce-scatter / all-gather
+        kernels, a few CTAs of work) the other half's GEMMs keep the tensor cores busy.  The second half's attention
+        reads the keys the first half appended to the same layer's cache (ordered with an event per layer).
+        Returns this rank's vocabulary slice of the last-position logits, [B, V/tp] fp32."""
         c = self.config
         eps = c.rms_norm_eps
         nh, nkv, hd = self.nh, self.nkv, self.hd
         M = B * S
-        sp = self.comm.nvls_state(M, c.hidden_size)
-        mloc, r = sp.mloc, self.rank
+        halves = 2 if (B == 1 and M % (2 * 128 * self.tp) == 0 and os.environ.get("JLLAMA_SP_PIPELINE", "1") != "0") else 1
+        Mc = M // halves
         start = cache.index
         ids = input_ids.reshape(-1)
-        x = K.embed(ids[r * mloc:(r + 1) * mloc], self.embedding)                 # this rank's rows of the stream
-        sp.rs_reduce(x, self.layers[0].attn_norm, eps, has_partials=False)       # starts the chain: norm + broadcast
+        main = torch.cuda.current_stream()
+        if halves == 2 and getattr(self, "_sp_side", None) is None:
+            self._sp_side = torch.cuda.Stream()
+        streams = [main] if halves == 1 else [main, self._sp_side]
+        states = [self.comm.nvls_state(Mc, c.hidden_size, tag=h) for h in range(halves)]
+        if halves == 2:
+            self._sp_side.wait_stream(main)
+        Bc, Sc = (B, S) if halves == 1 else (1, Mc)
+        xs, lens = [], []
+        for h, (sp, stream) in enumerate(zip(states, streams)):
+            with torch.cuda.stream(stream):
+                r, mloc = self.rank, sp.mloc
+                rows = ids[h * Mc + r * mloc:h * Mc + (r + 1) * mloc]
+                xs.append(K.embed(rows, self.embedding))                          # this rank's rows of the stream
+                lens.append(cache.len_dev + h * Mc if h else cache.len_dev)       # first cache slot of this half
+                sp.rs_reduce(xs[h], self.layers[0].attn_norm, eps, has_partials=False)    # chain start: norm + broadcast
         for i, l in enumerate(self.layers):
             kc, vc = cache.k[i], cache.v[i]
-            qkv = sp.ag_gemm(l.wqkv, K.PLAIN)                                    # [M, (nh+2nkv)·hd] local heads, all tokens
-            q_rot = torch.empty((M, nh * hd), dtype=qkv.dtype, device=qkv.device)
-            K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
-                            pad_left=cache.pad_left, q_out=q_rot)
-            attn = self._prefill_attn(q_rot.view(B, S, nh, hd), kc, vc, start, S, cache).view(M, nh * hd)
-            K.linear(attn, l.wo, out=sp.next_part())                             # partial product stays on this rank
-            sp.rs_reduce(x, l.ffn_norm, eps, has_partials=True)                  # in-switch reduce-scatter + norm + all-gather
-            h = sp.ag_gemm(l.w13, K.SWIGLU)
-            K.linear(h, l.w2, out=sp.next_part())
             nxt = self.layers[i + 1].attn_norm if i + 1 < len(self.layers) else self.final_norm
-            sp.rs_reduce(x, nxt, eps, has_partials=True)
+            appended = None
+            for h, (sp, stream) in enumerate(zip(states, streams)):
+                with torch.cuda.stream(stream):
+                    qkv = sp.ag_gemm(l.wqkv, K.PLAIN)                             # [Mc, (nh+2nkv)·hd] local heads
+                    q_rot = torch.empty((Mc, nh * hd), dtype=qkv.dtype, device=qkv.device)
+                    K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, Bc, Sc, nh, nkv, hd, cache_len=lens[h],
+                                    pad_left=cache.pad_left, q_out=q_rot)
+                    if halves == 2 and h == 0:
+                        appended = torch.cuda.Event()
+                        appended.record(stream)
+                    elif halves == 2:
+                        stream.wait_event(appended)                               # the first half's keys of this layer
+                    attn = self._prefill_attn(q_rot.view(Bc, Sc, nh, hd), kc, vc, start + h * Mc, Sc, cache).view(Mc, nh * hd)
+                    K.linear(attn, l.wo, out=sp.next_part())                      # partial product stays on this rank
+                    sp.rs_reduce(xs[h], l.ffn_norm, eps, has_partials=True)       # in-switch reduce-scatter + norm + all-gather
+                    hmid = sp.ag_gemm(l.w13, K.SWIGLU)
+                    K.linear(hmid, l.w2, out=sp.next_part())
+                    sp.rs_reduce(xs[h], nxt, eps, has_partials=True)
+        if halves == 2:
+            main.wait_stream(self._sp_side)
         # last position of every batch row, already final-normed: its owner stored it into every rank's copy
-        last = torch.arange(B, device=self.device) * S + (S - 1)
-        xl = sp.read_rows(last).contiguous()
+        if halves == 1:
+            last = torch.arange(B, device=self.device) * S + (S - 1)
+        else:
+            last = torch.tensor([Mc - 1], device=self.device)
+        xl = states[-1].read_rows(last).contiguous()
         return K.linear(xl, self.lm_head, out_f32=True)
 
     def _row_parallel(self, a: torch.Tensor, w: torch.Tensor, x: torch.Tensor) -> torch.Tensor:

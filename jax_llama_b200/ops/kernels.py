@@ -208,6 +208,14 @@ def linear(x: torch.Tensor, w: torch.Tensor, *, norm_w: Optional[torch.Tensor] =
             ensure_gemm_workspace(x.device)
         _lib.check(L.jl_gemm(x.data_ptr(), w.data_ptr(), _p(residual), out.data_ptr(), m, n, k, mode,
                              int(out_f32), sms, _stream()), "jl_gemm")
+    elif path == "gemm_2cta":
+        # the CTA-pair kernel alone (tests): shapes it does not cover are an error here, not a fallback
+        if norm_w is not None:
+            x = rmsnorm(x.view(m, k), norm_w, eps)
+        rc = L.jl_gemm_2cta(x.data_ptr(), w.data_ptr(), _p(residual), out.data_ptr(), m, n, k, mode, sms, _stream())
+        if rc == 3:
+            raise ValueError(f"jl_gemm_2cta does not cover M={m}, N={n}, K={k} (needs M >= 256, N % 256 == 0, K % 64 == 0)")
+        _lib.check(rc, "jl_gemm_2cta")
     elif path != "gemv_tma":
         raise ValueError(f"unknown linear path {path!r}")
     return out

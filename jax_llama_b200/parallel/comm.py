@@ -39,6 +39,7 @@ _EXTRA_SIGNATURES = {
     "jl_allgather_small": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "jl_comm_bump": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "jl_flag_exchange": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "jl_wait_flags": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "jl_memcpy_d2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "jl_ag_gemm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -227,12 +228,13 @@ class PeerComm:
             states[key] = SPState(self, M, H, kmax)
         return states[key]
 
-    def nvls_state(self, M: int, H: int) -> "NvlsPrefill":
-        """Symmetric (multicast-mapped) buffers of the prefill collectives for one (tokens, hidden) shape."""
-        key = (M, H)
+    def nvls_state(self, M: int, H: int, tag: int = 0) -> "NvlsPrefill":
+        """Symmetric (multicast-mapped) buffers of the prefill collectives for one (tokens, hidden) shape; `tag`
+        distinguishes independent chains of the same shape (the two halves of a pipelined prompt)."""
+        key = (M, H, tag)
         states = self.__dict__.setdefault("_nvls_states", {})
         if key not in states:
-            states[key] = NvlsPrefill(self, M, H)
+            states[key] = NvlsPrefill(self, M, H, tag)
         return states[key]
 
     # ------------------------------------------------------------------ NCCL baseline (measured, not the product)
@@ -328,9 +330,14 @@ class NvlsPrefill:
     Two ways to use it, both without NCCL:
     * sequence parallel (token count a multiple of 128·tp): `rs_reduce` on the rank's row shard, `ag_gemm`;
     * `allreduce_add` for any token count: every rank pulls the in-switch sum of all rows into its replicated stream.
+
+    No kernel that moves data ever spins on a peer: the "my GEMM is done" exchange and the wait for the owners' "rows
+    are in every copy" flags are one-warp kernels (`jl_flag_exchange`, `jl_wait_flags`) between them, so two of these
+    chains can run on two streams (the engine pipelines two halves of the prompt) without one chain's waiting kernel
+    keeping the other's producer off the SMs.
     """
 
-    def __init__(self, comm: PeerComm, M: int, H: int):
+    def __init__(self, comm: PeerComm, M: int, H: int, tag: int = 0):
         from .symm import SymmetricHeap
         self.comm, self.M, self.H = comm, M, H
         tp = comm.tp
@@ -343,20 +350,30 @@ class NvlsPrefill:
         self.part_off = [self.heap.alloc(one), self.heap.alloc(one)]
         self.a_off = [self.heap.alloc(one), self.heap.alloc(one)]
         self.part = [self.heap.view(o, (M, H), torch.bfloat16) for o in self.part_off]
-        self.counters = torch.zeros(max(1, M // 128), dtype=torch.int32, device=comm.device)
+        self.a_full = [self.heap.view(o, (M, H), torch.bfloat16) for o in self.a_off]
         self.ticket = torch.zeros(1, dtype=torch.int32, device=comm.device)
-        self.gemm_off = comm.flag_block(("nvls_gemm",), MAX_TP)
-        self.ready_off = comm.flag_block(("nvls_ready",), MAX_TP)
+        self.gemm_off = comm.flag_block(("nvls_gemm", M, H, tag), MAX_TP)
+        self.ready_off = comm.flag_block(("nvls_ready", M, H, tag), MAX_TP)
         self.parity = 0
         self.slot = 0
         self.use_nccl_baseline = False          # bench only: time the NCCL all-reduce in place of the in-switch pull
-        comm.__dict__.setdefault("_nvls_epochs", {"gemm": 0, "ready": 0})
-        self.ep = comm._nvls_epochs            # epochs persist across forwards and shapes (flags are never reset)
+        self.ep = {"gemm": 0, "ready": 0}      # this state's flag blocks are its own: epochs start at zero with them
 
     def next_part(self) -> torch.Tensor:
         """Output buffer of the next row-parallel GEMM (its partial product stays on this rank)."""
         self.slot ^= 1
         return self.part[self.slot]
+
+    def _exchange_gemm_done(self) -> None:
+        cm = self.comm
+        self.ep["gemm"] += 1
+        _lib.check(_L().jl_flag_exchange(cm.flag_ptrs, self.gemm_off, self.ep["gemm"], cm.tp, cm.rank, K._stream()),
+                   "jl_flag_exchange")
+
+    def _wait_ready(self) -> None:
+        cm = self.comm
+        _lib.check(_L().jl_wait_flags(cm._own_flags + 4 * self.ready_off, self.ep["ready"], None, cm.tp, cm.rank,
+                                      K._stream()), "jl_wait_flags")
 
     def allreduce_add(self, x: torch.Tensor) -> torch.Tensor:
         """x += Σ_ranks part (the buffer handed out by the last `next_part`), all rows, replicated result."""
@@ -365,9 +382,9 @@ class NvlsPrefill:
             y = self.part[self.slot].clone()
             dist.all_reduce(y, group=cm.group)
             return x.add_(y)
-        self.ep["gemm"] += 1
+        self._exchange_gemm_done()
         _lib.check(_L().jl_rs_reduce_mm(x.data_ptr(), self.heap.mc(self.part_off[self.slot]), None, None, self.M, self.H,
-                                        1, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off, self.ready_off,
+                                        2, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off, self.ready_off,
                                         self.ep["gemm"], 0, self.ticket.data_ptr(), 0.0, K._stream()), "jl_rs_reduce_mm")
         return x
 
@@ -377,32 +394,22 @@ class NvlsPrefill:
         self.parity ^= 1
         self.ep["ready"] += 1
         if has_partials:
-            self.ep["gemm"] += 1
+            self._exchange_gemm_done()
         row0 = cm.rank * self.mloc * self.H * 2
         part_mc = self.heap.mc(self.part_off[self.slot] + row0) if has_partials else None
         _lib.check(_L().jl_rs_reduce_mm(x_shard.data_ptr(), part_mc, norm_w.data_ptr(),
                                         self.heap.mc(self.a_off[self.parity] + row0), self.mloc, self.H,
-                                        1 if has_partials else 0, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off,
+                                        2 if has_partials else 0, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off,
                                         self.ready_off, self.ep["gemm"], self.ep["ready"], self.ticket.data_ptr(),
                                         float(eps), K._stream()), "jl_rs_reduce_mm")
 
     def ag_gemm(self, w: torch.Tensor, mode: int) -> torch.Tensor:
-        """y = (gathered normalised rows) · wᵀ; the GEMM's TMA producer waits per row owner for its "ready" flag."""
-        cm = self.comm
-        n, k = w.shape
-        odim = n // 2 if mode == K.SWIGLU else n
-        out = torch.empty((self.M, odim), dtype=torch.bfloat16, device=cm.device)
-        flags_local = cm._own_flags + 4 * self.ready_off
-        _lib.check(_L().jl_ag_gemm(None, self.heap.local_ptr + self.a_off[self.parity], w.data_ptr(), out.data_ptr(),
-                                   self.M, n, k, mode, cm.tp, cm.rank, flags_local, self.ep["ready"],
-                                   self.counters.data_ptr(), K.num_sms(cm.device), K._stream()), "jl_ag_gemm")
-        return out
+        """y = (gathered normalised rows) · wᵀ: a one-warp kernel waits for every owner's "ready" flag, then the plain
+        tcgen05 GEMM reads this rank's copy of the gathered activations."""
+        self._wait_ready()
+        return K.linear(self.a_full[self.parity], w, mode=mode)
 
     def read_rows(self, rows: torch.Tensor) -> torch.Tensor:
-        """Rows (global token indices) of the current gathered, normalised activations.  Every rank holds all rows
-        (their owners stored them into every copy); a one-warp kernel first waits for the owners' "ready" flags."""
-        cm = self.comm
-        _lib.check(_L().jl_wait_flags(cm._own_flags + 4 * self.ready_off, self.ep["ready"], None, cm.tp, cm.rank, K._stream()),
-                   "jl_wait_flags")
-        a = self.heap.view(self.a_off[self.parity], (self.M, self.H), torch.bfloat16)
-        return a[rows]
+        """Rows (global token indices) of the current gathered, normalised activations (every rank holds all rows)."""
+        self._wait_ready()
+        return self.a_full[self.parity][rows]

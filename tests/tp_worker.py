@@ -111,6 +111,19 @@ def main():
     assert rel(got_ar, want_sp) < 3e-2, rel(got_ar, want_sp)
     assert rel(got_sp, got_ar) < 3e-2 and rel(cache.k, cache2.k) < 2e-2
     eng.set_prefill_path(None)
+    # one long prompt: two halves pipelined on two streams (the second half attends to the first half's keys)
+    S1 = 256 * world
+    ids_1 = torch.randint(3, cfg.vocab_size, (1, S1), generator=torch.Generator().manual_seed(10))
+    want_1 = ref.forward(full32, cfg, ids_1).logits[:, -1]
+    for _ in range(2):
+        cache_1 = eng.new_cache(1, S1 + 8)
+        got_1 = eng.forward(ids_1.to(dev), cache=cache_1, last_only=True).logits[:, 0]
+        assert rel(got_1, want_1) < 3e-2, rel(got_1, want_1)
+    os.environ["JLLAMA_SP_PIPELINE"] = "0"
+    cache_1b = eng.new_cache(1, S1 + 8)
+    got_1b = eng.forward(ids_1.to(dev), cache=cache_1b, last_only=True).logits[:, 0]
+    del os.environ["JLLAMA_SP_PIPELINE"]
+    assert rel(got_1, got_1b) < 1e-2 and rel(cache_1.k, cache_1b.k) < 1e-2
     # a token count that is not a multiple of 128·tp takes the all-reduce path on its own
     ids_odd = ids_sp[:, :S - 3]
     want_odd = ref.forward(full32, cfg, ids_odd).logits[:, -1]
