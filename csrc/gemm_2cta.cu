@@ -17,6 +17,8 @@
 // Used for token-major GEMMs with M >= 256 and N a multiple of 256 (every prefill GEMM of the LLaMA shapes); other
 // shapes take the single-CTA kernel (gemm_tcgen05.cu).  Replaces the cuBLAS GEMMs XLA emitted for
 // /root/reference/jax_llama/model.py:119-150 (wq/wk/wv/wo) and :311-338 (w1/w2/w3).
+#include <stdlib.h>
+
 #include "jllama_b200.h"
 #include "tcgen05.cuh"
 
@@ -54,8 +56,11 @@ __device__ __forceinline__ uint32_t g2_mapa(uint32_t local_smem_addr, uint32_t r
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
   return r;
 }
+// arrive on an mbarrier of another CTA of the cluster.  Default semantics on purpose: `.release.cluster` compiles to
+// MEMBAR.ALL.GPU + ERRBAR in front of the arrive, which in the producer loop waited for the previous stage's TMA
+// loads every time (pipeline depth 1: the first version of this kernel ran at half the single-CTA kernel's speed).
 __device__ __forceinline__ void g2_remote_arrive(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load issued by either CTA of the pair; the bytes are accounted on the LEADER's mbarrier
 __device__ __forceinline__ void g2_tma_load_2d(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
@@ -267,6 +272,10 @@ int make_tmap_2d_bf16_plain(CUtensorMap* out, const void* base, uint64_t rows, u
 using namespace jl;
 
 // 0 = launched; JL_ERR_UNSUPPORTED (3) = shape not covered by the pair kernel (caller takes the single-CTA kernel)
+// clusters of this kernel that can be resident at once (0 until the first launch of that epilogue mode)
+static int g2_pairs_used = 0;
+extern "C" JL_API int jl_gemm_2cta_pairs(void) { return g2_pairs_used; }
+
 extern "C" JL_API int jl_gemm_2cta(const void* x, const void* w, const void* residual, void* out, int M, int N, int K,
                                    int mode, int num_sms, void* stream) {
   if (M < 256 || N % G2_BN != 0 || K % G2_BK != 0 || mode < 0 || mode > 2) return JL_ERR_UNSUPPORTED;
@@ -288,17 +297,32 @@ extern "C" JL_API int jl_gemm_2cta(const void* x, const void* w, const void* res
   if (stages > num_kb * 2) stages = num_kb * 2 < 2 ? 2 : num_kb * 2;
   p.stages = stages;
   const size_t smem = (size_t)stages * G2_STAGE_BYTES + G2_EPI_BYTES + 8 * (2 * stages + 4) + 16 + 1024;
-  int grid = p.a_blocks * p.b_blocks * 2;
-  const int max_grid = (num_sms / 2) * 2;
-  if (grid > max_grid) grid = max_grid;
   void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const Gemm2Params) =
       mode == G2_SWIGLU ? gemm2_kernel<G2_SWIGLU> : (mode == G2_RESIDUAL ? gemm2_kernel<G2_RESIDUAL> : gemm2_kernel<G2_PLAIN>);
   JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(G2_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = (cudaStream_t)stream;
+  // The tile loop is persistent, so every cluster of the grid must be resident at once: a pair that only starts when
+  // another one has finished doubles the run time.  Not every TPC can host a 2-CTA cluster of this size on every part
+  // (measured here: fewer than num_sms / 2), so ask the runtime how many fit.
+  static int max_pairs[3] = {0, 0, 0};
+  if (max_pairs[mode] == 0) {
+    cfg.gridDim = dim3((num_sms / 2) * 2);
+    cudaLaunchAttribute cattr[1];
+    cattr[0].id = cudaLaunchAttributeClusterDimension;
+    cattr[0].val.clusterDim.x = 2; cattr[0].val.clusterDim.y = 1; cattr[0].val.clusterDim.z = 1;
+    cfg.attrs = cattr; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n < 1) { cudaGetLastError(); n = num_sms / 2; }
+    if (const char* e = getenv("JLLAMA_GEMM_PAIRS")) { const int v = atoi(e); if (v >= 1) n = v; }
+    max_pairs[mode] = n < num_sms / 2 ? n : num_sms / 2;
+  }
+  int grid = p.a_blocks * p.b_blocks * 2;
+  if (grid > 2 * max_pairs[mode]) grid = 2 * max_pairs[mode];
+  cfg.gridDim = dim3(grid);
+  g2_pairs_used = max_pairs[mode];
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;

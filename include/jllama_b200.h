@@ -240,6 +240,7 @@ int jl_nvls_bcast_f32(const float* src, float* dst_mc, int rows, int cols, int s
  * Returns 3 (nothing launched) for other shapes; jl_gemm tries this first and falls back to its single-CTA kernel. */
 int jl_gemm_2cta(const void* x, const void* w, const void* residual, void* out, int M, int N, int K, int mode,
                  int num_sms, void* stream);
+int jl_gemm_2cta_pairs(void);   /* 2-CTA clusters resident at once on this GPU (the persistent grid uses exactly these) */
 
 /* NVLS form of the owner-side step of the sequence-parallel prefill, and the all-reduce of a row-parallel GEMM for any
  * token count (partition.py:67,70 is what GSPMD all-reduced there).  The GEMM before it stored this rank's bf16 partial
