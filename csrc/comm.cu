@@ -173,18 +173,20 @@ __global__ void __launch_bounds__(256) allgather_small_kernel(const GatherParams
 }
 
 // stream-side wait: later kernels on this stream may read what the peers published before raising their flags
+// (No early `launch_dependents` in the two waiting kernels: a GEMM launched programmatically behind them would take every
+// SM's shared memory and then sit in its dependency wait while this kernel spins — and the kernel this one waits for,
+// on another stream of a peer whose GPU is in the same state, could never be scheduled.  Measured: deadlock on 8B.)
 __global__ void wait_flags_kernel(const int* flags, int epoch, const int* seq_ptr, int tp, int rank) {
   pdl_wait();
-  pdl_launch_dependents();
   if (threadIdx.x < tp) wait_flag(flags + threadIdx.x, epoch + (seq_ptr ? *seq_ptr : 0), rank, threadIdx.x, 6);
 }
 
 // publish this rank's flag to every rank, then wait for everybody's: one warp.  Kernels that move data never spin on
 // a peer themselves (a kernel that fills the SMs while it waits could keep the very kernel it waits for — on another
 // stream of a peer — from being scheduled); the waiting is done by these one-warp kernels between them.
-__global__ void flag_exchange_kernel(PeerTable peers, int flag_off, int epoch, int tp, int rank) {
+__global__ void flag_exchange_kernel(PeerTable peers, int flag_off, int epoch, const int* base, int tp, int rank) {
   pdl_wait();
-  pdl_launch_dependents();
+  if (base != nullptr) epoch += *base;         // device epoch base: the same captured launch is right on every graph replay
   if (threadIdx.x < tp) {
     __threadfence_system();
     st_release_sys(peers.flags[threadIdx.x] + flag_off + rank, epoch);
@@ -288,11 +290,12 @@ extern "C" JL_API int jl_wait_flags(const int* flags, int epoch, const int* seq_
   return JL_OK;
 }
 
-extern "C" JL_API int jl_flag_exchange(void* const* peer_flags, int flag_off, int epoch, int tp, int rank, void* stream) {
+extern "C" JL_API int jl_flag_exchange(void* const* peer_flags, int flag_off, int epoch, const int* base, int tp, int rank,
+                                       void* stream) {
   JL_CHECK_ARG(peer_flags && tp >= 1 && tp <= MAX_TP && rank >= 0 && rank < tp, "jl_flag_exchange: bad arguments");
   PeerTable t{};
   for (int i = 0; i < tp; ++i) t.flags[i] = (int*)peer_flags[i];
-  JL_CUDA(launch_pdl(flag_exchange_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, t, flag_off, epoch, tp, rank));
+  JL_CUDA(launch_pdl(flag_exchange_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, t, flag_off, epoch, base, tp, rank));
   return JL_OK;
 }
 

@@ -142,6 +142,7 @@ struct RsMmParams {
   uint4* xn_mc;                     // multicast address of the gathered activations at this rank's first row (or null)
   int* flags[8];                    // every rank's flag array (index rank = local)
   int* ticket;
+  const int* epoch_base;            // device epoch base added to ready_epoch (null: 0) — CUDA-graph replays stay correct
   int H8, tp, rank, gemm_flag_off, ready_flag_off, gemm_epoch, ready_epoch, has_partials;
   float inv_h, eps;
 };
@@ -228,7 +229,7 @@ __global__ void __launch_bounds__(512) rs_reduce_mm_kernel(const RsMmParams p) {
     __syncthreads();
     if (s_last && threadIdx.x < p.tp) {
       __threadfence_system();
-      st_release_sys(p.flags[threadIdx.x] + p.ready_flag_off + p.rank, p.ready_epoch);
+      st_release_sys(p.flags[threadIdx.x] + p.ready_flag_off + p.rank, p.ready_epoch + (p.epoch_base ? *p.epoch_base : 0));
     }
   }
 }
@@ -273,15 +274,15 @@ extern "C" JL_API int jl_rs_reduce(void* x, const void* partials, const void* no
 // has_partials = 0 skips the reduction (chain start on the embedding rows).
 extern "C" JL_API int jl_rs_reduce_mm(void* x, const void* part_mc, const void* norm_w, void* xn_mc, int rows, int H,
                                       int has_partials, int tp, int rank, void* const* peer_flags, int gemm_flag_off,
-                                      int ready_flag_off, int gemm_epoch, int ready_epoch, int* ticket, float eps,
-                                      void* stream) {
+                                      int ready_flag_off, int gemm_epoch, int ready_epoch, const int* epoch_base, int* ticket,
+                                      float eps, void* stream) {
   JL_CHECK_ARG(H % 8 == 0 && H <= 16384, "jl_rs_reduce_mm: H=%d must be a multiple of 8 and <= 16384", H);
   JL_CHECK_ARG(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "jl_rs_reduce_mm: bad tp/rank");
   JL_CHECK_ARG(!has_partials || part_mc != nullptr, "jl_rs_reduce_mm: needs the multicast address of the partials");
   if (rows == 0) return JL_OK;
   RsMmParams p{};
   p.x = (__nv_bfloat16*)x; p.part_mc = (const uint4*)part_mc; p.norm_w = (const __nv_bfloat16*)norm_w;
-  p.xn_mc = (uint4*)xn_mc; p.ticket = ticket;
+  p.xn_mc = (uint4*)xn_mc; p.ticket = ticket; p.epoch_base = epoch_base;
   for (int i = 0; i < tp; ++i) p.flags[i] = (int*)peer_flags[i];
   p.H8 = H / 8; p.tp = tp; p.rank = rank; p.gemm_flag_off = gemm_flag_off; p.ready_flag_off = ready_flag_off;
   p.gemm_epoch = gemm_epoch; p.ready_epoch = ready_epoch; p.has_partials = has_partials;

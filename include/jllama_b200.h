@@ -191,7 +191,8 @@ int jl_allgather_small(const void* src, void* out, int n_bytes, int slot_bytes, 
 int jl_comm_bump(int* seq_ptr, int n, void* stream);
 /* one warp: flags[r][flag_off + rank] = epoch on every rank r, then wait until this rank's flags[flag_off + 0..tp) >= epoch
  * ("every rank has finished the kernel before this one on its stream") */
-int jl_flag_exchange(void* const* peer_flags, int flag_off, int epoch, int tp, int rank, void* stream);
+int jl_flag_exchange(void* const* peer_flags, int flag_off, int epoch, const int* base /* device int added to epoch, or NULL */,
+                     int tp, int rank, void* stream);
 /* one warp waits (on the stream) until flags[0..tp) >= epoch (+ *seq_ptr if given: device epoch counter, graph safe):
  * later kernels may read what the peers published first */
 int jl_wait_flags(const int* flags, int epoch, const int* seq_ptr, int tp, int rank, void* stream);
@@ -251,7 +252,8 @@ int jl_gemm_2cta_pairs(void);   /* 2-CTA clusters resident at once on this GPU (
  * plain all-reduce into a replicated residual stream (rows = all tokens). */
 int jl_rs_reduce_mm(void* x, const void* part_mc, const void* norm_w, void* xn_mc, int rows, int H, int has_partials,
                     int tp, int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off, int gemm_epoch,
-                    int ready_epoch, int* ticket, float eps, void* stream);
+                    int ready_epoch, const int* epoch_base /* device int added to ready_epoch, or NULL */, int* ticket,
+                    float eps, void* stream);
 
 /* NVLS self-test over a multicast mapping of a symmetric buffer (parallel/symm.py): `mc` is the multicast
  * address.  op 0: out[i] = sum over ranks of fp32 buf[i] (multimem.ld_reduce); 1: 8-byte packets {src[i], tag}

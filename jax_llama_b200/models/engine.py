@@ -365,6 +365,8 @@ class B200Engine:
         if halves == 2:
             self._sp_side.wait_stream(main)
         Bc, Sc = (B, S) if halves == 1 else (1, Mc)
+        last_rows = (torch.arange(B, device=self.device) * S + (S - 1)) if halves == 1 else \
+            torch.arange(Mc - 1, Mc, device=self.device)                         # device-side (graph capturable)
         xs, lens = [], []
         for h, (sp, stream) in enumerate(zip(states, streams)):
             with torch.cuda.stream(stream):
@@ -394,15 +396,43 @@ class B200Engine:
                     hmid = sp.ag_gemm(l.w13, K.SWIGLU)
                     K.linear(hmid, l.w2, out=sp.next_part())
                     sp.rs_reduce(xs[h], nxt, eps, has_partials=True)
+        # last position of every batch row, already final-normed: its owner stored it into every rank's copy
+        with torch.cuda.stream(streams[-1]):
+            xl = states[-1].read_rows(last_rows).contiguous()
+        for sp, stream in zip(states, streams):
+            with torch.cuda.stream(stream):
+                sp.end_forward()                                                  # device epoch base += collectives issued
         if halves == 2:
             main.wait_stream(self._sp_side)
-        # last position of every batch row, already final-normed: its owner stored it into every rank's copy
-        if halves == 1:
-            last = torch.arange(B, device=self.device) * S + (S - 1)
-        else:
-            last = torch.tensor([Mc - 1], device=self.device)
-        xl = states[-1].read_rows(last).contiguous()
         return K.linear(xl, self.lm_head, out_f32=True)
+
+    def _prefill_sp_graphed(self, input_ids: torch.Tensor, cache: DeviceKVCache, B: int, S: int) -> torch.Tensor:
+        """`_prefill_sp` replayed from a CUDA graph.  At tp > 1 the prefill is a few hundred short kernels per forward
+        (GEMMs of 1/tp the width, one-warp flag kernels, two streams): issued eagerly it is bound by the host's launch
+        rate, not by the GPU.  One graph per (cache, batch, length, start slot); everything that changes between calls
+        (token ids, cache fill level, left-padding counts, flag epochs) is read from device memory."""
+        if not self.use_cuda_graph or os.environ.get("JLLAMA_SP_GRAPH", "1") == "0":
+            return self._prefill_sp(input_ids, cache, B, S)
+        graphs = self.__dict__.setdefault("_sp_graphs", {})
+        # the graph bakes the addresses of the cache tensors: all of them are part of the key, so a later cache object
+        # that happens to reuse one address can never pick up a graph that points at freed memory
+        key = (cache.k.data_ptr(), cache.v.data_ptr(), cache.len_dev.data_ptr(), cache.pad_left.data_ptr(), B, S, cache.index)
+        ent = graphs.get(key)
+        if ent is None:
+            while len(graphs) >= 4:                # each graph owns its activations: keep a handful
+                graphs.pop(next(iter(graphs)))
+            ids_static = input_ids.clone()
+            for _ in range(2):                     # eager warm-up: symmetric buffers, streams, both flag parities
+                self._prefill_sp(ids_static, cache, B, S)
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                out_static = self._prefill_sp(ids_static, cache, B, S)
+            ent = graphs[key] = (g, ids_static, out_static)
+        g, ids_static, out_static = ent
+        ids_static.copy_(input_ids)
+        g.replay()
+        return out_static.clone()
 
     def _row_parallel(self, a: torch.Tensor, w: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
         """x += a · wᵀ summed over tensor-parallel ranks (the reference's GSPMD all-reduce after wo / w2)."""
@@ -459,7 +489,8 @@ class B200Engine:
         if (self.tp > 1 and S > 1 and last_only and with_head and positions is None and self.hd == 128
                 and (B * S) % (128 * self.tp) == 0 and self.sequence_parallel_prefill):
             # sequence-parallel prefill: all-gather→GEMM and GEMM→reduce-scatter fused over NVLink peer memory
-            logits = self._prefill_sp(input_ids, cache, B, S)
+            # a cache that lives beyond this call (decode state, caller-owned) is worth a graph; a throw-away one is not
+            logits = self._prefill_sp(input_ids, cache, B, S) if own_cache else self._prefill_sp_graphed(input_ids, cache, B, S)
             cache.set_index(cache.index + S)
             out = ModelOutput(past_key_values=None if own_cache else cache)
             if gather_logits:
@@ -475,6 +506,8 @@ class B200Engine:
         x = self._layers(x, B, S, cache, positions)
         if self.comm is not None:
             self.comm.end_sequence()
+            if self.tp > 1:
+                self.comm.nvls_end_forward()        # in-switch all-reduces of this forward: advance their epoch base
         cache.set_index(cache.index + S)
         out = ModelOutput(past_key_values=None if own_cache else cache)
         if last_only:
@@ -649,6 +682,8 @@ class B200Engine:
         self._select_and_advance(st, cache, sampling, eos, pad)
         if self.comm is not None:
             self.comm.end_sequence()
+            if self.tp > 1:
+                self.comm.nvls_end_forward()
 
     def _graph_for(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int
                    ) -> Optional[torch.cuda.CUDAGraph]:

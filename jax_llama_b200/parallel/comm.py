@@ -39,7 +39,7 @@ _EXTRA_SIGNATURES = {
     "jl_allgather_small": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "jl_comm_bump": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
-    "jl_flag_exchange": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "jl_flag_exchange": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "jl_wait_flags": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "jl_memcpy_d2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "jl_ag_gemm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -47,8 +47,8 @@ _EXTRA_SIGNATURES = {
     "jl_gemm_rs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                              C.c_void_p]),
     "jl_rs_reduce_mm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
-                                  C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
-                                  C.c_void_p]),
+                                  C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                  C.c_float, C.c_void_p]),
     "jl_rs_reduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
                                C.c_void_p]),
@@ -221,13 +221,6 @@ class PeerComm:
             dist.barrier(group=self.group)
         return local, (C.c_void_p * MAX_TP)(*ptrs)
 
-    def sp_state(self, M: int, H: int, kmax: int) -> "SPState":
-        key = (M, H, kmax)
-        states = self.__dict__.setdefault("_sp_states", {})
-        if key not in states:
-            states[key] = SPState(self, M, H, kmax)
-        return states[key]
-
     def nvls_state(self, M: int, H: int, tag: int = 0) -> "NvlsPrefill":
         """Symmetric (multicast-mapped) buffers of the prefill collectives for one (tokens, hidden) shape; `tag`
         distinguishes independent chains of the same shape (the two halves of a pipelined prompt)."""
@@ -237,86 +230,17 @@ class PeerComm:
             states[key] = NvlsPrefill(self, M, H, tag)
         return states[key]
 
+    def nvls_end_forward(self) -> None:
+        """End of a forward: every NVLS prefill state that issued collectives advances its device epoch base."""
+        for st in self.__dict__.get("_nvls_states", {}).values():
+            if st.rel:
+                st.end_forward()
+
     # ------------------------------------------------------------------ NCCL baseline (measured, not the product)
     def allreduce_nccl(self, t: torch.Tensor) -> torch.Tensor:
         if self.tp > 1:
             dist.all_reduce(t, group=self.group)
         return t
-
-
-class SPState:
-    """Buffers and epochs of the sequence-parallel prefill chain for one (tokens, hidden) shape.
-
-    rs_buf     [tp][mloc][H] bf16   receive buffer for the partial tiles peers scatter out of their GEMM epilogues
-    a_full[2]  [M][H] bf16          the gathered, normalised activations (peer-visible, double-buffered by parity):
-                                    every row owner pushes its rows into every rank's copy from `rs_reduce`
-    """
-
-    def __init__(self, comm: PeerComm, M: int, H: int, kmax: int):
-        tp = comm.tp
-        if M % (tp * 128):
-            raise ValueError(f"sequence-parallel prefill needs a token count that is a multiple of {tp * 128}, got {M}")
-        self.comm, self.M, self.H, self.mloc = comm, M, H, M // tp
-        dev = comm.device
-        self.rs_local, self.rs_ptrs = comm.symmetric_alloc(tp * self.mloc * H * 2)
-        if kmax != H:
-            raise ValueError("the gathered operand of both column-parallel GEMMs is the hidden state (kmax == H)")
-        a0, ptrs0 = comm.symmetric_alloc(M * H * 2)
-        a1, ptrs1 = comm.symmetric_alloc(M * H * 2)
-        self.a_local = (a0, a1)
-        self.a_ptrs = (ptrs0, ptrs1)
-        self.counters = torch.zeros(M // 128, dtype=torch.int32, device=dev)
-        self.ticket = torch.zeros(1, dtype=torch.int32, device=dev)
-        self.gemm_off = comm.flag_block(("sp_gemm",), MAX_TP)
-        self.ready_off = comm.flag_block(("sp_ready",), MAX_TP)
-        self.parity = 0
-        # epochs persist across forwards (flags are never reset)
-        comm.__dict__.setdefault("_sp_epochs", {"gemm": 0, "ready": 0})
-        self.ep = comm._sp_epochs
-
-    def rs_reduce(self, x_shard: torch.Tensor, norm_w: torch.Tensor, eps: float, n_src: int) -> None:
-        """x_shard += Σ partials (n_src = tp) or nothing (n_src = 0); RMSNorm → next parity's shard; publish."""
-        cm = self.comm
-        self.parity ^= 1
-        self.ep["ready"] += 1
-        if n_src:
-            self.ep["gemm"] += 1
-        _lib.check(_L().jl_rs_reduce(x_shard.data_ptr(), self.rs_local, norm_w.data_ptr(), self.a_ptrs[self.parity],
-                                     cm.rank * self.mloc, self.mloc, self.H, n_src, cm.tp, cm.rank, cm.flag_ptrs,
-                                     self.gemm_off, self.ready_off,
-                                     self.ep["gemm"], self.ep["ready"], self.ticket.data_ptr(), float(eps), K._stream()),
-                   "jl_rs_reduce")
-
-    def ag_gemm(self, w: torch.Tensor, mode: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """y = all_gather(normalised shards) · wᵀ: the rows were pushed by their owners (`rs_reduce`); the GEMM's TMA
-        producer waits for an owner's flag before the first tile that needs its rows."""
-        cm = self.comm
-        n, k = w.shape
-        odim = n // 2 if mode == K.SWIGLU else n
-        if out is None:
-            out = torch.empty((self.M, odim), dtype=torch.bfloat16, device=cm.device)
-        if k != self.H:
-            raise ValueError(f"ag_gemm expects K == hidden size ({self.H}), got {k}")
-        flags_local = cm._own_flags + 4 * self.ready_off
-        _lib.check(_L().jl_ag_gemm(None, self.a_local[self.parity], w.data_ptr(), out.data_ptr(), self.M, n,
-                                   k, mode, cm.tp, cm.rank, flags_local, self.ep["ready"], self.counters.data_ptr(),
-                                   K.num_sms(cm.device), K._stream()), "jl_ag_gemm")
-        return out
-
-    def gemm_rs(self, a: torch.Tensor, w: torch.Tensor) -> None:
-        """Partial a · wᵀ scattered tile by tile into the row owners' receive buffers."""
-        cm = self.comm
-        n, k = w.shape
-        _lib.check(_L().jl_gemm_rs(a.data_ptr(), w.data_ptr(), self.rs_ptrs, self.M, n, k, cm.tp, cm.rank,
-                                   K.num_sms(cm.device), K._stream()), "jl_gemm_rs")
-
-    def read_rows(self, rows: torch.Tensor) -> torch.Tensor:
-        """Rows (global token indices owned by this rank) of the current normalised shard as a torch tensor."""
-        out = torch.empty((self.mloc, self.H), dtype=torch.bfloat16, device=self.comm.device)
-        src = self.a_local[self.parity] + self.comm.rank * self.mloc * self.H * 2
-        _lib.check(_L().jl_memcpy_d2d(out.data_ptr(), src, out.numel() * 2, K._stream()),
-                   "jl_memcpy_d2d")
-        return out[rows - self.comm.rank * self.mloc]
 
 
 class NvlsPrefill:
@@ -357,7 +281,12 @@ class NvlsPrefill:
         self.parity = 0
         self.slot = 0
         self.use_nccl_baseline = False          # bench only: time the NCCL all-reduce in place of the in-switch pull
-        self.ep = {"gemm": 0, "ready": 0}      # this state's flag blocks are its own: epochs start at zero with them
+        # Flag values are (device epoch base) + (position of the collective inside this forward): the base lives on the
+        # device and is advanced by one tiny kernel at the end of every forward (`end_forward`), so a forward captured
+        # in a CUDA graph stays correct on every replay; `rel` only counts inside one forward.
+        self.base = torch.zeros(1, dtype=torch.int32, device=comm.device)
+        self.rel = 0
+        self.last_ready = 0
 
     def next_part(self) -> torch.Tensor:
         """Output buffer of the next row-parallel GEMM (its partial product stays on this rank)."""
@@ -366,14 +295,21 @@ class NvlsPrefill:
 
     def _exchange_gemm_done(self) -> None:
         cm = self.comm
-        self.ep["gemm"] += 1
-        _lib.check(_L().jl_flag_exchange(cm.flag_ptrs, self.gemm_off, self.ep["gemm"], cm.tp, cm.rank, K._stream()),
-                   "jl_flag_exchange")
+        self.rel += 1
+        _lib.check(_L().jl_flag_exchange(cm.flag_ptrs, self.gemm_off, self.rel, self.base.data_ptr(), cm.tp, cm.rank,
+                                         K._stream()), "jl_flag_exchange")
 
     def _wait_ready(self) -> None:
         cm = self.comm
-        _lib.check(_L().jl_wait_flags(cm._own_flags + 4 * self.ready_off, self.ep["ready"], None, cm.tp, cm.rank,
-                                      K._stream()), "jl_wait_flags")
+        _lib.check(_L().jl_wait_flags(cm._own_flags + 4 * self.ready_off, self.last_ready, self.base.data_ptr(), cm.tp,
+                                      cm.rank, K._stream()), "jl_wait_flags")
+
+    def end_forward(self) -> None:
+        """Advance the device epoch base past the collectives of this forward (on the current stream)."""
+        if self.rel:
+            _lib.check(_L().jl_comm_bump(self.base.data_ptr(), self.rel, K._stream()), "jl_comm_bump")
+        self.rel = 0
+        self.last_ready = 0
 
     def allreduce_add(self, x: torch.Tensor) -> torch.Tensor:
         """x += Σ_ranks part (the buffer handed out by the last `next_part`), all rows, replicated result."""
@@ -385,22 +321,23 @@ class NvlsPrefill:
         self._exchange_gemm_done()
         _lib.check(_L().jl_rs_reduce_mm(x.data_ptr(), self.heap.mc(self.part_off[self.slot]), None, None, self.M, self.H,
                                         2, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off, self.ready_off,
-                                        self.ep["gemm"], 0, self.ticket.data_ptr(), 0.0, K._stream()), "jl_rs_reduce_mm")
+                                        0, 0, None, self.ticket.data_ptr(), 0.0, K._stream()), "jl_rs_reduce_mm")
         return x
 
     def rs_reduce(self, x_shard: torch.Tensor, norm_w: torch.Tensor, eps: float, has_partials: bool) -> None:
         """Owner step: x_shard += in-switch Σ of this rank's rows; RMSNorm → every rank's a_full[next parity]; publish."""
         cm = self.comm
         self.parity ^= 1
-        self.ep["ready"] += 1
         if has_partials:
             self._exchange_gemm_done()
+        self.rel += 1
+        self.last_ready = self.rel
         row0 = cm.rank * self.mloc * self.H * 2
         part_mc = self.heap.mc(self.part_off[self.slot] + row0) if has_partials else None
         _lib.check(_L().jl_rs_reduce_mm(x_shard.data_ptr(), part_mc, norm_w.data_ptr(),
                                         self.heap.mc(self.a_off[self.parity] + row0), self.mloc, self.H,
                                         2 if has_partials else 0, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off,
-                                        self.ready_off, self.ep["gemm"], self.ep["ready"], self.ticket.data_ptr(),
+                                        self.ready_off, 0, self.last_ready, self.base.data_ptr(), self.ticket.data_ptr(),
                                         float(eps), K._stream()), "jl_rs_reduce_mm")
 
     def ag_gemm(self, w: torch.Tensor, mode: int) -> torch.Tensor:
