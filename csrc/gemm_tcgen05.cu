@@ -36,21 +36,6 @@ struct GemmParams {
   int a_blocks, b_blocks;   // tile counts
   int stages;
   uint64_t hint_a, hint_b;
-  // ---- tensor-parallel, sequence-parallel prefill (COMM != 0) ------------------------------------------
-  // COMM_SCATTER (GEMM → reduce-scatter): the D tile of token rows [m0, m0+128) is stored, as this rank's bf16
-  // partial, straight into the row owner's receive buffer over NVLink: owner = m0 / mloc,
-  // dst = scatter_out[owner] + ((rank·mloc + row − owner·mloc)·ldo + col).
-  void* scatter_out[8];
-  // COMM_GATHER (all-gather → GEMM): warp 3 of every CTA copies a slice of the peers' activation shards
-  // (gather_src[r]: [mloc, K] on rank r, peer-mapped) into the local A buffer gather_dst [tp·mloc, K] and bumps
-  // a per-row-block counter; the TMA producer only loads an A tile once its row block is complete.
-  const void* gather_src[8];
-  void* gather_dst;
-  const int* ready_flags;            // local flag array: ready_flags[r] >= ready_epoch ⇔ rank r's shard is final
-  unsigned int* gather_counters;     // [a_blocks], monotonically increasing
-  unsigned int gather_target;        // value counters reach when this call's copies of a row block are done
-  int ready_epoch, tp, rank, mloc, gather_parts;
-  bool gather_pushed;                // rows are pushed into the A buffer by their owners; nothing to copy here
   // ---- split-K for swap-AB launches with fewer weight-row tiles than SMs (decode at batch 9..128: N = 4096
   // gives 32 tiles, i.e. 22 % of the SMs streaming): each tile's K range is cut into `ksplit` work items, the
   // fp32 partials meet in `ws` ([ksplit][tokens][features]) and the last item to arrive (ticket) sums them in
@@ -60,16 +45,13 @@ struct GemmParams {
   int* tickets;                      // [tiles], zero between launches (the finishing item resets its ticket)
 };
 
-enum { COMM_NONE = 0, COMM_GATHER = 1, COMM_SCATTER = 2 };
-
 __host__ __device__ constexpr int tmem_cols_for(int bn) {
   return 2 * bn <= 32 ? 32 : (2 * bn <= 64 ? 64 : (2 * bn <= 128 ? 128 : (2 * bn <= 256 ? 256 : 512)));
 }
 
-template <int BN, int EPI, bool SWAP, bool OUT_F32, int COMM = COMM_NONE>
+template <int BN, int EPI, bool SWAP, bool OUT_F32>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-            const __grid_constant__ CUtensorMap tmap_a_local, const GemmParams p) {
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2;
   constexpr uint32_t B_BYTES = BN * GEMM_BK * 2;
@@ -117,38 +99,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // ===================================================== TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      uint32_t seen = 0;                                   // sources whose "rows pushed" flag was already observed
       for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
         const int t = wi % num_tiles, split = wi / num_tiles;
         const int kb0 = split * num_kb / ksplit, kb1 = (split + 1) * num_kb / ksplit;
         const int b_blk = t / p.a_blocks;
-        int a_blk = t % p.a_blocks;
-        bool a_is_local = false;
-        if constexpr (COMM == COMM_GATHER) {
-          // local rows first: remote row blocks arrive over NVLink while these tiles compute
-          a_blk = (a_blk + p.rank * (p.mloc / GEMM_BM)) % p.a_blocks;
-          a_is_local = (a_blk * GEMM_BM) / p.mloc == p.rank && !p.gather_pushed;
-          if (p.gather_pushed) {
-            // the row owners push their rows into this rank's A buffer (jl_rs_reduce); wait for the owner's flag
-            const int src = (a_blk * GEMM_BM) / p.mloc;
-            if (!((seen >> src) & 1u)) { wait_flag(p.ready_flags + src, p.ready_epoch, p.rank, src, 5); seen |= 1u << src; }
-          } else if (a_is_local) {
-            // this rank's own rows are read in place from its shard (no copy); it must be final
-            wait_flag(p.ready_flags + p.rank, p.ready_epoch, p.rank, p.rank, 5);
-          } else {
-            unsigned spins = 0;
-            while ((int)(ld_acquire_gpu_u32(p.gather_counters + a_blk) - p.gather_target) < 0) {
-              if (++spins > (1u << 26)) { printf("jllama_b200: gather of row block %d never completed\n", a_blk); __trap(); }
-            }
-          }
-          asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores → TMA (async proxy) reads
-        }
+        const int a_blk = t % p.a_blocks;
         for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
           tc::mbar_expect_tx(full_bar(stage), A_BYTES + B_BYTES);
-          if (a_is_local) tc::tma_load_2d(sa, &tmap_a_local, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM - p.rank * p.mloc, p.hint_a);
-          else tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM, p.hint_a);
+          tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM, p.hint_a);
           tc::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * GEMM_BK, b_blk * BN, p.hint_b);
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
@@ -179,39 +139,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         tc::mma_commit(tfull_bar(as));                      // accumulator complete → epilogue
       }
     }
-  } else if (warp == 3) {
-    if constexpr (COMM == COMM_GATHER) {
-      // ===================================================== all-gather: peers' shards → local A buffer
-      const int K16 = p.K / 8;                                   // 16-byte chunks per row
-      const int per_rb = GEMM_BM * K16;                          // chunks per 128-row block
-      const int per_part = (per_rb + p.gather_parts - 1) / p.gather_parts;
-      const int local_blocks = p.mloc / GEMM_BM;
-      const int n_items = p.gather_pushed ? 0 : (p.a_blocks - local_blocks) * p.gather_parts;   // remote row blocks only
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int part = item % p.gather_parts;
-        // k-th remote row block in the order the tiles will want them (the blocks after this rank's own)
-        const int rb = (p.rank * local_blocks + local_blocks + item / p.gather_parts) % p.a_blocks;
-        const int src = (rb * GEMM_BM) / p.mloc;
-        if (lane == 0) wait_flag(p.ready_flags + src, p.ready_epoch, p.rank, src, 3);
-        __syncwarp();
-        const uint4* sp = reinterpret_cast<const uint4*>(p.gather_src[src]) + (size_t)(rb * GEMM_BM - src * p.mloc) * K16;
-        uint4* dp = reinterpret_cast<uint4*>(p.gather_dst) + (size_t)rb * per_rb;
-        const int lo = part * per_part, hi = min(lo + per_part, per_rb);
-        for (int i = lo + lane; i < hi; i += 32 * 16) {
-          uint4 v[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (i + j * 32 < hi)
-              asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "l"(sp + i + j * 32) : "memory");
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (i + j * 32 < hi) dp[i + j * 32] = v[j];
-        }
-        __threadfence();
-        __syncwarp();
-        if (lane == 0) atomicAdd(p.gather_counters + rb, 1u);
-      }
-    }
   } else if (warp >= 4) {
     // ===================================================== epilogue: TMEM → registers → global
     const int quarter = warp & 3;                           // TMEM lanes [32·quarter, 32·quarter+32)
@@ -219,8 +146,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x, ++it) {
       const int t = wi % num_tiles, split = wi / num_tiles;
       const int b_blk = t / p.a_blocks;
-      int a_blk = t % p.a_blocks;
-      if constexpr (COMM == COMM_GATHER) a_blk = (a_blk + p.rank * (p.mloc / GEMM_BM)) % p.a_blocks;
+      const int a_blk = t % p.a_blocks;
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
       tc::mbar_wait(tfull_bar(as), aphase);
       tc::fence_after_sync();
@@ -286,11 +212,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
               }
             } else {
               __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)ra * p.ldo + cb0;
-              if constexpr (COMM == COMM_SCATTER) {
-                const int owner = ra / p.mloc;
-                o = reinterpret_cast<__nv_bfloat16*>(p.scatter_out[owner]) +
-                    ((size_t)p.rank * p.mloc + (ra - owner * p.mloc)) * p.ldo + cb0;
-              }
               const bool full = cb0 + CH <= p.Rb;
               uint32_t w[CH / 2];
               if constexpr (EPI == EPI_RESIDUAL) {
@@ -379,7 +300,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     }
   }
 
-  if constexpr (COMM == COMM_SCATTER) __threadfence_system();     // partial tiles must be visible to their owners
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 2) tc::tmem_dealloc(tmem_base, TMEM_COLS);
@@ -394,7 +314,7 @@ static SplitKWorkspace splitk_workspace() {
   return g_splitk[dev];
 }
 
-template <int BN, int EPI, bool SWAP, bool OUT_F32, int COMM = COMM_NONE>
+template <int BN, int EPI, bool SWAP, bool OUT_F32>
 static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int Ra, int Rb, int K, int num_sms,
                        cudaStream_t stream) {
   GemmParams p = p0;
@@ -414,11 +334,11 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
   p.a_blocks = (Ra + GEMM_BM - 1) / GEMM_BM;
   p.b_blocks = (Rb + BN - 1) / BN;
   const size_t smem = (size_t)stages * STAGE_BYTES + 8 * (2 * stages + 4) + 16 + 1024;
-  auto kern = gemm_kernel<BN, EPI, SWAP, OUT_F32, COMM>;
+  auto kern = gemm_kernel<BN, EPI, SWAP, OUT_F32>;
   JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = p.a_blocks * p.b_blocks;
   p.ksplit = 1;
-  if constexpr (SWAP && COMM == COMM_NONE) {
+  if constexpr (SWAP) {
     // few weight-row tiles (N <= ~9k at decode batch sizes): cut K so that (nearly) every SM streams weights
     const SplitKWorkspace wsp = splitk_workspace();
     // measured (8B decode, ms/step, split vs not): batch 16 5.10 vs 6.20, batch 32 6.44 vs 7.09, batch 64 9.29 vs 8.72
@@ -431,14 +351,7 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
     }
   }
   if (grid > num_sms) grid = num_sms;
-  CUtensorMap tl = ta;                          // local-shard map (COMM_GATHER only; otherwise a copy of A's)
-  if constexpr (COMM == COMM_GATHER) {
-    if (!p.gather_pushed) {
-      rc = make_tmap_2d_bf16(&tl, p.gather_src[p.rank], p.mloc, K, K, GEMM_BM);
-      if (rc) return rc;
-    }
-  }
-  JL_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), smem, stream, ta, tb, tl, p));
+  JL_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), smem, stream, ta, tb, p));
   return JL_OK;
 }
 
@@ -503,59 +416,4 @@ extern "C" JL_API int jl_gemm(const void* x, const void* w, const void* residual
   if (mode == EPI_PLAIN) return dispatch_gemm<EPI_PLAIN, false>(x, w, p, M, N, K, num_sms, s);
   if (mode == EPI_RESIDUAL) return dispatch_gemm<EPI_RESIDUAL, false>(x, w, p, M, N, K, num_sms, s);
   return dispatch_gemm<EPI_SWIGLU, false>(x, w, p, M, N, K, num_sms, s);
-}
-
-
-// ------------------------------------------------------------------------------------ sequence-parallel prefill
-// all-gather → GEMM: y[M, N] = gather(peer shards)[M, K] · W[N, K]^T, M = tp·mloc.  The gather runs INSIDE the
-// GEMM kernel (warp 3 of every CTA pulls peers' rows over NVLink into `a_full` while tiles of the local rows
-// already compute).  `counters` ([M/128] u32) is zeroed on the stream before the launch.
-extern "C" JL_API int jl_ag_gemm(void* const* peer_shards, void* a_full, const void* w, void* out, int M, int N, int K,
-                                 int mode, int tp, int rank, const int* ready_flags, int ready_epoch, void* counters,
-                                 int num_sms, void* stream) {
-  JL_CHECK_ARG(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "jl_ag_gemm: bad tp/rank %d/%d", tp, rank);
-  JL_CHECK_ARG(M % (tp * GEMM_BM) == 0, "jl_ag_gemm: M=%d must be a multiple of tp*128", M);
-  JL_CHECK_ARG(M > 128 && K % 8 == 0 && N % 16 == 0, "jl_ag_gemm: needs M > 128, K %% 8 == 0, N %% 16 == 0");
-  JL_CHECK_ARG(mode == EPI_PLAIN || mode == EPI_SWIGLU, "jl_ag_gemm: mode must be plain or SwiGLU");
-  if (num_sms <= 0) num_sms = 148;
-  GemmParams p{};
-  p.out = out; p.K = K; p.ldo = mode == EPI_SWIGLU ? N / 2 : N;
-  p.Ra = M; p.Rb = N; p.hint_a = tc::EVICT_LAST; p.hint_b = tc::EVICT_NORMAL;
-  p.tp = tp; p.rank = rank; p.mloc = M / tp;
-  p.gather_pushed = peer_shards == nullptr;       // rows arrive by push (jl_rs_reduce): only the flags are waited for
-  for (int i = 0; i < tp; ++i) p.gather_src[i] = peer_shards ? peer_shards[i] : nullptr;
-  p.gather_dst = a_full; p.ready_flags = ready_flags; p.ready_epoch = ready_epoch;
-  p.gather_counters = (unsigned int*)counters;
-  const int a_blocks = M / GEMM_BM;
-  const int remote_blocks = a_blocks - a_blocks / tp;
-  int parts = remote_blocks > 0 ? num_sms / remote_blocks : 1;
-  if (parts < 1) parts = 1;
-  p.gather_parts = parts; p.gather_target = (unsigned)parts;
-  auto s = (cudaStream_t)stream;
-  JL_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned int) * a_blocks, s));
-  if (mode == EPI_SWIGLU) {
-    if (N >= 256) return launch_gemm<256, EPI_SWIGLU, false, false, COMM_GATHER>(a_full, w, p, M, N, K, num_sms, s);
-    return launch_gemm<128, EPI_SWIGLU, false, false, COMM_GATHER>(a_full, w, p, M, N, K, num_sms, s);
-  }
-  if (N >= 256) return launch_gemm<256, EPI_PLAIN, false, false, COMM_GATHER>(a_full, w, p, M, N, K, num_sms, s);
-  return launch_gemm<128, EPI_PLAIN, false, false, COMM_GATHER>(a_full, w, p, M, N, K, num_sms, s);
-}
-
-// GEMM → reduce-scatter: this rank's partial x[M, K_local] · W[N, K_local]^T leaves the epilogue tile by tile
-// straight into the row owner's receive buffer peer_rs_buf[owner] ([tp][mloc][N] bf16 on that rank); the sum
-// over ranks, the residual add and the next RMSNorm happen in jl_rs_reduce on the owner.
-extern "C" JL_API int jl_gemm_rs(const void* x, const void* w, void* const* peer_rs_buf, int M, int N, int K, int tp,
-                                 int rank, int num_sms, void* stream) {
-  JL_CHECK_ARG(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "jl_gemm_rs: bad tp/rank %d/%d", tp, rank);
-  JL_CHECK_ARG(M % (tp * GEMM_BM) == 0, "jl_gemm_rs: M=%d must be a multiple of tp*128", M);
-  JL_CHECK_ARG(M > 128 && K % 8 == 0 && N % 32 == 0, "jl_gemm_rs: needs M > 128, K %% 8 == 0, N %% 32 == 0");
-  if (num_sms <= 0) num_sms = 148;
-  GemmParams p{};
-  p.out = nullptr; p.K = K; p.ldo = N;
-  p.Ra = M; p.Rb = N; p.hint_a = tc::EVICT_LAST; p.hint_b = tc::EVICT_NORMAL;
-  p.tp = tp; p.rank = rank; p.mloc = M / tp;
-  for (int i = 0; i < tp; ++i) p.scatter_out[i] = peer_rs_buf[i];
-  auto s = (cudaStream_t)stream;
-  if (N >= 256) return launch_gemm<256, EPI_PLAIN, false, false, COMM_SCATTER>(x, w, p, M, N, K, num_sms, s);
-  return launch_gemm<128, EPI_PLAIN, false, false, COMM_SCATTER>(x, w, p, M, N, K, num_sms, s);
 }

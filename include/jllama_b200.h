@@ -198,26 +198,6 @@ int jl_flag_exchange(void* const* peer_flags, int flag_off, int epoch, const int
 int jl_wait_flags(const int* flags, int epoch, const int* seq_ptr, int tp, int rank, void* stream);
 int jl_memcpy_d2d(void* dst, const void* src, size_t bytes, void* stream);
 
-/* Sequence-parallel prefill (M % (128*tp) == 0).  The residual stream is sharded by rows; per layer:
- *   jl_ag_gemm  — column-parallel GEMM (wqkv, w13) whose A operand is the all-gather of every rank's
- *                 normalised row shard.  peer_shards == NULL (the engine's mode): the owners PUSH their rows
- *                 into a_full from jl_rs_reduce and the TMA producer only waits for each owner's flag before
- *                 the first tile that needs its rows.  peer_shards != NULL: a gather warp inside the kernel
- *                 pulls remote row blocks over NVLink (first version, kept for A/B).
- *   jl_gemm_rs  — row-parallel GEMM (wo, w2) whose epilogue writes each bf16 output tile straight into the
- *                 row owner's receive buffer (reduce-scatter by remote stores).
- *   jl_rs_reduce— owner side: wait for all partial tiles, fp32 sum in rank order + residual, RMSNorm, store the
- *                 normalised rows into EVERY rank's a_full (xn_peers, at row xn_row0), publish "rows ready".
- * Replaces the whole-activation all-reduce GSPMD placed after wo / w2 (partition.py:67,70). */
-int jl_ag_gemm(void* const* peer_shards, void* a_full, const void* w, void* out, int M, int N, int K, int mode,
-               int tp, int rank, const int* ready_flags, int ready_epoch, void* counters, int num_sms,
-               void* stream);
-int jl_gemm_rs(const void* x, const void* w, void* const* peer_rs_buf, int M, int N, int K, int tp, int rank,
-               int num_sms, void* stream);
-int jl_rs_reduce(void* x, const void* partials, const void* norm_w, void* const* xn_peers, int xn_row0, int mloc,
-                 int H, int n_src, int tp, int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off,
-                 int gemm_epoch, int ready_epoch, int* ticket, float eps, void* stream);
-
 /* HF Flax warpers + categorical sampling + `_sample` bookkeeping (generation.py:28-41) over the WHOLE vocabulary, exact
  * for any top_k / top_p (no candidate budget), deterministic ties (lower index), identical on every rank: see
  * csrc/sample_full.cu.  logits fp32 [B, ld] with V valid columns; temperature 0 = arg-max; top_k <= 0 or >= V and

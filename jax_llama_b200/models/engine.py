@@ -32,7 +32,6 @@ from .reference import KVCache, ModelOutput, rope_cos_sin
 logger = logging.getLogger(__name__)
 
 Tree = Dict[str, Any]
-MAX_TOPK = 64
 
 
 @dataclass
@@ -74,8 +73,6 @@ class DecodeState:
     attn: torch.Tensor
     mlp: torch.Tensor
     logits: torch.Tensor
-    cand_val: torch.Tensor
-    cand_idx: torch.Tensor
     tok: torch.Tensor
     finished: torch.Tensor
     sequences: torch.Tensor
@@ -544,15 +541,10 @@ class B200Engine:
             qkv=torch.zeros(B, (self.nh + 2 * self.nkv) * self.hd, **bf),
             attn=torch.zeros(B, self.nh * self.hd, **bf), mlp=torch.zeros(B, c.intermediate_size // self.tp, **bf),
             logits=torch.zeros(B, self.v_local, dtype=torch.float32, device=dev),
-            cand_val=torch.zeros(B, MAX_TOPK, dtype=torch.float32, device=dev),
-            cand_idx=torch.zeros(B, MAX_TOPK, **i32), tok=torch.zeros(B, **i32),
+            tok=torch.zeros(B, **i32),
             finished=torch.zeros(B, **i32), sequences=torch.zeros(B, max_len, **i32),
             cur_len=torch.zeros(1, **i32), step=torch.zeros(1, **i32), n_unfinished=torch.zeros(1, **i32),
             splits=splits, scratch=scratch)
-        if self.tp > 1:
-            # packed (values | indices) candidate lists: local and gathered-over-ranks
-            st.cand_local = torch.zeros(2 * B * MAX_TOPK, dtype=torch.int32, device=dev)
-            st.cand_all = torch.zeros(self.tp * 2 * B * MAX_TOPK, dtype=torch.int32, device=dev)
         self._decode_states[key] = st
         return st
 
@@ -576,7 +568,18 @@ class B200Engine:
     def _gather_logits(self, st: DecodeState) -> torch.Tensor:
         """tp > 1: this rank's [B, V/tp] logits shard → every rank's [B, V] buffer over NVLS (multimem.st), then a
         stream-side wait for all ranks' shards.  Returns the local [B, V] view."""
-        self._mega_tp_args()                       # the symmetric buffers exist
+        self._mega_tp_args()                       # the symmetric buffers of the decode kernel exist
+        buf, buf_mc = self._logits_full, self._logits_full_mc
+        if st.B > buf.shape[0]:
+            # batches beyond the decode kernel's 8 rows (per-op path): a larger gathered-logits buffer of its own
+            big = self.__dict__.get("_logits_big")
+            if big is None or big[0].shape[0] < st.B:
+                from ..parallel.symm import SymmetricHeap
+                rows = 1 << (st.B - 1).bit_length()
+                heap = SymmetricHeap(self.tp, self.rank, self.device, rows * self.config.vocab_size * 4,
+                                     group=getattr(self.comm, "group", None))
+                big = self._logits_big = (heap.view(0, (rows, self.config.vocab_size), torch.float32), heap.mc(0), heap)
+            buf, buf_mc = big[0], big[1]
         L = _lib.lib()
         from ..parallel.comm import _L as comm_lib
         comm_lib()
@@ -585,44 +588,20 @@ class B200Engine:
         # correct on every CUDA-graph replay (the counter is advanced at the end of the step, `end_sequence`)
         epoch_rel = cm.call_index + 1
         cm.call_index += 1
-        _lib.check(L.jl_nvls_bcast_f32(st.logits.data_ptr(), self._logits_full_mc, st.B, self.v_local, self.v_local,
+        _lib.check(L.jl_nvls_bcast_f32(st.logits.data_ptr(), buf_mc, st.B, self.v_local, self.v_local,
                                        self.config.vocab_size, self.rank * self.v_local, self.tp, self.rank, cm.flag_ptrs,
                                        self._bcast_flag_off, epoch_rel, cm.seq.data_ptr(), self._bcast_ticket.data_ptr(),
                                        K._stream()), "jl_nvls_bcast_f32")
         _lib.check(L.jl_wait_flags(cm._own_flags + 4 * self._bcast_flag_off, epoch_rel, cm.seq.data_ptr(), self.tp,
                                    self.rank, K._stream()), "jl_wait_flags")
-        return self._logits_full[:st.B]
+        return buf[:st.B]
 
     def _select_and_advance(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int) -> None:
         """st.logits (this rank's vocabulary shard) → token (greedy or temperature/top-k/top-p) → sequences / finished /
-        counters, on device.  Batches up to 8 rows: exact full-vocabulary kernel (at tp > 1 after an NVLS gather of
-        the shards).  Larger batches at tp > 1: per-rank top-k candidates exchanged through peer memory (top_k <= 64)."""
-        do_sample, temperature, top_k, top_p, seed = sampling
-        if self.tp == 1:
-            return self._sample_full(st, cache, sampling, eos, pad, st.logits, wait_mega=False)
-        if st.B <= 8:
-            return self._sample_full(st, cache, sampling, eos, pad, self._gather_logits(st), wait_mega=False)
-        if do_sample and (not top_k or top_k > MAX_TOPK):
-            raise NotImplementedError(f"tensor-parallel sampling at batch > 8 exchanges at most {MAX_TOPK} candidates per "
-                                      f"rank: pass 1 <= top_k <= {MAX_TOPK} (got {top_k})")
-        # vocab-parallel head: each rank extracts its local top-k (value, global index) pairs, the pairs are exchanged
-        # through peer memory, and every rank runs the identical final selection (SURVEY §2.6 O17)
-        B = st.B
-        k = 2 if not do_sample else max(2, int(top_k))
-        n = B * k
-        vals = st.cand_local[:n].view(torch.float32).view(B, k)
-        idx = st.cand_local[n:2 * n].view(B, k)
-        K.topk_candidates(st.logits, k, idx_offset=self.rank * self.v_local, out=(vals, idx))
-        gathered = st.cand_all[:self.tp * 2 * n]
-        self.comm.allgather_small(st.cand_local[:2 * n], gathered)
-        K.sample_candidates(gathered[:n].view(torch.float32).view(B, k), gathered[n:2 * n].view(B, k),
-                            n_lists=self.tp, list_stride=2 * n, top_k=(top_k if do_sample else 1) or k,
-                            top_p=top_p, temperature=temperature if do_sample else 0.0, seed=seed,
-                            step=st.step, out=st.tok)
-        _lib.check(_lib.lib().jl_decode_advance(
-            st.tok.data_ptr(), st.ids.data_ptr(), st.finished.data_ptr(), st.sequences.data_ptr(), st.B,
-            st.max_len, int(eos), int(pad), st.cur_len.data_ptr(), cache.len_dev.data_ptr(), st.step.data_ptr(),
-            st.n_unfinished.data_ptr(), K._stream()), "jl_decode_advance")
+        counters, on device: one launch of the exact full-vocabulary kernel (csrc/sample_full.cu), at tp > 1 after an
+        NVLS gather of the shards so that every rank selects from identical logits."""
+        full = st.logits if self.tp == 1 else self._gather_logits(st)
+        self._sample_full(st, cache, sampling, eos, pad, full, wait_mega=False)
 
     def _decode_step(self, st: DecodeState, cache: DeviceKVCache, sampling: Tuple, eos: int, pad: int) -> None:
         """One token for every row: ids → logits → next ids.  All state on device; capturable."""

@@ -42,16 +42,9 @@ _EXTRA_SIGNATURES = {
     "jl_flag_exchange": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "jl_wait_flags": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "jl_memcpy_d2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
-    "jl_ag_gemm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
-                             C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
-    "jl_gemm_rs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
-                             C.c_void_p]),
     "jl_rs_reduce_mm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                   C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                   C.c_float, C.c_void_p]),
-    "jl_rs_reduce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
-                               C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_float,
-                               C.c_void_p]),
 }
 
 
@@ -235,12 +228,6 @@ class PeerComm:
         for st in self.__dict__.get("_nvls_states", {}).values():
             if st.rel:
                 st.end_forward()
-
-    # ------------------------------------------------------------------ NCCL baseline (measured, not the product)
-    def allreduce_nccl(self, t: torch.Tensor) -> torch.Tensor:
-        if self.tp > 1:
-            dist.all_reduce(t, group=self.group)
-        return t
 
 
 class NvlsPrefill:
