@@ -27,7 +27,7 @@ def main():
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     cfg = LLaMAConfig(vocab_size=1024, hidden_size=1024, intermediate_size=2048, num_hidden_layers=2,
-                      num_attention_heads=8, num_key_value_heads=8 if world > 4 else 4, max_sequence_length=256,
+                      num_attention_heads=8, num_key_value_heads=8 if world > 4 else 4, max_sequence_length=2048,
                       initializer_range=0.05)
     full = tree_to(ref.init_params(cfg, seed=1), dtype=torch.bfloat16)
     full32 = tree_to(full, dtype=torch.float32)
