@@ -132,17 +132,21 @@ def tp_check(args, cfg, eng, dev, rank: int, world: int) -> dict:
     equal = bool(torch.equal(seq_tp, seq_1))
     # teacher-forced: the single-GPU engine scores the TP engine's tokens
     forced = full.forward(seq_tp[:, :-1], last_only=False).logits.float()
+    # A token the TP engine picked may trail the single-GPU arg-max by what two bf16 engines with different reduction
+    # orders differ by on these (nearly flat, random-init) logits: twice the measured logits error, at least 2 %.
+    tol = max(2e-2, 2.0 * err)
     ok_forced = True
     for t in range(P, P + n_new):
         row = forced[:, t - 1]
         chosen = row.gather(-1, seq_tp[:, t:t + 1])[:, 0]
-        ok_forced &= bool(((row.max(-1).values - chosen) <= 2e-2 * row.abs().max()).all())
+        ok_forced &= bool(((row.max(-1).values - chosen) <= tol * row.abs().max()).all())
     gathered = [torch.empty_like(seq_tp) for _ in range(world)]
     dist.all_gather(gathered, seq_tp)
     agree = all(bool(torch.equal(gathered[0], t)) for t in gathered)
     out = {"layers": ccfg.num_hidden_layers, "prompt_len": P, "new_tokens": n_new,
            "logits_max_rel_err": round(err, 5), "greedy_tokens_equal": equal,
-           "greedy_tokens_teacher_forced_ok": ok_forced, "ranks_agree": agree}
+           "greedy_tokens_teacher_forced_ok": ok_forced, "teacher_forced_tolerance_rel": round(tol, 4),
+           "ranks_agree": agree}
     # fused sequence-parallel prefill vs the all-reduce prefill (same engine)
     if P % (128 * world) == 0 and hasattr(eng_tp, "prefill_paths"):
         outs = {}

@@ -95,6 +95,23 @@ def main():
     gc = [torch.empty_like(c1) for _ in range(world)]
     dist.all_gather(gc, c1)
     assert all(torch.equal(gc[0], t) for t in gc), "ranks sampled different tokens with top_k=None"
+    # batch above the whole-step kernel's 8 rows: per-op decode path — tcgen05 GEMMs + in-switch all-reduce kernel inside
+    # the captured step, logits of all ranks gathered over NVLS for the exact sampler
+    ids9 = torch.randint(3, cfg.vocab_size, (9, 17), generator=torch.Generator().manual_seed(12))
+    seq9 = eng.generate(ids9.to(dev), None, max_length=26, eos_token_id=-7, pad_token_id=0)
+    g9 = [torch.empty_like(seq9) for _ in range(world)]
+    dist.all_gather(g9, seq9)
+    assert all(torch.equal(g9[0], t) for t in g9), "ranks generated different tokens at batch 9"
+    logits9 = ref.forward(full32, cfg, seq9.cpu()).logits
+    for t in range(17, 26):
+        row = logits9[:, t - 1]
+        chosen = row.gather(-1, seq9[:, t:t + 1].cpu())[:, 0]
+        assert ((row.max(-1).values - chosen) < 3e-2 * row.abs().max()).all(), ("batch 9", t)
+    s9a = eng.generate(ids9.to(dev), None, max_length=24, do_sample=True, temperature=0.8, top_k=None, top_p=0.9, seed=4,
+                       eos_token_id=-7)
+    s9b = eng.generate(ids9.to(dev), None, max_length=24, do_sample=True, temperature=0.8, top_k=None, top_p=0.9, seed=4,
+                       eos_token_id=-7)
+    assert torch.equal(s9a, s9b)
     # ---- 3. sequence-parallel prefill (all-gather→GEMM, GEMM→reduce-scatter fused over peer memory)
     S = 64 * world if world > 2 else 128
     ids_sp = torch.randint(3, cfg.vocab_size, (2, S), generator=torch.Generator().manual_seed(9))
