@@ -35,6 +35,82 @@ struct FusedAttnParams {
   float scale_log2;
 };
 
+// Shared tail of both kernels: s_o / s_ml hold the (m, l, o) triples of the CTA's NG independent streams.  Folds them,
+// then (splits > 1) the last CTA of this (batch, kv-head) to finish — found with an atomic ticket — merges the
+// partial triples of all splits.  The ticket counter is reset by that CTA.
+template <int NG, int G, int HD>
+__device__ __forceinline__ void df_fold_and_merge(const FusedAttnParams& p, float (*s_o)[G][HD], float (*s_ml)[G][2],
+                                                  int* s_last_p, const int b, const int kvh, const int split) {
+  const int nh = p.nkv * G;
+  int& s_last = *s_last_p;
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < G * HD; idx += (int)blockDim.x) {
+    const int g = idx / HD, d = idx - g * HD;
+    float M = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < NG; ++j) M = fmaxf(M, s_ml[j][g][0]);
+    const float Ms = M == -INFINITY ? 0.f : M;
+    float acc = 0.f, L = 0.f;
+#pragma unroll
+    for (int j = 0; j < NG; ++j) {
+      const float w = exp2f(s_ml[j][g][0] - Ms);
+      acc += w * s_o[j][g][d];
+      L += w * s_ml[j][g][1];
+    }
+    const int h = kvh * G + g;
+    if (p.splits == 1) {
+      p.out[((size_t)b * nh + h) * HD + d] = __float2bfloat16(L > 0.f ? acc / L : 0.f);
+    } else {
+      const size_t pi = ((size_t)b * nh + h) * p.splits + split;
+      p.o_part[pi * HD + d] = acc;
+      if (d == 0) { p.ml_part[pi * 2] = M; p.ml_part[pi * 2 + 1] = L; }
+    }
+  }
+  if (p.splits == 1) return;
+
+  // ---- ticket: the last CTA of this (b, kv head) merges all splits
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int* t = p.tickets + b * p.nkv + kvh;
+    const int prev = atomicAdd(t, 1);
+    s_last = prev == p.splits - 1;
+    if (s_last) *t = 0;                                  // everyone has arrived: safe to re-arm for the next launch
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // stage the (m, l) pairs of all splits in shared memory (one parallel round trip), then every thread
+  // folds its outputs with independent, unrolled loads
+  float* s_m = &s_o[0][0][0];                       // reuse: G*splits floats each, far below NG*G*HD
+  float* s_l = s_m + G * 64;
+  __syncthreads();
+  for (int i = threadIdx.x; i < G * p.splits; i += (int)blockDim.x) {
+    const int g = i / p.splits, sp = i - g * p.splits;
+    const size_t bh = (size_t)b * nh + kvh * G + g;
+    s_m[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2);
+    s_l[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2 + 1);
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < G * HD; idx += (int)blockDim.x) {
+    const int g = idx / HD, d = idx - g * HD;
+    const size_t bh = (size_t)b * nh + kvh * G + g;
+    float M = -INFINITY;
+    for (int sp = 0; sp < p.splits; ++sp) M = fmaxf(M, s_m[g * 64 + sp]);
+    const float Ms = M == -INFINITY ? 0.f : M;
+    float acc = 0.f, L = 0.f;
+    const float* op = p.o_part + bh * p.splits * HD + d;
+#pragma unroll 8
+    for (int sp = 0; sp < p.splits; ++sp) {
+      const float w = exp2f(s_m[g * 64 + sp] - Ms);
+      const float ov = __ldcg(op + (size_t)sp * HD);
+      acc += w > 0.f ? w * ov : 0.f;
+      L += w * s_l[g * 64 + sp];
+    }
+    p.out[bh * HD + d] = __float2bfloat16(L > 0.f ? acc / L : 0.f);
+  }
+}
+
 template <int G, int HD>
 __global__ void __launch_bounds__(DF_WARPS * 32) decode_attn_fused_kernel(const FusedAttnParams p) {
   constexpr int LPK = HD / 8;
@@ -222,77 +298,255 @@ __global__ void __launch_bounds__(DF_WARPS * 32) decode_attn_fused_kernel(const 
     for (int e = 0; e < 8; ++e) s_o[gid][g][lig * 8 + e] = o[g][e];
     if (lig == 0) { s_ml[gid][g][0] = m[g]; s_ml[gid][g][1] = l[g]; }
   }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < G * HD; idx += DF_WARPS * 32) {
-    const int g = idx / HD, d = idx - g * HD;
-    float M = -INFINITY;
-#pragma unroll
-    for (int j = 0; j < NG; ++j) M = fmaxf(M, s_ml[j][g][0]);
-    const float Ms = M == -INFINITY ? 0.f : M;
-    float acc = 0.f, L = 0.f;
-#pragma unroll
-    for (int j = 0; j < NG; ++j) {
-      const float w = exp2f(s_ml[j][g][0] - Ms);
-      acc += w * s_o[j][g][d];
-      L += w * s_ml[j][g][1];
-    }
-    const int h = kvh * G + g;
-    if (p.splits == 1) {
-      p.out[((size_t)b * nh + h) * HD + d] = __float2bfloat16(L > 0.f ? acc / L : 0.f);
-    } else {
-      const size_t pi = ((size_t)b * nh + h) * p.splits + split;
-      p.o_part[pi * HD + d] = acc;
-      if (d == 0) { p.ml_part[pi * 2] = M; p.ml_part[pi * 2 + 1] = L; }
-    }
-  }
-  if (p.splits == 1) return;
+  df_fold_and_merge<NG, G, HD>(p, s_o, s_ml, &s_last, b, kvh, split);
+}
 
-  // ---- ticket: the last CTA of this (b, kv head) merges all splits
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int* t = p.tickets + b * p.nkv + kvh;
-    const int prev = atomicAdd(t, 1);
-    s_last = prev == p.splits - 1;
-    if (s_last) *t = 0;                                  // everyone has arrived: safe to re-arm for the next launch
+// =====================================================================================================================
+// Tensor-core variant for batched decode (batch x kv-heads large enough to fill the GPU; head_dim 128).
+//
+// Why: at batch 32 / 2k context the kernel above moves 268 MB per layer in 133 µs (2 TB/s) — ncu shows ~1 issued
+// instruction per cycle and no memory stall: the bf16 → fp32 unpacking and the G x 256 FMAs per key are the limit,
+// not HBM.  Here both products go through mma.sync.m16n8k16 (bf16 in, fp32 accumulate) with the G query heads of
+// the kv head as rows 0..G-1 of the 16-row operand, and K / V travel global memory → registers → MMA with no
+// shared memory, no ldmatrix and no barrier in the loop; every warp runs an independent online softmax over its
+// own 32-key blocks.
+//   S = Q Kᵀ: the contraction index d may be permuted freely as long as Q and K use the same permutation, so thread
+//     (g = lane / 4, t = lane % 4) loads the 16-byte chunks t, t + 4, t + 8, t + 12 of K[key g] (four LDG.128, each
+//     one 64 contiguous bytes per quad = whole sectors) and k-step s = 2u + v uses words (2v, 2v+1) of chunk u as
+//     (b0, b1); Q is held the same way.  Blocks two iterations ahead are requested into L2 with
+//     cp.async.bulk.prefetch (no registers), so the register loads mostly hit L2.
+//   O = P V: the C fragment of S (row g, keys 2t, 2t+1) is already the A fragment of P.  The B operand needs two
+//     KEYS of one d packed per register: thread (g, t) loads V[key][8 g .. 8 g + 7] and V[key][64 + 8 g ..] for its
+//     four keys (2t, 2t+1, 2t+8, 2t+9) and pairs them with PRMT; output tile (h, e) column n is d = 64 h + 8 n + e.
+// The new token is folded in by the same code as a block whose only valid key is slot 0.
+constexpr int DM_WARPS = 4;
+
+__device__ __forceinline__ void mma_16816(float (&d)[4], uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+__device__ __forceinline__ uint32_t u4w(const uint4& v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : (i == 2 ? v.z : v.w)); }
+
+// rotate the four (re, im) pairs of one 16-byte chunk; pair j uses cos/sin entry j of cs / sn
+__device__ __forceinline__ uint4 rope_chunk(const uint4 a, const float4 cs, const float4 sn) {
+  const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+  const float c[4] = {cs.x, cs.y, cs.z, cs.w}, s[4] = {sn.x, sn.y, sn.z, sn.w};
+  uint32_t r[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float re = bf16_lo(w[j]), im = bf16_hi(w[j]);
+    r[j] = pack_bf16(re * c[j] - im * s[j], re * s[j] + im * c[j]);
   }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  // stage the (m, l) pairs of all splits in shared memory (one parallel round trip), then every thread
-  // folds its outputs with independent, unrolled loads
-  float* s_m = &s_o[0][0][0];                       // reuse: G*splits floats each, far below NG*G*HD
-  float* s_l = s_m + G * 64;
-  __syncthreads();
-  for (int i = threadIdx.x; i < G * p.splits; i += DF_WARPS * 32) {
-    const int g = i / p.splits, sp = i - g * p.splits;
-    const size_t bh = (size_t)b * nh + kvh * G + g;
-    s_m[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2);
-    s_l[g * 64 + sp] = __ldcg(p.ml_part + (bh * p.splits + sp) * 2 + 1);
-  }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < G * HD; idx += DF_WARPS * 32) {
-    const int g = idx / HD, d = idx - g * HD;
-    const size_t bh = (size_t)b * nh + kvh * G + g;
-    float M = -INFINITY;
-    for (int sp = 0; sp < p.splits; ++sp) M = fmaxf(M, s_m[g * 64 + sp]);
-    const float Ms = M == -INFINITY ? 0.f : M;
-    float acc = 0.f, L = 0.f;
-    const float* op = p.o_part + bh * p.splits * HD + d;
-#pragma unroll 8
-    for (int sp = 0; sp < p.splits; ++sp) {
-      const float w = exp2f(s_m[g * 64 + sp] - Ms);
-      const float ov = __ldcg(op + (size_t)sp * HD);
-      acc += w > 0.f ? w * ov : 0.f;
-      L += w * s_l[g * 64 + sp];
+  return make_uint4(r[0], r[1], r[2], r[3]);
+}
+
+template <int G, int KPI>
+__global__ void __launch_bounds__(DM_WARPS * 32, KPI == 32 ? 2 : 3) decode_attn_mma_kernel(const FusedAttnParams p) {
+  constexpr int HD = 128;
+  constexpr int NT = KPI / 8;                  // 8-key S tiles per block
+  constexpr int NB = KPI / 16;                 // 16-key P·V steps per block
+  __shared__ float s_o[DM_WARPS][G][HD];
+  __shared__ float s_ml[DM_WARPS][G][2];
+  __shared__ int s_last;
+
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+  const int nh = p.nkv * G;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+
+  int len = *p.cache_len_ptr;
+  len = len > p.T ? p.T : len;
+  const int first = p.pad_left ? p.pad_left[b] : 0;
+  const int valid = len - first > 0 ? len - first : 0;
+  int pos = len - first;
+  pos = pos < 0 ? 0 : (pos >= p.max_pos ? p.max_pos - 1 : pos);
+  int chunk = (valid + p.splits - 1) / p.splits;
+  chunk = ((chunk + DM_WARPS * KPI - 1) / (DM_WARPS * KPI)) * (DM_WARPS * KPI);
+  const int lo = first + split * chunk;
+  const int hi = lo + chunk < len ? lo + chunk : len;
+
+  // K and V rows of a block are contiguous (KPI x 256 bytes each): one lane asks for them to be brought into L2
+  const size_t head_off = ((size_t)b * p.nkv + kvh) * (size_t)p.T * HD;
+  auto prefetch_block = [&](const int base) {
+    if (lane == 0 && base < hi) {
+      const int n = hi - base < KPI ? hi - base : KPI;
+      const size_t off = head_off + (size_t)base * HD;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.kc + off), "r"(n * HD * 2) : "memory");
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.vc + off), "r"(n * HD * 2) : "memory");
     }
-    p.out[bh * HD + d] = __float2bfloat16(L > 0.f ? acc / L : 0.f);
+  };
+  prefetch_block(lo + warp * KPI);                       // overlaps the position → cos/sin → q dependency chain below
+  prefetch_block(lo + warp * KPI + DM_WARPS * KPI);
+
+  const __nv_bfloat16* row = p.qkv + (size_t)b * (nh + 2 * p.nkv) * HD;
+  const float4* cos4 = reinterpret_cast<const float4*>(p.cos_t) + (size_t)pos * (HD / 8) + t;   // chunk t + 4u: entry 4u
+  const float4* sin4 = reinterpret_cast<const float4*>(p.sin_t) + (size_t)pos * (HD / 8) + t;
+
+  // Q of head kvh·G + g, rotated and rounded to bf16 (as the unfused path does): qa[s] = (a0, a2) of k-step s
+  uint32_t qa[8][2];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    uint4 r = make_uint4(0, 0, 0, 0);
+    if (g < G)
+      r = rope_chunk(*reinterpret_cast<const uint4*>(row + (size_t)(kvh * G + g) * HD + 8 * t + 32 * u),
+                     __ldg(cos4 + 4 * u), __ldg(sin4 + 4 * u));
+    qa[2 * u][0] = r.x; qa[2 * u][1] = r.y; qa[2 * u + 1][0] = r.z; qa[2 * u + 1][1] = r.w;
   }
+
+  float m = -INFINITY, l = 0.f;                // row g: m is quad-uniform, l is this thread's share of the sum
+  float o[2][8][4];
+#pragma unroll
+  for (int h = 0; h < 2; ++h)
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) o[h][e][i] = 0.f;
+
+  const __nv_bfloat16* kbase = p.kc + head_off + 8 * t;
+  const __nv_bfloat16* vbase = p.vc + head_off + 8 * g;
+
+  // one online-softmax update with a KPI-key block whose K / V fragments are in registers; keys >= limit are masked
+  auto process = [&](const uint4 (&kr)[NT][4], const uint4 (&vr)[NB][4][2], const int base, const int limit) {
+    float c[NT][4];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      c[j][0] = c[j][1] = c[j][2] = c[j][3] = 0.f;
+#pragma unroll
+      for (int s = 0; s < 8; ++s)
+        mma_16816(c[j], qa[s][0], qa[s][1], u4w(kr[j][s >> 1], (s & 1) * 2), u4w(kr[j][s >> 1], (s & 1) * 2 + 1));
+    }
+    float mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      const int key = base + 8 * j + 2 * t;
+      c[j][0] = key < limit ? c[j][0] * p.scale_log2 : -INFINITY;
+      c[j][1] = key + 1 < limit ? c[j][1] * p.scale_log2 : -INFINITY;
+      mx = fmaxf(mx, fmaxf(c[j][0], c[j][1]));
+    }
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    const float m_new = fmaxf(m, mx);
+    const float m_safe = m_new == -INFINITY ? 0.f : m_new;
+    const float corr = exp2f(m - m_safe);
+    m = m_new;
+    float psum = 0.f;
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      c[j][0] = exp2f(c[j][0] - m_safe);
+      c[j][1] = exp2f(c[j][1] - m_safe);
+      psum += c[j][0] + c[j][1];
+    }
+    l = l * corr + psum;
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { o[h][e][0] *= corr; o[h][e][1] *= corr; }
+#pragma unroll
+    for (int kb = 0; kb < NB; ++kb) {
+      const uint32_t a0 = pack_bf16(c[2 * kb][0], c[2 * kb][1]), a2 = pack_bf16(c[2 * kb + 1][0], c[2 * kb + 1][1]);
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const uint32_t sel = (e & 1) ? 0x7632u : 0x5410u;
+          const uint32_t b0 = prmt(u4w(vr[kb][0][h], e >> 1), u4w(vr[kb][1][h], e >> 1), sel);
+          const uint32_t b1 = prmt(u4w(vr[kb][2][h], e >> 1), u4w(vr[kb][3][h], e >> 1), sel);
+          mma_16816(o[h][e], a0, a2, b0, b1);
+        }
+    }
+  };
+
+  for (int base = lo + warp * KPI; base < hi; base += DM_WARPS * KPI) {
+    prefetch_block(base + 2 * DM_WARPS * KPI);
+    uint4 kr[NT][4], vr[NB][4][2];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      const int key = base + 8 * j + g;
+      const __nv_bfloat16* src = kbase + (size_t)key * HD;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) kr[j][u] = key < hi ? ldg_stream(src + 32 * u) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int kb = 0; kb < NB; ++kb)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int key = base + 16 * kb + 2 * t + (q & 1) + (q >> 1) * 8;
+        const __nv_bfloat16* src = vbase + (size_t)key * HD;
+        vr[kb][q][0] = key < hi ? ldg_stream(src) : make_uint4(0, 0, 0, 0);
+        vr[kb][q][1] = key < hi ? ldg_stream(src + 64) : make_uint4(0, 0, 0, 0);
+      }
+    process(kr, vr, base, hi);
+  }
+
+  // ---- the new token (split 0, warp 0): rotate k, append k and v to the cache, fold it in as key 0 of a block
+  if (split == 0 && warp == 0) {
+    uint4 kr[NT][4], vr[NB][4][2];
+#pragma unroll
+    for (int j = 0; j < NT; ++j)
+#pragma unroll
+      for (int u = 0; u < 4; ++u) kr[j][u] = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int kb = 0; kb < NB; ++kb)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) vr[kb][q][0] = vr[kb][q][1] = make_uint4(0, 0, 0, 0);
+    if (g == 0) {                                          // K fragment of key 0 lives in the quad g == 0
+      const __nv_bfloat16* src = row + (size_t)(nh + kvh) * HD + 8 * t;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        kr[0][u] = rope_chunk(*reinterpret_cast<const uint4*>(src + 32 * u), __ldg(cos4 + 4 * u), __ldg(sin4 + 4 * u));
+        if (len < p.T) *reinterpret_cast<uint4*>(p.kc + head_off + (size_t)len * HD + 8 * t + 32 * u) = kr[0][u];
+      }
+    }
+    if (t == 0) {                                          // V fragments of key 0 = key slot 2t, t == 0
+      const __nv_bfloat16* src = row + (size_t)(nh + p.nkv + kvh) * HD + 8 * g;
+      vr[0][0][0] = *reinterpret_cast<const uint4*>(src);
+      vr[0][0][1] = *reinterpret_cast<const uint4*>(src + 64);
+      if (len < p.T) {
+        *reinterpret_cast<uint4*>(p.vc + head_off + (size_t)len * HD + 8 * g) = vr[0][0][0];
+        *reinterpret_cast<uint4*>(p.vc + head_off + (size_t)len * HD + 64 + 8 * g) = vr[0][0][1];
+      }
+    }
+    process(kr, vr, 0, 1);
+  }
+
+  // ---- this warp's triple → shared memory; tile (h, e) holds columns d = 64 h + 8 n + e, n = 2t (c0), 2t + 1 (c1)
+  l += __shfl_xor_sync(0xffffffffu, l, 1);
+  l += __shfl_xor_sync(0xffffffffu, l, 2);
+  if (g < G) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        s_o[warp][g][64 * h + 16 * t + e] = o[h][e][0];
+        s_o[warp][g][64 * h + 16 * t + 8 + e] = o[h][e][1];
+      }
+    if (t == 0) { s_ml[warp][g][0] = m; s_ml[warp][g][1] = l; }
+  }
+  df_fold_and_merge<DM_WARPS, G, HD>(p, s_o, s_ml, &s_last, b, kvh, split);
 }
 
 }  // namespace jl
 
 using namespace jl;
+
+static int g_attn_variant = 0;      // 0 = by shape, 1 = SIMT kernel, 2 = tensor-core kernel (head_dim 128 only)
+
+// Pins the kernel behind jl_decode_attn_fused (tests and A/B measurements); 0 restores the shape-based choice.
+extern "C" JL_API int jl_decode_attn_fused_set_variant(int variant) {
+  JL_CHECK_ARG(variant >= 0 && variant <= 2, "jl_decode_attn_fused_set_variant: %d outside 0..2", variant);
+  g_attn_variant = variant;
+  return JL_OK;
+}
 
 extern "C" JL_API size_t jl_decode_attn_fused_scratch_bytes(int B, int nh, int nkv, int hd, int splits) {
   const size_t parts = splits <= 1 ? 0 : (size_t)B * nh * splits * (hd + 2) * sizeof(float);
@@ -328,6 +582,28 @@ extern "C" JL_API int jl_decode_attn_fused(const void* qkv, void* k_cache, void*
   p.scale_log2 = scale * 1.4426950408889634f;
   auto s = (cudaStream_t)stream;
   cudaError_t e = cudaErrorInvalidValue;
+  // enough (batch, kv-head) pairs to fill the GPU: the tensor-core kernel (see its header); otherwise the SIMT kernel
+  // with many short splits, which has the lower latency at batch 1
+  const bool use_mma = hd == 128 && (g_attn_variant == 2 || (g_attn_variant == 0 && B * nkv >= 64));
+  if (use_mma) {
+    // one resident wave (2 CTAs per SM) of long CTAs: every CTA pays the position → q → first-block latency chain and
+    // the fold / ticket / merge tail once, and with 2.6 waves of short CTAs that fixed cost was ~25 of 72 us at
+    // batch 32.  The scratch layout (ticket offset) still follows the caller's `splits`.
+    static int sms = 0;
+    if (sms == 0) {
+      int dev = 0;
+      if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+        sms = 148;
+    }
+    int ms = (2 * sms + B * nkv - 1) / (B * nkv);
+    p.splits = ms < splits ? ms : splits;
+    splits = p.splits;
+#define JL_DM(G_) \
+    if (G == G_) e = launch_pdl(decode_attn_mma_kernel<G_, 32>, dim3(splits, nkv, B), dim3(DM_WARPS * 32), 0, s, p);
+    JL_DM(1) else JL_DM(2) else JL_DM(4) else JL_DM(8)
+#undef JL_DM
+    if (e != cudaErrorInvalidValue) { JL_CUDA(e); return JL_OK; }
+  }
 #define JL_DF(G_, HD_) \
   if (G == G_ && hd == HD_) e = launch_pdl(decode_attn_fused_kernel<G_, HD_>, dim3(splits, nkv, B), dim3(DF_WARPS * 32), 0, s, p);
   JL_DF(1, 128) else JL_DF(2, 128) else JL_DF(4, 128) else JL_DF(8, 128)

@@ -42,7 +42,8 @@ struct GemmParams {
   // split order — deterministic — and runs the epilogue.  ksplit == 1: off.
   int ksplit;
   float* ws;
-  int* tickets;                      // [tiles], zero between launches (the finishing item resets its ticket)
+  int* tickets;                      // [2][ticket_half]: arrivals, completions per tile; zero between launches
+  int ticket_half;
 };
 
 __host__ __device__ constexpr int tmem_cols_for(int bn) {
@@ -50,7 +51,7 @@ __host__ __device__ constexpr int tmem_cols_for(int bn) {
 }
 
 template <int BN, int EPI, bool SWAP, bool OUT_F32>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, SWAP ? 2 : 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2;
@@ -75,8 +76,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   const int num_tiles = p.a_blocks * p.b_blocks;
   const int ksplit = SWAP ? p.ksplit : 1;
   const int num_work = num_tiles * ksplit;              // (tile, K split) items; split-major so neighbours differ in tile
-  __shared__ int s_last_split;
 
+  // swap-AB (decode): the next kernel of the chain may start right away — it waits for this grid itself before it
+  // touches anything this grid writes — so that ITS weight prefetch (below) overlaps our epilogue
+  if constexpr (SWAP) pdl_launch_dependents();
   if (warp == 0 && lane == 0) {
     tc::prefetch_tensormap(&tmap_a);
     tc::prefetch_tensormap(&tmap_b);
@@ -92,23 +95,45 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   tc::fence_after_sync();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  pdl_wait();                 // everything above overlapped the previous kernel's tail
-  pdl_launch_dependents();
+  if constexpr (!SWAP) {
+    pdl_wait();               // everything above overlapped the previous kernel's tail
+    pdl_launch_dependents();
+  }
 
   if (warp == 0) {
     // ===================================================== TMA producer
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
+      int pre = 0;            // leading k-blocks of the first item whose weight tile is already on its way
+      if constexpr (SWAP) {
+        // the weights do not depend on the previous kernel: fill the ring with A tiles NOW — they stream from HBM
+        // while that kernel runs its tail — and only then wait for it; the activation tiles follow after the wait
+        if ((int)blockIdx.x < num_work) {
+          const int t = blockIdx.x % num_tiles, split = blockIdx.x / num_tiles;
+          const int kb0 = split * num_kb / ksplit, kb1 = (split + 1) * num_kb / ksplit;
+          const int a_blk = t % p.a_blocks;
+          pre = kb1 - kb0 < stages ? kb1 - kb0 : stages;
+          for (int i = 0; i < pre; ++i) {
+            tc::mbar_expect_tx(full_bar(i), A_BYTES + B_BYTES);
+            tc::tma_load_2d(smem_base + i * STAGE_BYTES, &tmap_a, full_bar(i), (kb0 + i) * GEMM_BK, a_blk * GEMM_BM, p.hint_a);
+          }
+        }
+        pdl_wait();
+      }
       for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
         const int t = wi % num_tiles, split = wi / num_tiles;
         const int kb0 = split * num_kb / ksplit, kb1 = (split + 1) * num_kb / ksplit;
         const int b_blk = t / p.a_blocks;
         const int a_blk = t % p.a_blocks;
         for (int kb = kb0; kb < kb1; ++kb) {
-          tc::mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
-          tc::mbar_expect_tx(full_bar(stage), A_BYTES + B_BYTES);
-          tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM, p.hint_a);
+          if (pre > 0) {
+            --pre;
+          } else {
+            tc::mbar_wait(empty_bar(stage), phase ^ 1);
+            tc::mbar_expect_tx(full_bar(stage), A_BYTES + B_BYTES);
+            tc::tma_load_2d(sa, &tmap_a, full_bar(stage), kb * GEMM_BK, a_blk * GEMM_BM, p.hint_a);
+          }
           tc::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * GEMM_BK, b_blk * BN, p.hint_b);
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
@@ -143,6 +168,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     // ===================================================== epilogue: TMEM → registers → global
     const int quarter = warp & 3;                           // TMEM lanes [32·quarter, 32·quarter+32)
     int it = 0;
+    if constexpr (SWAP) pdl_wait();                         // residual, output, split-K scratch: after the previous kernel
     for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x, ++it) {
       const int t = wi % num_tiles, split = wi / num_tiles;
       const int b_blk = t / p.a_blocks;
@@ -267,18 +293,31 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       if (lane == 0) tc::mbar_arrive(tempty_bar(as));
       if constexpr (SWAP) {
         if (ksplit > 1) {
-          // ---- split-K finish: the last of this tile's K splits to get here sums all partials and emits
+          // ---- split-K finish, shared by the K splits of the tile: all of them run at the same time (one work item
+          // per CTA, see launch_gemm), so each publishes its partial, waits until the tile's ticket shows all ksplit
+          // arrivals and then sums + emits ITS share of the tile's tokens (a single L2 round trip of ksplit x 4-8
+          // loads per thread; when the last split to arrive did the whole tile alone that was 8 dependent round
+          // trips at batch 32: 10 us of a 25 us GEMM).  Sums run in split order: deterministic.
           __threadfence();
           asm volatile("bar.sync 1, 128;" ::: "memory");                // the four epilogue warps
-          if (threadIdx.x == 128) s_last_split = atomicAdd(p.tickets + t, 1) == ksplit - 1;
+          if (threadIdx.x == 128) {
+            atomicAdd(p.tickets + t, 1);
+            unsigned spins = 0;
+            while (ld_acquire_gpu_u32(reinterpret_cast<const unsigned int*>(p.tickets + t)) < (unsigned)ksplit) {
+              if (++spins > (1u << 26)) {
+                printf("jllama_b200: gemm split-K timed out waiting for tile %d (block %d)\n", t, (int)blockIdx.x);
+                __trap();
+              }
+            }
+          }
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (s_last_split) {
-            __threadfence();
-            // 4 tokens x up to 16 splits of independent L2 loads in flight per thread (a token-at-a-time loop
-            // paid one L2 round trip per token: 45 us for 64 tokens)
+          __threadfence();
+          {
+            const int per = ((BN + ksplit - 1) / ksplit + 3) & ~3;      // tokens per split, whole groups of 4
+            const int j_lo = split * per, j_hi = j_lo + per < BN ? j_lo + per : BN;
             const size_t split_stride = (size_t)p.Rb * p.Ra;
 #pragma unroll 1
-            for (int j0 = 0; j0 < BN; j0 += 4) {
+            for (int j0 = j_lo; j0 < j_hi; j0 += 4) {
               float x[4] = {0.f, 0.f, 0.f, 0.f};
               const float* src = p.ws + (size_t)(b_blk * BN + j0) * p.Ra + ra;
 #pragma unroll
@@ -292,9 +331,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 #pragma unroll
               for (int u = 0; u < 4; ++u) swap_emit(b_blk * BN + j0 + u, x[u]);
             }
-            if (threadIdx.x == 128) p.tickets[t] = 0;
           }
-          asm volatile("bar.sync 1, 128;" ::: "memory");                // s_last_split is reused by the next item
+          // the last split to finish re-arms the tile's two counters for the next launch
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (threadIdx.x == 128) {
+            int* done = p.tickets + p.ticket_half + t;
+            if (atomicAdd(done, 1) == ksplit - 1) { *done = 0; p.tickets[t] = 0; }
+          }
         }
       }
     }
@@ -326,31 +369,40 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
   constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2;
   constexpr uint32_t B_BYTES = BN * GEMM_BK * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + (B_BYTES < 1024 ? 1024 : B_BYTES);
-  int stages = (int)((200 * 1024) / STAGE_BYTES);
-  if (stages > 10) stages = 10;
   const int num_kb = (K + GEMM_BK - 1) / GEMM_BK;
-  if (stages > num_kb * 2) stages = num_kb * 2 < 2 ? 2 : num_kb * 2;
-  p.stages = stages;
   p.a_blocks = (Ra + GEMM_BM - 1) / GEMM_BM;
   p.b_blocks = (Rb + BN - 1) / BN;
-  const size_t smem = (size_t)stages * STAGE_BYTES + 8 * (2 * stages + 4) + 16 + 1024;
-  auto kern = gemm_kernel<BN, EPI, SWAP, OUT_F32>;
-  JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = p.a_blocks * p.b_blocks;
   p.ksplit = 1;
   if constexpr (SWAP) {
-    // few weight-row tiles (N <= ~9k at decode batch sizes): cut K so that (nearly) every SM streams weights
+    // few weight-row tiles (N <= ~9k at decode batch sizes): cut K so that (nearly) every SM streams weights.  Every
+    // (tile, split) item gets its own CTA — the shared finish in the kernel relies on all splits running at once.
     const SplitKWorkspace wsp = splitk_workspace();
-    // measured (8B decode, ms/step, split vs not): batch 16 5.10 vs 6.20, batch 32 6.44 vs 7.09, batch 64 9.29 vs 8.72
-    if (wsp.ws != nullptr && Rb <= 32 && grid * 2 <= num_sms && grid <= wsp.n_tickets) {
+    if (wsp.ws != nullptr && Rb <= 64 && grid * 2 <= num_sms && grid <= wsp.n_tickets / 2) {
       int ks = num_sms / grid;
       if (ks > num_kb / 4) ks = num_kb / 4;               // at least 4 k-blocks (256 columns) per item
       if (ks > 16) ks = 16;
       while (ks > 1 && (size_t)ks * Rb * Ra * sizeof(float) > wsp.ws_bytes) --ks;
-      if (ks > 1) { p.ksplit = ks; p.ws = wsp.ws; p.tickets = wsp.tickets; grid *= ks; }
+      if (ks > 1) {
+        p.ksplit = ks; p.ws = wsp.ws; p.tickets = wsp.tickets; p.ticket_half = wsp.n_tickets / 2;
+        grid *= ks;
+      }
     }
   }
   if (grid > num_sms) grid = num_sms;
+  // Ring depth.  Token-major GEMMs and long weight streams (> 1.25 MB per CTA: w13, lm_head) take the whole shared
+  // memory (10 stages).  Short decode GEMMs (wqkv, wo, w2 at batch 9..128) stay under half of it, so that the CTAs of
+  // the NEXT kernel of the chain fit on the same SM and their weight prefetch — issued before they wait for this
+  // grid — runs under our epilogue and split-K finish; those prologue / tail latencies were most of a 25 us GEMM.
+  int budget = 200 * 1024;
+  if (SWAP && (size_t)Ra * K * 2 / grid <= (size_t)1280 * 1024) budget = 100 * 1024;
+  int stages = (int)(budget / STAGE_BYTES);
+  if (stages > 10) stages = 10;
+  if (stages > num_kb * 2) stages = num_kb * 2 < 2 ? 2 : num_kb * 2;
+  p.stages = stages;
+  const size_t smem = (size_t)stages * STAGE_BYTES + 8 * (2 * stages + 4) + 16 + 1024;
+  auto kern = gemm_kernel<BN, EPI, SWAP, OUT_F32>;
+  JL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   JL_CUDA(launch_pdl(kern, dim3(grid), dim3(GEMM_THREADS), smem, stream, ta, tb, p));
   return JL_OK;
 }

@@ -89,6 +89,11 @@ int jl_decode_attn_fused_splits(int B, int nkv, int max_len, int num_sms);
 int jl_decode_attn_fused(const void* qkv, void* k_cache, void* v_cache, const float* cos_t, const float* sin_t,
                          const int* cache_len_ptr, const int* pad_left, void* scratch, void* out, int B, int nh,
                          int nkv, int hd, int T, int max_pos, float scale, int splits, void* stream);
+/* Two kernels stand behind jl_decode_attn_fused: a SIMT one with many short splits (lowest latency at batch 1) and,
+ * for head_dim 128 with batch * nkv >= 64, a tensor-core one (mma.sync, K/V from global memory straight into MMA
+ * fragments) that streams the cache ~2.5x faster at batch 16-64.  variant: 0 = choose by shape, 1 = SIMT, 2 = tensor
+ * core (where it applies).  Process-wide; meant for tests and A/B measurements. */
+int jl_decode_attn_fused_set_variant(int variant);
 
 /* No counterpart in the reference: an allocation-free form of jl_decode_attn for callers that cannot get
  * device memory themselves (HBM fully owned by another runtime's arena, hosts that ban cudaMalloc/cudaFree

@@ -35,6 +35,7 @@ _SIGNATURES = {
     "jl_decode_attn_fused_scratch_bytes": (sz, [i32, i32, i32, i32, i32]),
     "jl_decode_attn_fused_splits": (i32, [i32, i32, i32, i32]),
     "jl_decode_attn_fused": (i32, [vp, vp, vp, fp, fp, ip, ip, vp, vp, i32, i32, i32, i32, i32, i32, f32, i32, vp]),
+    "jl_decode_attn_fused_set_variant": (i32, [i32]),
     "jl_decode_mega_scratch_bytes": (sz, [i32, i32, i32, i32, i32, i32]),
     "jl_decode_mega_cand_offset": (sz, [i32, i32, i32, i32, i32, i32]),
     "jl_decode_mega_peer_bytes": (sz, [i32, i32, i32, i32, vp]),

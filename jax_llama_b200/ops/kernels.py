@@ -267,6 +267,12 @@ def decode_attn_fused_plan(B: int, nh: int, nkv: int, hd: int, max_len: int, dev
     return splits, torch.zeros((nbytes + 3) // 4, dtype=torch.int32, device=device)
 
 
+def set_decode_attn_variant(variant: int) -> None:
+    """Pins the kernel behind `decode_attn_fused`: 0 = by shape (default), 1 = SIMT, 2 = tensor-core (head_dim 128).
+    Process-wide; for tests and A/B timing."""
+    _lib.check(_lib.lib().jl_decode_attn_fused_set_variant(int(variant)), "jl_decode_attn_fused_set_variant")
+
+
 def decode_attn_fused(qkv: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, cos: torch.Tensor,
                       sin: torch.Tensor, cache_len: torch.Tensor, pad_left: Optional[torch.Tensor], nh: int,
                       nkv: int, hd: int, splits: int = 1, scratch: Optional[torch.Tensor] = None,

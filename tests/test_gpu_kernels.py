@@ -307,10 +307,19 @@ def test_flash_prefill_growing_and_shrinking_scores(ramp):
     assert ((got.float().cpu() - want).abs().max() / (want.abs().max() + 1e-6)).item() < 2e-2
 
 
-@pytest.mark.parametrize("nh,nkv,hd", [(8, 2, 128), (8, 8, 128), (8, 1, 128), (4, 2, 64)])
+@pytest.fixture
+def attn_variant(request):
+    K.set_decode_attn_variant(request.param)
+    yield request.param
+    K.set_decode_attn_variant(0)
+
+
+@pytest.mark.parametrize("attn_variant", [1, 2], indirect=True, ids=["simt", "mma"])
+@pytest.mark.parametrize("nh,nkv,hd", [(8, 2, 128), (8, 8, 128), (8, 1, 128), (4, 2, 64), (4, 2, 128)])
 @pytest.mark.parametrize("B,filled,max_len", [(1, 0, 64), (2, 77, 256), (1, 2048, 2304), (3, 700, 4096)])
-def test_decode_attention_fused(nh, nkv, hd, B, filled, max_len):
-    """RoPE + append + attention + merge in one launch == the three separate CPU statements."""
+def test_decode_attention_fused(nh, nkv, hd, B, filled, max_len, attn_variant):
+    """RoPE + append + attention + merge in one launch == the three separate CPU statements; both kernels behind the
+    entry point (SIMT; tensor-core for head_dim 128 — the 64-wide case then stays on the SIMT kernel)."""
     T = max_len
     qkv = rnd(B, (nh + 2 * nkv) * hd, seed=30)
     kc, vc = rnd(B, nkv, T, hd, seed=31), rnd(B, nkv, T, hd, seed=32)
@@ -327,6 +336,32 @@ def test_decode_attention_fused(nh, nkv, hd, B, filled, max_len):
         assert rel_err(got, want) < 1.5e-2
     assert rel_err(gk[:, :, filled], kc_ref[:, :, filled]) < 1e-2 and rel_err(gv[:, :, filled], vc_ref[:, :, filled]) < 1e-2
     assert torch.equal(gk[:, :, :filled].cpu(), kc[:, :, :filled]) and (scratch[-B * nkv:] == 0).all()
+
+
+@pytest.mark.parametrize("nh,nkv", [(32, 8), (8, 1), (8, 8)])
+def test_decode_attention_fused_batched_shape_picks_tensor_core_kernel(nh, nkv):
+    """Batch 16-64 shapes (batch x kv heads >= 64 → the tensor-core kernel by default): rows with different left
+    padding, a context that is not a multiple of the 128-key chunk, per-head / per-column error bounds."""
+    B, hd, filled, T = 64 // nkv + 8, 128, 1111, 1280
+    qkv = rnd(B, (nh + 2 * nkv) * hd, seed=33)
+    kc, vc = rnd(B, nkv, T, hd, seed=34), rnd(B, nkv, T, hd, seed=35)
+    cos, sin = ref.rope_cos_sin(hd, 2 * T, 500000.0)
+    pad = (torch.arange(B, dtype=torch.int32) * 37) % 600
+    clen = torch.tensor([filled], dtype=torch.int32)
+    want = K.decode_attn_fused(qkv.float(), kc.float(), vc.float(), cos, sin, clen, pad, nh, nkv, hd)
+    splits, scratch = K.decode_attn_fused_plan(B, nh, nkv, hd, T, torch.device(DEV))
+    outs = []
+    for variant in (0, 1):
+        K.set_decode_attn_variant(variant)
+        gk, gv = kc.to(DEV), vc.to(DEV)
+        got = K.decode_attn_fused(qkv.to(DEV), gk, gv, cos.to(DEV), sin.to(DEV), clen.to(DEV), pad.to(DEV), nh, nkv,
+                                  hd, splits, scratch)
+        K.set_decode_attn_variant(0)
+        assert_close(got.view(B * nh, hd), want.view(B * nh, hd), 1.5e-2)
+        outs.append((got.float().cpu(), gk[:, :, filled].cpu(), gv[:, :, filled].cpu()))
+    # the two kernels write the same cache slot bit for bit and agree on the output within bf16 noise
+    assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
+    assert rel_err(outs[0][0], outs[1][0]) < 1e-2
 
 
 def test_decode_attention_plan():
