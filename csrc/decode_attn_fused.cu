@@ -582,9 +582,9 @@ extern "C" JL_API int jl_decode_attn_fused(const void* qkv, void* k_cache, void*
   p.scale_log2 = scale * 1.4426950408889634f;
   auto s = (cudaStream_t)stream;
   cudaError_t e = cudaErrorInvalidValue;
-  // enough (batch, kv-head) pairs to fill the GPU: the tensor-core kernel (see its header); otherwise the SIMT kernel
-  // with many short splits, which has the lower latency at batch 1
-  const bool use_mma = hd == 128 && (g_attn_variant == 2 || (g_attn_variant == 0 && B * nkv >= 64));
+  // 16 or more (batch, kv-head) pairs: the tensor-core kernel (see its header; measured faster from 2 x 8 pairs up:
+  // 19.5 vs 27.6 us at 2k context, 55 vs 162 us at batch 32); below that the SIMT kernel with many short splits
+  const bool use_mma = hd == 128 && (g_attn_variant == 2 || (g_attn_variant == 0 && B * nkv >= 16));
   if (use_mma) {
     // one resident wave (2 CTAs per SM) of long CTAs: every CTA pays the position → q → first-block latency chain and
     // the fold / ticket / merge tail once, and with 2.6 waves of short CTAs that fixed cost was ~25 of 72 us at
@@ -595,9 +595,18 @@ extern "C" JL_API int jl_decode_attn_fused(const void* qkv, void* k_cache, void*
       if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
         sms = 148;
     }
-    int ms = (2 * sms + B * nkv - 1) / (B * nkv);
-    p.splits = ms < splits ? ms : splits;
-    splits = p.splits;
+    // fewest splits whose CTA count fills whole waves of the 2 x sms resident slots best (e.g. 192 pairs x 3 = 576 of
+    // 592 slots); at equal fill the smaller count wins (less fixed cost, no merge at 1)
+    const int slots = 2 * sms, pairs = B * nkv;
+    int ms = 1;
+    float best = 0.f;
+    for (int c = 1; c <= splits && c <= 16; ++c) {
+      const int n = pairs * c;
+      const float fill = (float)n / (float)(((n + slots - 1) / slots) * slots);
+      if (fill > best + 0.02f) { best = fill; ms = c; }
+    }
+    p.splits = ms;
+    splits = ms;
 #define JL_DM(G_) \
     if (G == G_) e = launch_pdl(decode_attn_mma_kernel<G_, 32>, dim3(splits, nkv, B), dim3(DM_WARPS * 32), 0, s, p);
     JL_DM(1) else JL_DM(2) else JL_DM(4) else JL_DM(8)

@@ -90,8 +90,8 @@ int jl_decode_attn_fused(const void* qkv, void* k_cache, void* v_cache, const fl
                          const int* cache_len_ptr, const int* pad_left, void* scratch, void* out, int B, int nh,
                          int nkv, int hd, int T, int max_pos, float scale, int splits, void* stream);
 /* Two kernels stand behind jl_decode_attn_fused: a SIMT one with many short splits (lowest latency at batch 1) and,
- * for head_dim 128 with batch * nkv >= 64, a tensor-core one (mma.sync, K/V from global memory straight into MMA
- * fragments) that streams the cache ~2.5x faster at batch 16-64.  variant: 0 = choose by shape, 1 = SIMT, 2 = tensor
+ * for head_dim 128 with batch * nkv >= 16, a tensor-core one (mma.sync, K/V from global memory straight into MMA
+ * fragments) that streams the cache ~3x faster at batch 16-64.  variant: 0 = choose by shape, 1 = SIMT, 2 = tensor
  * core (where it applies).  Process-wide; meant for tests and A/B measurements. */
 int jl_decode_attn_fused_set_variant(int variant);
 

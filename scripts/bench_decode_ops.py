@@ -42,6 +42,27 @@ ang = torch.arange(T + 64, device=dev, dtype=torch.float32)[:, None] * (
     500000.0 ** (-torch.arange(half, device=dev, dtype=torch.float32) / half))[None]
 cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
 
+if os.environ.get("ATTN_SWEEP") == "1":
+    # attention alone, both kernels, over (batch, kv heads per rank, group) shapes of the benchmark configs
+    for B, kv, G in [(16, 1, 8), (64, 1, 8), (9, 8, 4), (16, 8, 4), (32, 8, 4), (8, 32, 1), (32, 32, 1), (2, 8, 4), (4, 8, 4)]:
+        q = torch.randn(B, (kv * G + 2 * kv) * hd, device=dev).bfloat16()
+        kc = torch.randn(B, kv, T + 64, hd, device=dev).bfloat16()
+        vc = torch.randn(B, kv, T + 64, hd, device=dev).bfloat16()
+        clen = torch.full((1,), T, device=dev, dtype=torch.int32)
+        pad = torch.zeros(B, device=dev, dtype=torch.int32)
+        splits, scratch = K.decode_attn_fused_plan(B, kv * G, kv, hd, T + 64, dev)
+        out = torch.empty(B, kv * G * hd, device=dev, dtype=torch.bfloat16)
+        fn = lambda: K.decode_attn_fused(q, kc, vc, cos, sin, clen, pad, kv * G, kv, hd, splits, scratch, out=out)
+        ts = []
+        for v in (1, 2):
+            K.set_decode_attn_variant(v)
+            ts.append(timeit(fn) * 1e3)
+        K.set_decode_attn_variant(0)
+        by = 2 * B * kv * T * hd * 2
+        print(f"attn B={B:3d} nkv={kv:2d} G={G}: simt {ts[0]:7.1f} us  mma {ts[1]:7.1f} us  floor {by / HBM * 1e6:6.1f} us  "
+              f"(plan splits {splits})")
+    sys.exit(0)
+
 for B in batches:
     x = torch.randn(B, H, device=dev).bfloat16()
     kc = torch.randn(B, nkv, T + 64, hd, device=dev).bfloat16()

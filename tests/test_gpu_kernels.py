@@ -340,7 +340,7 @@ def test_decode_attention_fused(nh, nkv, hd, B, filled, max_len, attn_variant):
 
 @pytest.mark.parametrize("nh,nkv", [(32, 8), (8, 1), (8, 8)])
 def test_decode_attention_fused_batched_shape_picks_tensor_core_kernel(nh, nkv):
-    """Batch 16-64 shapes (batch x kv heads >= 64 → the tensor-core kernel by default): rows with different left
+    """Batch 16-64 shapes (batch x kv heads >= 16 → the tensor-core kernel by default): rows with different left
     padding, a context that is not a multiple of the 128-key chunk, per-head / per-column error bounds."""
     B, hd, filled, T = 64 // nkv + 8, 128, 1111, 1280
     qkv = rnd(B, (nh + 2 * nkv) * hd, seed=33)
