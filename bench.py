@@ -184,6 +184,8 @@ def main() -> None:
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-baseline", action="store_true", help="skip the same-box PyTorch (cuBLAS + SDPA + NCCL) arm")
     ap.add_argument("--no-tp-check", action="store_true", help="skip the pre-run TP-vs-single-GPU correctness check")
+    ap.add_argument("--sweep-batches", default="", help="comma-separated extra batch sizes measured with the same engine "
+                    "after the headline run (device-timed decode + prefill); reported under \"batch_sweep\"")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
@@ -311,6 +313,7 @@ def main() -> None:
     launches_eager = _lib.launch_count() - launches0
     per_step_launches = eng.launches_per_step(stream.st) if hasattr(eng, "launches_per_step") else None
     gpu_launches = launches_eager if stream.graph is None else (per_step_launches or 0) * args.steps
+    used_graph = stream.graph is not None
 
     # ---------------------------------------------------------------- end to end through the public API
     stream2 = llama.stream(prompt, mask, max_gen_len=max_len - P, temperature=0.0, top_p=1.0)
@@ -325,6 +328,43 @@ def main() -> None:
         feed.copy_(out)
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+    h2d_bytes, d2h_bytes = stream2.h2d_bytes, stream2.d2h_bytes
+
+    # ---------------------------------------------------------------- other batch sizes, same engine (optional)
+    sweep = None
+    if args.sweep_batches:
+        sweep = []
+        del stream, stream2, st
+        for b in [int(v) for v in args.sweep_batches.split(",") if v]:
+            eng._decode_states.clear()                     # drop the previous batch's KV cache and graphs
+            torch.cuda.empty_cache()
+            pr = torch.randint(0, cfg.vocab_size, (b, P), generator=g).pin_memory()
+            mk = torch.ones(b, P, dtype=torch.int32).pin_memory()
+            barrier()
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record()
+            sb = llama.stream(pr, mk, max_gen_len=max_len - P, temperature=0.0, top_p=1.0)       # prefill + first token
+            p1.record()
+            torch.cuda.synchronize()
+            pre_ms = max_over_ranks(p0.elapsed_time(p1))
+            step = (sb.graph.replay if sb.graph is not None else
+                    (lambda sb=sb: eng._decode_step(sb.st, sb.cache, sb.sampling, sb.eos, sb.pad)))
+            for _ in range(args.warmup):
+                step()
+            barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            for _ in range(args.steps):
+                step()
+            s1.record()
+            barrier()
+            ms = max_over_ranks(s0.elapsed_time(s1)) / args.steps
+            kv_bytes = 2 * len(eng.layers) * b * eng.nkv * eng.hd * 2 * (P + args.warmup + args.steps // 2)
+            sweep.append({"global_batch": b, "ms_per_step": round(ms, 4), "tokens_per_sec": round(b / (ms / 1e3), 1),
+                          "prefill_ms_incl_first_token_and_graph_capture": round(pre_ms, 2),
+                          "kv_bytes_per_step_per_rank": kv_bytes,
+                          "launches_per_step": eng.launches_per_step(sb.st)})
+            del sb
 
     # ---------------------------------------------------------------- same-box library yardstick
     baseline = None
@@ -383,7 +423,7 @@ def main() -> None:
             "config": {"model": args.model, "global_batch": B, "seq_len": P, "parallelism": f"tp{world}",
                        "decode_context": f"{P}+{args.warmup}..{P + args.warmup + args.steps}",
                        "l2": "no flush needed: per-step weight stream (%.1f GB/rank) >> 126 MB L2" % (weight_bytes / 1e9),
-                       "cuda_graph": stream.graph is not None},
+                       "cuda_graph": used_graph},
             "p50_ms_per_token": round(ms_per_step, 4),
             "hbm_roofline_frac_of_measured": round((weight_bytes / (ms_per_step / 1e3)) / (hbm * 1e9), 4),
             "prefill": {"tokens_per_sec": round(B * P / (prefill_best / 1e3), 1), "ms": round(prefill_best, 3),
@@ -392,9 +432,10 @@ def main() -> None:
                         "path": PATH_NAMES[default_path],
                         "other_path": prefill_alt},
             "e2e": {"value": round(B * args.steps / (e2e_ms / 1e3), 2), "unit": "tokens/s",
-                    "h2d_bytes_per_step": stream2.h2d_bytes, "d2h_bytes_per_step": stream2.d2h_bytes,
+                    "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "api": "LLaMA.stream(...).step(feed)"},
             "gpu_launches": int(gpu_launches), "clocks": clocks, "tp_check": check,
+            "batch_sweep": sweep,
             "same_box_library_baseline": baseline,
             "speedup_vs_library_baseline": (round(baseline["ms_per_step"] / ms_per_step, 3)
                                             if baseline and "ms_per_step" in baseline else None),
