@@ -38,16 +38,26 @@ struct GemmParams {
   uint64_t hint_a, hint_b;
   // ---- split-K for swap-AB launches with fewer weight-row tiles than SMs (decode at batch 9..128: N = 4096
   // gives 32 tiles, i.e. 22 % of the SMs streaming): each tile's K range is cut into `ksplit` work items, the
-  // fp32 partials meet in `ws` ([ksplit][tokens][features]) and the last item to arrive (ticket) sums them in
-  // split order — deterministic — and runs the epilogue.  ksplit == 1: off.
+  // fp32 partials meet in `ws` ([ksplit][features][tokens]); once all splits of a tile have arrived (ticket) each of
+  // them sums its share of the tokens in split order — deterministic — and runs the epilogue.  ksplit == 1: off.
   int ksplit;
   float* ws;
   int* tickets;                      // [2][ticket_half]: arrivals, completions per tile; zero between launches
   int ticket_half;
+  unsigned long long* trace;         // optional [grid][16] %globaltimer stamps (jl_gemm_set_trace), NULL = off
 };
 
 __host__ __device__ constexpr int tmem_cols_for(int bn) {
   return 2 * bn <= 32 ? 32 : (2 * bn <= 64 ? 64 : (2 * bn <= 128 ? 128 : (2 * bn <= 256 ? 256 : 512)));
+}
+
+// one thread records when it reached a point of the kernel (scripts/gemm_trace.py prints the timeline)
+__device__ __forceinline__ void gemm_stamp(const GemmParams& p, int ev) {
+  if (p.trace != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    p.trace[(size_t)blockIdx.x * 16 + ev] = t;
+  }
 }
 
 template <int BN, int EPI, bool SWAP, bool OUT_F32>
@@ -80,6 +90,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   // swap-AB (decode): the next kernel of the chain may start right away — it waits for this grid itself before it
   // touches anything this grid writes — so that ITS weight prefetch (below) overlaps our epilogue
   if constexpr (SWAP) pdl_launch_dependents();
+  if (threadIdx.x == 0) gemm_stamp(p, 0);
   if (warp == 0 && lane == 0) {
     tc::prefetch_tensormap(&tmap_a);
     tc::prefetch_tensormap(&tmap_b);
@@ -94,6 +105,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  if (threadIdx.x == 0) gemm_stamp(p, 1);
 
   if constexpr (!SWAP) {
     pdl_wait();               // everything above overlapped the previous kernel's tail
@@ -120,6 +132,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         }
         pdl_wait();
       }
+      gemm_stamp(p, 2);
       for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
         const int t = wi % num_tiles, split = wi / num_tiles;
         const int kb0 = split * num_kb / ksplit, kb1 = (split + 1) * num_kb / ksplit;
@@ -153,6 +166,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(full_bar(stage), phase);
           tc::fence_after_sync();
+          if (it == 0 && kb == kb0) gemm_stamp(p, 3);
           const uint32_t sa = smem_base + stage * STAGE_BYTES, sb = sa + A_BYTES;
           const uint64_t da = tc::smem_desc_kmajor_sw128(sa), db = tc::smem_desc_kmajor_sw128(sb);
 #pragma unroll
@@ -162,6 +176,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
         tc::mma_commit(tfull_bar(as));                      // accumulator complete → epilogue
+        if (it == 0) gemm_stamp(p, 4);
       }
     }
   } else if (warp >= 4) {
@@ -176,11 +191,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
       tc::mbar_wait(tfull_bar(as), aphase);
       tc::fence_after_sync();
+      if (it == 0 && threadIdx.x == 128) gemm_stamp(p, 5);
       const int ra = a_blk * GEMM_BM + quarter * 32 + lane;  // A-side row of this thread
       const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
       constexpr int CH = BN >= 32 ? 32 : 16;
       // swap-AB epilogue of one (token, feature = this lane's weight row) value; whole warps call it together
-      auto swap_emit = [&](const int tok, float x) {
+      // rpre: the residual value when the caller already holds it (split-K finish), else it is loaded here
+      auto swap_emit = [&](const int tok, float x, const bool pre = false, const float rpre = 0.f) {
         if constexpr (EPI == EPI_SWIGLU) {
           // (gate, up) sit in adjacent lanes: even lane gets its neighbour's value
           const float xb = __bfloat162float(__float2bfloat16(x));
@@ -192,7 +209,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             reinterpret_cast<float*>(p.out)[(size_t)tok * p.ldo + ra] = x;
           } else {
             if constexpr (EPI == EPI_RESIDUAL)
-              x = __bfloat162float(__float2bfloat16(x)) + __bfloat162float(p.residual[(size_t)tok * p.ldo + ra]);
+              x = __bfloat162float(__float2bfloat16(x)) +
+                  (pre ? rpre : __bfloat162float(p.residual[(size_t)tok * p.ldo + ra]));
             reinterpret_cast<__nv_bfloat16*>(p.out)[(size_t)tok * p.ldo + ra] = __float2bfloat16(x);
           }
         }
@@ -274,17 +292,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             }
           }
         } else {
-          // swap-AB: lanes are weight rows (output features), columns are tokens → transposed store;
-          // for a fixed token the 32 lanes write 32 consecutive features (coalesced)
+          // swap-AB: lanes are weight rows (output features), columns are tokens
+          if (ksplit > 1) {
+            // fp32 partial of this K split: ws[split][feature][token] — a thread's tokens are contiguous, so both this
+            // store and the finish below move 4 tokens per instruction
+            if (ra < p.Ra) {
+              float* wrow = p.ws + ((size_t)split * p.Ra + ra) * (size_t)(p.b_blocks * BN) + cb0;
 #pragma unroll
-          for (int j = 0; j < CH; ++j) {
-            const int tok = cb0 + j;
-            const float x = __uint_as_float(v[j]);
-            if (ksplit > 1) {
-              if (tok < p.Rb && ra < p.Ra) p.ws[((size_t)split * p.Rb + tok) * p.Ra + ra] = x;     // fp32 partial
-            } else {
-              swap_emit(tok, x);
+              for (int j = 0; j < CH; j += 4)
+                *reinterpret_cast<uint4*>(wrow + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
             }
+          } else {
+            // transposed store: for a fixed token the 32 lanes write 32 consecutive features (coalesced)
+#pragma unroll
+            for (int j = 0; j < CH; ++j) swap_emit(cb0 + j, __uint_as_float(v[j]));
           }
         }
       }
@@ -295,12 +316,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         if (ksplit > 1) {
           // ---- split-K finish, shared by the K splits of the tile: all of them run at the same time (one work item
           // per CTA, see launch_gemm), so each publishes its partial, waits until the tile's ticket shows all ksplit
-          // arrivals and then sums + emits ITS share of the tile's tokens (a single L2 round trip of ksplit x 4-8
-          // loads per thread; when the last split to arrive did the whole tile alone that was 8 dependent round
-          // trips at batch 32: 10 us of a 25 us GEMM).  Sums run in split order: deterministic.
-          __threadfence();
+          // arrivals and then sums + emits ITS share of the tile's tokens (ksplit 16-byte loads per 4 tokens; when the
+          // last split to arrive did the whole tile alone, with scalar loads, the finish was 10 us of a 25 us GEMM).
+          // Sums run in split order: deterministic.
+          // publish: the four warps' partial stores, one barrier, then ONE fence + arrival (cumulative: it orders the
+          // stores of all 128 threads; 128 separate fences cost ~1 us more)
           asm volatile("bar.sync 1, 128;" ::: "memory");                // the four epilogue warps
           if (threadIdx.x == 128) {
+            gemm_stamp(p, 6);
+            __threadfence();
             atomicAdd(p.tickets + t, 1);
             unsigned spins = 0;
             while (ld_acquire_gpu_u32(reinterpret_cast<const unsigned int*>(p.tickets + t)) < (unsigned)ksplit) {
@@ -311,30 +335,40 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             }
           }
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          __threadfence();
+          if (threadIdx.x == 128) gemm_stamp(p, 7);
           {
-            const int per = ((BN + ksplit - 1) / ksplit + 3) & ~3;      // tokens per split, whole groups of 4
+            // this split's share of the tile's tokens, 4 (one 16-byte load per split) at a time; the residual values
+            // are requested first, the partials (L2, written by other SMs: ld.cg) of all splits right behind them
+            const int per = ((BN + ksplit - 1) / ksplit + 3) & ~3;
             const int j_lo = split * per, j_hi = j_lo + per < BN ? j_lo + per : BN;
-            const size_t split_stride = (size_t)p.Rb * p.Ra;
-#pragma unroll 1
+            const size_t tok_pitch = (size_t)(p.b_blocks * BN), split_stride = (size_t)p.Ra * tok_pitch;
+            const bool row_ok = ra < p.Ra;                  // (all lanes stay in the loop: the SwiGLU emit shuffles)
+            const float* wrow = p.ws + (size_t)(row_ok ? ra : 0) * tok_pitch + b_blk * BN;
+#pragma unroll 2
             for (int j0 = j_lo; j0 < j_hi; j0 += 4) {
-              float x[4] = {0.f, 0.f, 0.f, 0.f};
-              const float* src = p.ws + (size_t)(b_blk * BN + j0) * p.Ra + ra;
+              float rr[4] = {0.f, 0.f, 0.f, 0.f};
+              if constexpr (EPI == EPI_RESIDUAL) {
 #pragma unroll
-              for (int sp = 0; sp < 16; ++sp) {
-                if (sp < ksplit) {
-#pragma unroll
-                  for (int u = 0; u < 4; ++u)
-                    if (b_blk * BN + j0 + u < p.Rb && ra < p.Ra) x[u] += __ldcg(src + sp * split_stride + (size_t)u * p.Ra);
+                for (int u = 0; u < 4; ++u) {
+                  const int tok = b_blk * BN + j0 + u;
+                  if (tok < p.Rb && row_ok) rr[u] = __bfloat162float(p.residual[(size_t)tok * p.ldo + ra]);
                 }
               }
+              float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+              for (int sp = 0; sp < ksplit; ++sp) {
+                const float4 pv = __ldcg(reinterpret_cast<const float4*>(wrow + sp * split_stride + j0));
+                acc.x += pv.x; acc.y += pv.y; acc.z += pv.z; acc.w += pv.w;
+              }
+              const float x[4] = {acc.x, acc.y, acc.z, acc.w};
 #pragma unroll
-              for (int u = 0; u < 4; ++u) swap_emit(b_blk * BN + j0 + u, x[u]);
+              for (int u = 0; u < 4; ++u) swap_emit(b_blk * BN + j0 + u, x[u], true, rr[u]);
             }
           }
           // the last split to finish re-arms the tile's two counters for the next launch
           asm volatile("bar.sync 1, 128;" ::: "memory");
           if (threadIdx.x == 128) {
+            gemm_stamp(p, 8);
             int* done = p.tickets + p.ticket_half + t;
             if (atomicAdd(done, 1) == ksplit - 1) { *done = 0; p.tickets[t] = 0; }
           }
@@ -345,8 +379,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 
   tc::fence_before_sync();
   __syncthreads();
+  if (threadIdx.x == 0) gemm_stamp(p, 9);
   if (warp == 2) tc::tmem_dealloc(tmem_base, TMEM_COLS);
 }
+
+static unsigned long long* g_gemm_trace = nullptr;
 
 // Caller-provided scratch for split-K (jl_gemm_set_workspace), one per device; none registered → no split-K
 struct SplitKWorkspace { float* ws; size_t ws_bytes; int* tickets; int n_tickets; };
@@ -361,6 +398,7 @@ template <int BN, int EPI, bool SWAP, bool OUT_F32>
 static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int Ra, int Rb, int K, int num_sms,
                        cudaStream_t stream) {
   GemmParams p = p0;
+  p.trace = g_gemm_trace;
   CUtensorMap ta, tb;
   int rc = make_tmap_2d_bf16(&ta, a, Ra, K, K, GEMM_BM);
   if (rc) return rc;
@@ -382,7 +420,7 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
       int ks = num_sms / grid;
       if (ks > num_kb / 4) ks = num_kb / 4;               // at least 4 k-blocks (256 columns) per item
       if (ks > 16) ks = 16;
-      while (ks > 1 && (size_t)ks * Rb * Ra * sizeof(float) > wsp.ws_bytes) --ks;
+      while (ks > 1 && (size_t)ks * Ra * (size_t)(p.b_blocks * BN) * sizeof(float) > wsp.ws_bytes) --ks;
       if (ks > 1) {
         p.ksplit = ks; p.ws = wsp.ws; p.tickets = wsp.tickets; p.ticket_half = wsp.n_tickets / 2;
         grid *= ks;
@@ -436,6 +474,11 @@ using namespace jl;
 
 // Registers (or, with ws == NULL, removes) the split-K scratch of the CURRENT device: `ws` fp32 workspace of
 // ws_bytes, `tickets` n_tickets ints that must be zero.  The library keeps the pointers; the caller owns the memory.
+// Optional timeline of the single-CTA kernel: [grid][16] u64 device buffer (0 entry, 1 set-up done, 2 producer past
+// the dependency wait, 3 first stage landed, 4 last MMA issued, 5 accumulator complete, 6 partial published,
+// 7 all splits arrived, 8 share emitted, 9 exit); NULL switches it off.
+extern "C" JL_API void jl_gemm_set_trace(void* buf) { g_gemm_trace = (unsigned long long*)buf; }
+
 extern "C" JL_API int jl_gemm_set_workspace(void* ws, size_t ws_bytes, int* tickets, int n_tickets) {
   int dev = 0;
   JL_CUDA(cudaGetDevice(&dev));

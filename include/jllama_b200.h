@@ -68,6 +68,9 @@ int jl_gemm(const void* x, const void* w, const void* residual, void* out, int M
  * owns both buffers and keeps them alive; ws == NULL unregisters.  Calls that share the scratch must be ordered
  * on one stream. */
 int jl_gemm_set_workspace(void* ws, size_t ws_bytes, int* tickets, int n_tickets);
+/* Timeline hook of the single-CTA GEMM kernel for scripts/gemm_trace.py: [grid][16] u64 device buffer of
+ * %globaltimer stamps, NULL = off (default). */
+void jl_gemm_set_trace(void* buf);
 
 /* model.py:194-198,263-288 at S=1 — split-KV GQA decode attention over [pad_left[b], *cache_len+n_new).
  * q [B,nh,hd] with batch pitch q_bstride elements (0 = dense; lets q live inside the fused qkv

@@ -131,12 +131,18 @@ class B200Engine:
         self.use_megakernel = use_megakernel and self.hd == 128 \
             and config.hidden_size % 256 == 0 and (config.intermediate_size // self.tp) % 256 == 0 \
             and (self.nh * self.hd) % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
+        # Largest batch the whole-step kernel takes (it can hold 8 rows).  On one GPU the per-op path (tcgen05 swap-AB
+        # GEMMs + tensor-core decode attention) is faster from batch 5 up — measured, LLaMA-3 8B, 2k context, ms/step
+        # whole-step vs per-op: batch 4 3.68 vs 5.05, batch 6 5.13 vs 4.32, batch 8 5.23 vs 4.41 (LLaMA-2 7B batch 8:
+        # 7.12 vs 5.20).  Under tensor parallelism the whole-step kernel keeps all 8 (its all-reduce is in-kernel).
+        # JLLAMA_MEGA_MAX_BATCH overrides the hand-over point.
+        self.mega_max_batch = min(8, int(os.environ.get("JLLAMA_MEGA_MAX_BATCH", "4" if self.tp == 1 else "8")))
         self._stack_weights()
 
     def _mega_fits(self, batch: int) -> bool:
         """Whole-step kernel usable for this batch: its staged activations (batch x widest GEMV input) must
         leave room for a weight ring of at least 4 stages in shared memory (8B model: batch <= 4 at TP=1)."""
-        if not self.use_megakernel or batch > 8:
+        if not self.use_megakernel or batch > self.mega_max_batch:
             return False
         if batch not in self._mega_fit_cache:
             c = self.config

@@ -29,6 +29,7 @@ _SIGNATURES = {
     "jl_gemm": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "jl_gemm_2cta": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]),
     "jl_gemm_set_workspace": (i32, [vp, sz, vp, i32]),
+    "jl_gemm_set_trace": (None, [vp]),
     "jl_decode_attn_scratch_bytes": (sz, [i32, i32, i32, i32]),
     "jl_decode_attn_splits": (i32, [i32, i32, i32, i32]),
     "jl_decode_attn": (i32, [vp, vp, vp, ip, ip, vp, vp, i32, i32, i32, i32, i32, i32, f32, i32, i32, vp]),

@@ -149,6 +149,47 @@ def test_engine_cache_follows_the_parameter_tree():
     assert torch.equal(e2.final_norm.float(), gp["transformer"]["ln_f"]["kernel"].float())
 
 
+@pytest.mark.parametrize("shape", ["8b_tp1", "13b_tp2_slice", "70b_tp8_slice"])
+@pytest.mark.parametrize("B,ctx", [(6, 40), (16, 300), (33, 150)])
+def test_batched_per_op_decode_matches_fp32_oracle(shape, B, ctx):
+    """The path batches above the whole-step kernel's take (batch 5+ on one GPU): swap-AB tcgen05 GEMMs (split-K with
+    the shared finish) + tensor-core decode attention, CUDA-graph replayed as `generate` does, against the fp32
+    reference model, teacher-forced, with left padding on some rows."""
+    kw = MEGA_SHAPES[shape]
+    cfg = LLaMAConfig(vocab_size=2048, num_hidden_layers=2, max_sequence_length=512, initializer_range=0.02,
+                      head_dim=128, **kw)
+    tree = tree_to(ref.init_params(cfg, seed=5), dtype=torch.bfloat16)
+    tree32 = tree_to(tree, dtype=torch.float32)
+    eng = B200Engine.from_tree(cfg, tree_to(tree, device="cuda"), use_cuda_graph=True)
+    assert not eng._mega_fits(B)
+    g = torch.Generator().manual_seed(12)
+    ids = torch.randint(3, cfg.vocab_size, (B, ctx), generator=g)
+    mask = torch.ones(B, ctx, dtype=torch.int32)
+    mask[1, :5] = 0
+    mask[B - 1, :17] = 0
+    nxt = torch.randint(3, cfg.vocab_size, (3, B), generator=g)
+    st = eng._decode_state(B, ctx + 8)
+    cache = eng.prepare(st, ids.cuda(), mask.cuda(), 0)
+    samp = (False, 1.0, 0, 1.0, 0)
+    eng._select_and_advance_after_prefill(st, cache, samp, -7, 0)
+    graph = eng._graph_for(st, cache, samp, -7, 0)
+    assert graph is not None
+    got = []
+    for i in range(3):
+        st.ids.copy_(nxt[i].to(torch.int32))
+        graph.replay()
+        got.append(st.logits.clone().cpu())
+    seq = torch.cat([ids, nxt.t()], dim=1)
+    full_mask = torch.cat([mask, torch.ones(B, 3, dtype=torch.int32)], dim=1)
+    pos = ref.default_position_ids(full_mask, B, ctx + 3, "cpu")
+    want = ref.forward(tree32, cfg, seq, full_mask, pos).logits
+    for i in range(3):
+        w = want[:, ctx + i]
+        scale = float(w.abs().max())
+        assert rel(got[i], w) < 3e-2, (i, rel(got[i], w))
+        assert torch.allclose(got[i], w, rtol=5e-2, atol=3e-2 * scale), i
+
+
 def test_other_head_sizes_are_refused_not_run_through_pytorch():
     """head_dim != 128 has no prefill kernel: the engine says so instead of running a dense PyTorch statement on the GPU."""
     cfg = LLaMAConfig(vocab_size=512, hidden_size=256, intermediate_size=768, num_hidden_layers=1,
@@ -189,6 +230,7 @@ def test_megakernel_step_matches_unfused_step(B, monkeypatch):
     tree = tree_to(ref.init_params(cfg, seed=2), dtype=torch.bfloat16, device="cuda")
     engines = [B200Engine.from_tree(cfg, tree, use_cuda_graph=False, use_megakernel=flag) for flag in (False, True)]
     assert engines[1].use_megakernel and not engines[0].use_megakernel
+    engines[1].mega_max_batch = 8                # (one GPU hands batch 5-8 to the per-op path by default)
     engines[1].mega_write_logits = True          # the greedy path keeps only arg-max candidates unless asked
     ids = torch.randint(3, cfg.vocab_size, (B, 37), generator=torch.Generator().manual_seed(7)).cuda()
     mask = torch.ones(B, 37, dtype=torch.int32, device="cuda")
@@ -241,6 +283,7 @@ def test_megakernel_matches_fp32_oracle_at_benchmark_shapes(shape, B, ctx):
     tree = tree_to(ref.init_params(cfg, seed=3), dtype=torch.bfloat16)
     tree32 = tree_to(tree, dtype=torch.float32)
     eng = B200Engine.from_tree(cfg, tree_to(tree, device="cuda"), use_cuda_graph=False)
+    eng.mega_max_batch = 8                       # these are the shapes the kernel runs under tensor parallelism, batch 1-8
     if not eng._mega_fits(B):
         pytest.skip("batch does not fit the whole-step kernel at this shape")
     eng.mega_write_logits = True
