@@ -23,6 +23,7 @@ struct RsMmParams {
   const uint4* part_mc;             // multicast address of the partial-product buffer, at this kernel's first row
   const __nv_bfloat16* norm_w;      // [H] or null (no normalised output)
   uint4* xn_mc;                     // multicast address of the gathered activations at this rank's first row (or null)
+  uint4* xn_local;                  // or: normalised rows into an ordinary local buffer [rows, H] (batched decode under TP)
   int* flags[8];                    // every rank's flag array (index rank = local)
   int* ticket;
   const int* epoch_base;            // device epoch base added to ready_epoch (null: 0) — CUDA-graph replays stay correct
@@ -40,10 +41,15 @@ __global__ void __launch_bounds__(512) rs_reduce_mm_kernel(const RsMmParams p) {
   if (p.has_partials == 1) {
     // every rank's GEMM (the previous kernel on its stream) has written its partial product
     // (has_partials == 2: the caller already ran jl_flag_exchange — this kernel then never waits for a peer)
-    if (blockIdx.x == 0 && threadIdx.x < p.tp)
-      st_release_sys(p.flags[threadIdx.x] + p.gemm_flag_off + p.rank, p.gemm_epoch);
+    // (in-kernel exchange: only for grids that are resident at once and small — the batched decode, <= 128 rows; a
+    // prompt-sized grid waiting here could keep a peer-facing kernel of another stream off the SMs)
+    const int ge = p.gemm_epoch + (p.epoch_base ? *p.epoch_base : 0);
+    if (blockIdx.x == 0 && threadIdx.x < p.tp) {
+      __threadfence_system();
+      st_release_sys(p.flags[threadIdx.x] + p.gemm_flag_off + p.rank, ge);
+    }
     if (threadIdx.x < p.tp)
-      wait_flag(p.flags[p.rank] + p.gemm_flag_off + threadIdx.x, p.gemm_epoch, p.rank, threadIdx.x, 4);
+      wait_flag(p.flags[p.rank] + p.gemm_flag_off + threadIdx.x, ge, p.rank, threadIdx.x, 4);
     __syncthreads();
   }
   const uint4* xg = reinterpret_cast<const uint4*>(p.x);
@@ -78,7 +84,7 @@ __global__ void __launch_bounds__(512) rs_reduce_mm_kernel(const RsMmParams p) {
       }
     }
   }
-  if (p.xn_mc != nullptr) {
+  if (p.xn_mc != nullptr || p.xn_local != nullptr) {
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
     __syncthreads();
@@ -99,9 +105,11 @@ __global__ void __launch_bounds__(512) rs_reduce_mm_kernel(const RsMmParams p) {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           o[j] = pack_bf16(v[c][2 * j] * r * bf16_lo(gw[j]), v[c][2 * j + 1] * r * bf16_hi(gw[j]));
-        mm::st_v4bf16x2(p.xn_mc + row + i, make_uint4(o[0], o[1], o[2], o[3]));      // one store, every rank's copy
+        if (p.xn_local != nullptr) p.xn_local[row + i] = make_uint4(o[0], o[1], o[2], o[3]);
+        else mm::st_v4bf16x2(p.xn_mc + row + i, make_uint4(o[0], o[1], o[2], o[3]));      // one store, every rank's copy
       }
     }
+    if (p.xn_mc == nullptr) return;         // local output: nothing to publish
     __threadfence_system();                 // this CTA's rows have reached every copy before it takes a ticket
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -128,17 +136,23 @@ using namespace jl;
 //     all rows and adds it to its replicated residual stream (what GSPMD's all-reduce did for
 //     /root/reference/jax_llama/partition.py:67,70).
 // has_partials = 0 skips the reduction (chain start on the embedding rows).
-extern "C" JL_API int jl_rs_reduce_mm(void* x, const void* part_mc, const void* norm_w, void* xn_mc, int rows, int H,
-                                      int has_partials, int tp, int rank, void* const* peer_flags, int gemm_flag_off,
-                                      int ready_flag_off, int gemm_epoch, int ready_epoch, const int* epoch_base, int* ticket,
-                                      float eps, void* stream) {
+//   * batched decode under TP: rows = batch, has_partials = 1 (the "GEMM done" exchange happens inside: the grid is a
+//     few dozen resident CTAs), xn_mc = NULL, xn_local = where the rows normalised with `norm_w` go — all-reduce,
+//     residual add and the next RMSNorm in one launch.
+extern "C" JL_API int jl_rs_reduce_mm(void* x, const void* part_mc, const void* norm_w, void* xn_mc, void* xn_local,
+                                      int rows, int H, int has_partials, int tp, int rank, void* const* peer_flags,
+                                      int gemm_flag_off, int ready_flag_off, int gemm_epoch, int ready_epoch,
+                                      const int* epoch_base, int* ticket, float eps, void* stream) {
   JL_CHECK_ARG(H % 8 == 0 && H <= 16384, "jl_rs_reduce_mm: H=%d must be a multiple of 8 and <= 16384", H);
   JL_CHECK_ARG(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "jl_rs_reduce_mm: bad tp/rank");
   JL_CHECK_ARG(!has_partials || part_mc != nullptr, "jl_rs_reduce_mm: needs the multicast address of the partials");
+  JL_CHECK_ARG(!(xn_mc && xn_local), "jl_rs_reduce_mm: one normalised output, multicast or local");
+  JL_CHECK_ARG(!(xn_mc || xn_local) || norm_w != nullptr, "jl_rs_reduce_mm: a normalised output needs norm_w");
+  JL_CHECK_ARG(has_partials != 1 || rows <= 128, "jl_rs_reduce_mm: the in-kernel flag exchange is for <= 128 rows");
   if (rows == 0) return JL_OK;
   RsMmParams p{};
   p.x = (__nv_bfloat16*)x; p.part_mc = (const uint4*)part_mc; p.norm_w = (const __nv_bfloat16*)norm_w;
-  p.xn_mc = (uint4*)xn_mc; p.ticket = ticket; p.epoch_base = epoch_base;
+  p.xn_mc = (uint4*)xn_mc; p.xn_local = (uint4*)xn_local; p.ticket = ticket; p.epoch_base = epoch_base;
   for (int i = 0; i < tp; ++i) p.flags[i] = (int*)peer_flags[i];
   p.H8 = H / 8; p.tp = tp; p.rank = rank; p.gemm_flag_off = gemm_flag_off; p.ready_flag_off = ready_flag_off;
   p.gemm_epoch = gemm_epoch; p.ready_epoch = ready_epoch; p.has_partials = has_partials;

@@ -237,11 +237,14 @@ int jl_gemm_2cta_pairs(void);   /* 2-CTA clusters resident at once on this GPU (
  * the `rows` rows this call owns: x[rows, H] += sum over ranks (multimem.ld_reduce, fp32 in the switch).  With `xn_mc`
  * (multicast address of the gathered-activation buffer at the same first row) the updated rows are RMS-normalised and
  * stored into every rank's copy with multimem.st, then the "rows ready" flag is published; without it the call is a
- * plain all-reduce into a replicated residual stream (rows = all tokens). */
-int jl_rs_reduce_mm(void* x, const void* part_mc, const void* norm_w, void* xn_mc, int rows, int H, int has_partials,
-                    int tp, int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off, int gemm_epoch,
-                    int ready_epoch, const int* epoch_base /* device int added to ready_epoch, or NULL */, int* ticket,
-                    float eps, void* stream);
+ * plain all-reduce into a replicated residual stream (rows = all tokens).  With `xn_local` instead (an ordinary
+ * [rows, H] buffer) the normalised rows stay on this rank: all-reduce + residual add + the next RMSNorm of a batched
+ * decode step in one launch.  has_partials: 0 = no reduction (chain start), 2 = the caller already exchanged the "GEMM
+ * done" flags (jl_flag_exchange), 1 = exchange them inside this kernel (rows <= 128 only: a small resident grid). */
+int jl_rs_reduce_mm(void* x, const void* part_mc, const void* norm_w, void* xn_mc, void* xn_local, int rows, int H,
+                    int has_partials, int tp, int rank, void* const* peer_flags, int gemm_flag_off, int ready_flag_off,
+                    int gemm_epoch, int ready_epoch, const int* epoch_base /* device int added to both epochs, or NULL */,
+                    int* ticket, float eps, void* stream);
 
 /* NVLS self-test over a multicast mapping of a symmetric buffer (parallel/symm.py): `mc` is the multicast
  * address.  op 0: out[i] = sum over ranks of fp32 buf[i] (multimem.ld_reduce); 1: 8-byte packets {src[i], tag}

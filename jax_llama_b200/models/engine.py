@@ -313,9 +313,16 @@ class B200Engine:
         eps = c.rms_norm_eps
         nh, nkv, hd = self.nh, self.nkv, self.hd
         start = cache.index
+        # (see below) only the graph-replayed batched decode of a TP engine takes the fused all-reduce + norm form
+        fuse_norm = (self.tp > 1 and S == 1 and positions is None and ws is not None and 8 < B <= 128
+                     and os.environ.get("JLLAMA_TP_FUSE_NORM", "1") != "0")
+        xn = None
         for i, l in enumerate(self.layers):
             kc, vc = cache.k[i], cache.v[i]
-            qkv = K.linear(x, l.wqkv, norm_w=l.attn_norm, eps=eps, out=ws.qkv if ws else None)
+            if xn is None:
+                qkv = K.linear(x, l.wqkv, norm_w=l.attn_norm, eps=eps, out=ws.qkv if ws else None)
+            else:
+                qkv = K.linear(xn, l.wqkv, out=ws.qkv if ws else None)      # normalised by the previous layer's all-reduce
             if S == 1 and positions is None:
                 # decode: RoPE + KV append + split-KV attention + merge in one launch
                 attn = K.decode_attn_fused(qkv, kc, vc, self.cos, self.sin, cache.len_dev, cache.pad_left, nh, nkv,
@@ -332,9 +339,21 @@ class B200Engine:
                 K.rope_kv_write(qkv, kc, vc, self.cos, self.sin, B, S, nh, nkv, hd, cache_len=cache.len_dev,
                                 pad_left=cache.pad_left, positions=positions, q_out=q_rot)
                 attn = self._prefill_attn(q_rot.view(B, S, nh, hd), kc, vc, start, S, cache).view(B * S, nh * hd)
+            if fuse_norm:
+                # batched decode under TP: GEMM → one kernel that exchanges the "done" flags, pulls the in-switch sum,
+                # adds the residual and applies the NEXT RMSNorm (7 launches per layer instead of 11)
+                nv = self.comm.nvls_state(B, c.hidden_size)
+                K.linear(attn, l.wo, out=nv.next_part())
+                xn = nv.allreduce_add_norm(x, l.ffn_norm, eps)
+                h = K.linear(xn, l.w13, mode=K.SWIGLU, out=ws.mlp if ws else None)
+                K.linear(h, l.w2, out=nv.next_part())
+                xn = nv.allreduce_add_norm(x, self.layers[i + 1].attn_norm if i + 1 < len(self.layers) else self.final_norm, eps)
+                continue
             x = self._row_parallel(attn, l.wo, x)
             h = K.linear(x, l.w13, norm_w=l.ffn_norm, eps=eps, mode=K.SWIGLU, out=ws.mlp if ws else None)
             x = self._row_parallel(h, l.w2, x)
+        if ws is not None:
+            ws.xn_final = xn            # rows already normalised with final_norm (fused path), else None
         return x
 
     def _prefill_sp(self, input_ids: torch.Tensor, cache: DeviceKVCache, B: int, S: int) -> torch.Tensor:
@@ -663,7 +682,10 @@ class B200Engine:
         else:
             K.embed(st.ids, self.embedding, out=st.x)
             x = self._layers(st.x, st.B, 1, cache, None, ws=st)
-            K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True, out=st.logits)
+            if getattr(st, "xn_final", None) is not None:
+                K.linear(st.xn_final, self.lm_head, out_f32=True, out=st.logits)
+            else:
+                K.linear(x, self.lm_head, norm_w=self.final_norm, eps=c.rms_norm_eps, out_f32=True, out=st.logits)
         self._select_and_advance(st, cache, sampling, eos, pad)
         if self.comm is not None:
             self.comm.end_sequence()

@@ -42,9 +42,9 @@ _EXTRA_SIGNATURES = {
     "jl_flag_exchange": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "jl_wait_flags": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "jl_memcpy_d2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
-    "jl_rs_reduce_mm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
-                                  C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
-                                  C.c_float, C.c_void_p]),
+    "jl_rs_reduce_mm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                  C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                  C.c_void_p, C.c_float, C.c_void_p]),
 }
 
 
@@ -306,10 +306,29 @@ class NvlsPrefill:
             dist.all_reduce(y, group=cm.group)
             return x.add_(y)
         self._exchange_gemm_done()
-        _lib.check(_L().jl_rs_reduce_mm(x.data_ptr(), self.heap.mc(self.part_off[self.slot]), None, None, self.M, self.H,
-                                        2, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off, self.ready_off,
+        _lib.check(_L().jl_rs_reduce_mm(x.data_ptr(), self.heap.mc(self.part_off[self.slot]), None, None, None, self.M,
+                                        self.H, 2, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off, self.ready_off,
                                         0, 0, None, self.ticket.data_ptr(), 0.0, K._stream()), "jl_rs_reduce_mm")
         return x
+
+    def allreduce_add_norm(self, x: torch.Tensor, norm_w: torch.Tensor, eps: float) -> torch.Tensor:
+        """Batched decode (M <= 128 rows): x += Σ_ranks part, and the rows RMS-normalised with `norm_w` come back in a
+        local buffer — flag exchange, in-switch reduction, residual add and the next norm in ONE launch (the prompt-sized
+        form keeps the exchange in its own one-warp kernel, see the class docstring)."""
+        cm = self.comm
+        if self.M > 128 or self.use_nccl_baseline:
+            raise ValueError("allreduce_add_norm is the batched-decode form (M <= 128)")
+        if not hasattr(self, "xn_local"):
+            self.xn_local = [torch.empty((self.M, self.H), dtype=torch.bfloat16, device=cm.device) for _ in range(2)]
+            self.xn_slot = 0
+        self.xn_slot ^= 1
+        out = self.xn_local[self.xn_slot]
+        self.rel += 1
+        _lib.check(_L().jl_rs_reduce_mm(x.data_ptr(), self.heap.mc(self.part_off[self.slot]), norm_w.data_ptr(), None,
+                                        out.data_ptr(), self.M, self.H, 1, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off,
+                                        self.ready_off, self.rel, 0, self.base.data_ptr(), self.ticket.data_ptr(),
+                                        float(eps), K._stream()), "jl_rs_reduce_mm")
+        return out
 
     def rs_reduce(self, x_shard: torch.Tensor, norm_w: torch.Tensor, eps: float, has_partials: bool) -> None:
         """Owner step: x_shard += in-switch Σ of this rank's rows; RMSNorm → every rank's a_full[next parity]; publish."""
@@ -322,7 +341,7 @@ class NvlsPrefill:
         row0 = cm.rank * self.mloc * self.H * 2
         part_mc = self.heap.mc(self.part_off[self.slot] + row0) if has_partials else None
         _lib.check(_L().jl_rs_reduce_mm(x_shard.data_ptr(), part_mc, norm_w.data_ptr(),
-                                        self.heap.mc(self.a_off[self.parity] + row0), self.mloc, self.H,
+                                        self.heap.mc(self.a_off[self.parity] + row0), None, self.mloc, self.H,
                                         2 if has_partials else 0, cm.tp, cm.rank, cm.flag_ptrs, self.gemm_off,
                                         self.ready_off, 0, self.last_ready, self.base.data_ptr(), self.ticket.data_ptr(),
                                         float(eps), K._stream()), "jl_rs_reduce_mm")
