@@ -131,13 +131,16 @@ class B200Engine:
         self.use_megakernel = use_megakernel and self.hd == 128 \
             and config.hidden_size % 256 == 0 and (config.intermediate_size // self.tp) % 256 == 0 \
             and (self.nh * self.hd) % 256 == 0 and (self.nh // self.nkv) in (1, 2, 4, 8)
-        # Largest batch the whole-step kernel takes (it can hold 8 rows).  On one GPU the per-op path (tcgen05 swap-AB
-        # GEMMs + tensor-core decode attention) is faster from batch 5 up — measured, LLaMA-3 8B, 2k context, ms/step
-        # whole-step vs per-op: batch 4 3.68 vs 5.05, batch 6 5.13 vs 4.32, batch 8 5.23 vs 4.41 (LLaMA-2 7B batch 8:
-        # 7.12 vs 5.20).  Under tensor parallelism the whole-step kernel keeps all 8 (its all-reduce is in-kernel).
-        # JLLAMA_MEGA_MAX_BATCH overrides the hand-over point.
-        self.mega_max_batch = min(8, int(os.environ.get("JLLAMA_MEGA_MAX_BATCH", "4" if self.tp == 1 else "8")))
         self._stack_weights()
+        # Largest batch the whole-step kernel takes (it can hold 8 rows).  From batch 5 up the per-op path (tcgen05
+        # swap-AB GEMMs + tensor-core decode attention, under TP with the fused exchange / all-reduce / norm kernel) is
+        # faster whenever a rank streams a lot of weights per step; the whole-step kernel keeps all 8 rows only where
+        # the step is latency-bound (little weight per rank).  Measured, ms/step whole-step vs per-op, 2k context:
+        # 8B on one GPU (15 GB) batch 6 5.13 vs 4.32, batch 8 5.23 vs 4.41; 7B batch 8 7.12 vs 5.20; 8B at TP=2 (7.5 GB)
+        # batch 6 3.50 vs 3.22, batch 8 3.69 vs 3.31 (batch 5: 3.19 vs 3.36); 70B at TP=8 (17.6 GB) batch 8 9.53 vs
+        # 8.23 for batch 16; 8B at TP=8 (1.9 GB) batch 8 1.48 vs 2.17 for batch 16.  JLLAMA_MEGA_MAX_BATCH overrides.
+        default_max = 4 if self.weight_bytes_per_step() >= (5 << 30) else 8
+        self.mega_max_batch = min(8, int(os.environ.get("JLLAMA_MEGA_MAX_BATCH", str(default_max))))
 
     def _mega_fits(self, batch: int) -> bool:
         """Whole-step kernel usable for this batch: its staged activations (batch x widest GEMV input) must
@@ -314,7 +317,7 @@ class B200Engine:
         nh, nkv, hd = self.nh, self.nkv, self.hd
         start = cache.index
         # (see below) only the graph-replayed batched decode of a TP engine takes the fused all-reduce + norm form
-        fuse_norm = (self.tp > 1 and S == 1 and positions is None and ws is not None and 8 < B <= 128
+        fuse_norm = (self.tp > 1 and S == 1 and positions is None and ws is not None and 4 < B <= 128
                      and os.environ.get("JLLAMA_TP_FUSE_NORM", "1") != "0")
         xn = None
         for i, l in enumerate(self.layers):

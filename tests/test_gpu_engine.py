@@ -161,6 +161,7 @@ def test_batched_per_op_decode_matches_fp32_oracle(shape, B, ctx):
     tree = tree_to(ref.init_params(cfg, seed=5), dtype=torch.bfloat16)
     tree32 = tree_to(tree, dtype=torch.float32)
     eng = B200Engine.from_tree(cfg, tree_to(tree, device="cuda"), use_cuda_graph=True)
+    eng.mega_max_batch = 4                       # what a model with >= 5 GB of weights per rank gets by default
     assert not eng._mega_fits(B)
     g = torch.Generator().manual_seed(12)
     ids = torch.randint(3, cfg.vocab_size, (B, ctx), generator=g)

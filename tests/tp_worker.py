@@ -112,6 +112,20 @@ def main():
     s9b = eng.generate(ids9.to(dev), None, max_length=24, do_sample=True, temperature=0.8, top_k=None, top_p=0.9, seed=4,
                        eos_token_id=-7)
     assert torch.equal(s9a, s9b)
+    # batch 6 handed to the per-op path (what a wide model does under TP, engine.mega_max_batch = 4): swap-AB GEMMs at
+    # M = 6 + the fused exchange / all-reduce / norm kernel, against the fp32 model
+    old_max = eng.mega_max_batch
+    eng.mega_max_batch = 4
+    seq6 = eng.generate(ids9[:6].to(dev), None, max_length=26, eos_token_id=-7, pad_token_id=0)
+    eng.mega_max_batch = old_max
+    g6 = [torch.empty_like(seq6) for _ in range(world)]
+    dist.all_gather(g6, seq6)
+    assert all(torch.equal(g6[0], t) for t in g6), "ranks generated different tokens at batch 6 (per-op path)"
+    logits6 = ref.forward(full32, cfg, seq6.cpu()).logits
+    for t in range(17, 26):
+        row = logits6[:, t - 1]
+        chosen = row.gather(-1, seq6[:, t:t + 1].cpu())[:, 0]
+        assert ((row.max(-1).values - chosen) < 3e-2 * row.abs().max()).all(), ("batch 6 per-op", t)
     # ---- 3. sequence-parallel prefill (all-gather→GEMM, GEMM→reduce-scatter fused over peer memory)
     S = 64 * world if world > 2 else 128
     ids_sp = torch.randint(3, cfg.vocab_size, (2, S), generator=torch.Generator().manual_seed(9))
