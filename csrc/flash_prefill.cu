@@ -549,7 +549,12 @@ extern "C" JL_API int jl_flash_prefill(const void* q, const void* k_cache, const
                                        const int* cache_len_ptr, const int* pad_left, void* out, int B, int S,
                                        int nh, int nkv, int hd, int T, int start, float scale, void* stream) {
   (void)cache_len_ptr;
-  JL_CHECK_ARG(hd == FA_HD, "jl_flash_prefill: head_dim=%d (only 128 is built)", hd);
+  // 64-wide heads (1B-class LLaMA-architecture models) go to the warp-level tensor-core kernel (prefill_attn_mma.cu);
+  // JLLAMA_PREFILL_MMA=1 sends head_dim 128 there too (A/B against the tcgen05 kernel below)
+  static const bool force_mma = [] { const char* e = getenv("JLLAMA_PREFILL_MMA"); return e && e[0] == '1'; }();
+  if (hd == 64 || (force_mma && hd == 128))
+    return jl_prefill_attn_mma(q, k_cache, v_cache, pad_left, out, B, S, nh, nkv, hd, T, start, scale, stream);
+  JL_CHECK_ARG(hd == FA_HD, "jl_flash_prefill: head_dim=%d (64 and 128 are built)", hd);
   JL_CHECK_ARG(nkv > 0 && nh % nkv == 0, "jl_flash_prefill: nh=%d not a multiple of nkv=%d", nh, nkv);
   JL_CHECK_ARG(start >= 0 && start + S <= T, "jl_flash_prefill: start=%d + S=%d exceeds cache capacity %d", start, S, T);
   if (B * S == 0) return JL_OK;

@@ -119,6 +119,11 @@ int jl_flash_prefill_occupancy(int smem_override /* -1 */); /* resident CTAs per
 int jl_flash_prefill(const void* q, const void* k_cache, const void* v_cache, const int* cache_len_ptr,
                      const int* pad_left, void* out, int B, int S, int nh, int nkv, int hd, int T, int start,
                      float scale, void* stream);
+/* Same contract on warp-level tensor cores (mma.sync, K / V from global memory straight into fragments, one warp per
+ * 16 query rows): head_dim 64 and 128.  jl_flash_prefill routes head_dim 64 here (model.py:115 allows any
+ * hidden / heads; the 1B-class LLaMA-architecture models have 64-wide heads). */
+int jl_prefill_attn_mma(const void* q, const void* k_cache, const void* v_cache, const int* pad_left, void* out, int B,
+                        int S, int nh, int nkv, int hd, int T, int start, float scale, void* stream);
 
 /* generation.py:28-41 (HF warpers + categorical/argmax) — logits fp32 [B, ld] (V valid columns). */
 int jl_argmax(const float* logits, int B, int V, int ld, int idx_offset, float* out_val, int* out_idx,

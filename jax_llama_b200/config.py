@@ -220,6 +220,12 @@ PRESETS: Dict[str, Dict[str, Any]] = {
                       num_attention_heads=32, num_key_value_heads=8, rms_norm_eps=1e-5,
                       rope_theta=500000.0, max_sequence_length=8192, bos_token_id=128000,
                       eos_token_id=128001),
+    # 1B-class LLaMA-architecture shape with 64-wide heads and tied embeddings (the architecture of Llama-3.2-1B; its
+    # "llama3" RoPE frequency scaling is not applied — the reference has no RoPE scaling either)
+    "llama3.2-1b": dict(vocab_size=128256, hidden_size=2048, intermediate_size=8192, num_hidden_layers=16,
+                        num_attention_heads=32, num_key_value_heads=8, rms_norm_eps=1e-5, rope_theta=500000.0,
+                        max_sequence_length=8192, bos_token_id=128000, eos_token_id=128001,
+                        tie_word_embeddings=True),
     "llama3-70b": dict(vocab_size=128256, hidden_size=8192, intermediate_size=28672, num_hidden_layers=80,
                        num_attention_heads=64, num_key_value_heads=8, rms_norm_eps=1e-5,
                        rope_theta=500000.0, max_sequence_length=8192, bos_token_id=128000,

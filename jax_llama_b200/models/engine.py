@@ -482,11 +482,12 @@ class B200Engine:
 
     def _prefill_attn(self, q: torch.Tensor, kc: torch.Tensor, vc: torch.Tensor, start: int, S: int,
                       cache: DeviceKVCache) -> torch.Tensor:
-        if self.hd != 128:
-            # the flash kernel is built for the head size of every LLaMA (128); a dense O(S^2) PyTorch statement on the
-            # GPU path would be a silent library fallback — use the reference backend (CPU tensors) for other head sizes
-            raise NotImplementedError(f"the B200 prefill kernel is built for head_dim 128, got {self.hd}: run this model "
-                                      "through the reference backend (parameters on the CPU)")
+        if self.hd not in (64, 128):
+            # head_dim 128 (every LLaMA-1/2/3) runs the tcgen05 flash kernel, 64 (1B-class models) the warp-level
+            # tensor-core kernel; a dense O(S^2) PyTorch statement on the GPU path would be a silent library fallback —
+            # other head sizes go through the reference backend (CPU tensors)
+            raise NotImplementedError(f"the B200 prefill kernels are built for head_dim 128 and 64, got {self.hd}: run "
+                                      "this model through the reference backend (parameters on the CPU)")
         return K.prefill_attn(q, kc, vc, start, S, cache.pad_left, cache.len_dev)
 
     # ------------------------------------------------------------------ public forward

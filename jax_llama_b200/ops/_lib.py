@@ -57,6 +57,7 @@ _OPTIONAL = {
     "jl_flash_prefill_occupancy": (i32, [i32]),
     "jl_decode_mega_stages": (i32, [i32, i32, i32, i32, i32, i32]),
     "jl_flash_prefill": (i32, [vp, vp, vp, ip, ip, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
+    "jl_prefill_attn_mma": (i32, [vp, vp, vp, ip, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
 }
 
 

@@ -318,10 +318,11 @@ def prefill_attn_ref(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tens
 
 def prefill_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, start: int, S: int,
                  pad_left: Optional[torch.Tensor], cache_len: Optional[torch.Tensor] = None,
-                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 out: Optional[torch.Tensor] = None, force: Optional[str] = None) -> torch.Tensor:
     """Causal flash attention of S new tokens per row against the (already appended) cache.
 
     q [B, S, nh, hd] rotated; caches [B, nkv, T, hd]; keys [pad_left[b], start+S) are visible, causally.
+    head_dim 128 → tcgen05 kernel, 64 → warp-level tensor-core kernel; force="mma" pins the latter (64 / 128).
     """
     if not q.is_cuda:
         return prefill_attn_ref(q, k_cache, v_cache, start, S, pad_left)
@@ -332,6 +333,11 @@ def prefill_attn(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
     nkv, T = k_cache.shape[1], k_cache.shape[2]
     if out is None:
         out = torch.empty((B, S, nh * hd), dtype=q.dtype, device=q.device)
+    if force == "mma":
+        _lib.check(_lib.lib().jl_prefill_attn_mma(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), _p(pad_left),
+                                                  out.data_ptr(), B, S, nh, nkv, hd, T, start, 1.0 / math.sqrt(hd),
+                                                  _stream()), "jl_prefill_attn_mma")
+        return out
     _lib.check(_lib.lib().jl_flash_prefill(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), _p(cache_len),
                                            _p(pad_left), out.data_ptr(), B, S, nh, nkv, hd, T, start,
                                            1.0 / math.sqrt(hd), _stream()), "jl_flash_prefill")

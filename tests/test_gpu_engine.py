@@ -192,13 +192,45 @@ def test_batched_per_op_decode_matches_fp32_oracle(shape, B, ctx):
 
 
 def test_other_head_sizes_are_refused_not_run_through_pytorch():
-    """head_dim != 128 has no prefill kernel: the engine says so instead of running a dense PyTorch statement on the GPU."""
+    """head_dim outside {64, 128} has no prefill kernel: the engine says so instead of running a dense PyTorch
+    statement on the GPU."""
     cfg = LLaMAConfig(vocab_size=512, hidden_size=256, intermediate_size=768, num_hidden_layers=1,
-                      num_attention_heads=4, num_key_value_heads=4, max_sequence_length=64)
+                      num_attention_heads=8, num_key_value_heads=8, max_sequence_length=64)
+    assert cfg.head_dim == 32
     tree = tree_to(ref.init_params(cfg, seed=1), dtype=torch.bfloat16, device="cuda")
     eng = B200Engine.from_tree(cfg, tree)
-    with pytest.raises(NotImplementedError, match="head_dim 128"):
+    with pytest.raises(NotImplementedError, match="head_dim 128 and 64"):
         eng.forward(torch.randint(0, 512, (1, 5), device="cuda"))
+
+
+@pytest.mark.parametrize("nkv", [8, 2])
+def test_model_with_64_wide_heads_runs_on_the_gpu(nkv):
+    """1B-class shape (hidden / heads = 64): warp-level tensor-core prefill + per-op decode (the whole-step kernel is
+    built for 128-wide heads), against the fp32 reference model — last-token logits of a left-padded batch and a
+    teacher-forced check of every generated token."""
+    cfg = LLaMAConfig(vocab_size=1000, hidden_size=512, intermediate_size=1536, num_hidden_layers=3,
+                      num_attention_heads=8, num_key_value_heads=nkv, max_sequence_length=256, initializer_range=0.05)
+    assert cfg.head_dim == 64
+    tree = tree_to(ref.init_params(cfg, seed=4), dtype=torch.bfloat16)
+    tree32 = tree_to(tree, dtype=torch.float32)
+    eng = B200Engine.from_tree(cfg, tree_to(tree, device="cuda"))
+    assert not eng.use_megakernel
+    g = torch.Generator().manual_seed(8)
+    ids = torch.randint(3, cfg.vocab_size, (3, 70), generator=g)
+    mask = torch.ones(3, 70, dtype=torch.int32)
+    mask[1, :9] = 0
+    pos = ref.default_position_ids(mask, 3, 70, "cpu")
+    want = ref.forward(tree32, cfg, ids, mask, pos).logits[:, -1]
+    got = eng.forward(ids.cuda(), attention_mask=mask.cuda(), last_only=True).logits[:, -1].float().cpu()
+    assert rel(got, want) < 3e-2
+    seqs = eng.generate(ids.cuda(), mask.cuda(), max_length=90, eos_token_id=-7, pad_token_id=0).cpu()
+    full_mask = torch.ones(3, 90, dtype=torch.int32)
+    full_mask[1, :9] = 0
+    logits = ref.forward(tree32, cfg, seqs, full_mask, ref.default_position_ids(full_mask, 3, 90, "cpu")).logits
+    for t in range(70, 90):
+        row = logits[:, t - 1]
+        chosen = row.gather(-1, seqs[:, t:t + 1])[:, 0]
+        assert ((row.max(-1).values - chosen) < 3e-2 * row.abs().max()).all(), t
 
 
 def test_generate_reports_what_it_cost():

@@ -265,6 +265,33 @@ def test_flash_prefill(B, S, start, nh, nkv, pads):
     assert_close(g.reshape(-1, hd), w.reshape(-1, hd), 2e-2)
 
 
+@pytest.mark.parametrize("hd", [64, 128])
+@pytest.mark.parametrize("B,S,start,nh,nkv,pads", [
+    (1, 128, 0, 2, 2, [0]), (2, 300, 0, 8, 2, [0, 37]), (1, 200, 128, 4, 1, [5]), (1, 1000, 0, 4, 4, [0]),
+    (2, 130, 0, 2, 1, [129, 0]), (3, 17, 40, 8, 8, [0, 3, 44])])
+def test_prefill_attention_warp_mma(hd, B, S, start, nh, nkv, pads):
+    """The warp-level tensor-core prefill kernel (the path of 64-wide heads; pinned here at 128 too): causal mask,
+    left padding, continuation from a filled cache, ragged row blocks; the cache beyond the visible keys holds NaN —
+    nothing outside [pad_left, start + row] may leak into a row."""
+    T = start + S + 5
+    q = rnd(B, S, nh, hd, seed=23)
+    kc, vc = rnd(B, nkv, T, hd, seed=24), rnd(B, nkv, T, hd, seed=25)
+    pad = torch.tensor(pads, dtype=torch.int32)
+    want = K.prefill_attn_ref(q.float(), kc.float(), vc.float(), start, S, pad)
+    kd, vd = kc.to(DEV), vc.to(DEV)
+    kd[:, :, start + S:] = float("nan")
+    vd[:, :, start + S:] = float("nan")
+    got = K.prefill_attn(q.to(DEV), kd, vd, start, S, pad.to(DEV), force="mma")
+    slots = start + torch.arange(S)
+    valid = (slots[None, :] >= pad[:, None].long())
+    g, w = got.float().cpu()[valid], want[valid]
+    assert torch.isfinite(g).all()
+    assert_close(g.reshape(-1, hd), w.reshape(-1, hd), 2e-2)
+    if hd == 64:                                         # the default entry point routes 64-wide heads to the same kernel
+        got2 = K.prefill_attn(q.to(DEV), kd, vd, start, S, pad.to(DEV))
+        assert torch.equal(got2.cpu()[valid], got.cpu()[valid])
+
+
 def test_flash_prefill_many_ctas_repeated():
     """Thousands of CTAs, two per SM, launched back to back with cold caches: the barrier-phase discipline
     between the softmax warps and the MMA warp must hold when tile loads are slow (a missing guard showed up
