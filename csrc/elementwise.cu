@@ -24,7 +24,8 @@ __global__ void embed_kernel(const int* __restrict__ ids, const uint4* __restric
 // ------------------------------------------------------------------------------------ RMSNorm
 // One CTA per row.  Optional `delta` is added to x first (residual add) and the sum is written to
 // `x_out` (may alias x); `out` receives the normalised row.  Up to MAXC 16-byte chunks per thread
-// stay in registers so the row is read once.
+// stay in registers so the row is read once.  (A warp-per-row form — whole row in one lane set, no barrier — was
+// measured for prefill-sized inputs and lost: 18.4 vs 12.3 us for [2048, 4096], 32.7 vs 14.4 us with the residual add.)
 template <int MAXC>
 __global__ void __launch_bounds__(1024)
 rmsnorm_kernel(const uint4* __restrict__ x, const uint4* __restrict__ delta, const uint4* __restrict__ w,

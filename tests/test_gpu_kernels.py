@@ -54,9 +54,10 @@ def test_embed():
     assert torch.equal(got.cpu(), want)
 
 
-@pytest.mark.parametrize("H", [256, 4096, 5120, 8192])
-def test_rmsnorm(H):
-    x, w, d = rnd(7, H, seed=1), rnd(H, seed=2) * 0.1 + 1, rnd(7, H, seed=3)
+@pytest.mark.parametrize("rows", [7, 300])
+@pytest.mark.parametrize("H", [256, 2048, 4096, 5120, 8192])
+def test_rmsnorm(H, rows):
+    x, w, d = rnd(rows, H, seed=1), rnd(H, seed=2) * 0.1 + 1, rnd(rows, H, seed=3)
     want = ref.rms_norm(x.float(), w.float(), 1e-5)
     got = K.rmsnorm(x.to(DEV), w.to(DEV), 1e-5)
     assert rel_err(got, want) < 1e-2
