@@ -9,7 +9,7 @@ import torch
 from jax_llama_b200.ops import _lib, kernels as K
 
 NAMES = ["entry", "setup done", "producer past wait", "first stage landed", "last MMA issued", "accumulator complete",
-         "partial published", "all splits arrived", "share emitted", "exit", "group 1 summed", "group 1 emitted"]
+         "partial published", "all splits arrived", "share emitted", "exit"]
 dev = torch.device("cuda")
 L = _lib.lib()
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)

@@ -45,6 +45,8 @@ def test_presets_are_valid_and_sized():
         preset(name)
     assert abs(preset("llama2-7b").num_params() / 1e9 - 6.74) < 0.05
     assert abs(preset("llama3-8b").num_params() / 1e9 - 8.03) < 0.05
+    one_b = preset("llama3.2-1b")                      # 64-wide heads, tied embeddings: 1.24 B parameters
+    assert one_b.head_dim == 64 and one_b.tie_word_embeddings and abs(one_b.num_params() / 1e9 - 1.24) < 0.02
     assert abs(preset("llama3-70b").num_params() / 1e9 - 70.55) < 0.3
 
 
