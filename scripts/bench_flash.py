@@ -40,3 +40,20 @@ for (B, S, nh, nkv) in SHAPES:
     flops = 4.0 * B * nh * 128 * (S * (S + 1) / 2)
     print(f"flash B={B} S={S} nh={nh} nkv={nkv}: {ms * 1e3:8.1f} us  {flops / ms / 1e9:7.1f} TFLOP/s (causal)"
           f"  v1={os.environ.get('JLLAMA_FLASH_V1', '0')} psmem={os.environ.get('JLLAMA_FLASH_PSMEM', '0')}")
+    # the warp-level tensor-core kernel (the path of 64-wide heads) on the same shape, and at head_dim 64
+    for hd in (128, 64):
+        q2, k2, v2 = (t[..., :hd].contiguous() for t in (q, kc, vc))
+        for _ in range(2):
+            K.prefill_attn(q2, k2, v2, 0, S, pad, force="mma")
+        ts = []
+        for _ in range(max(ITERS // 2, 3)):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            K.prefill_attn(q2, k2, v2, 0, S, pad, force="mma")
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        ts.sort()
+        ms2 = ts[len(ts) // 2]
+        print(f"   warp-mma head_dim {hd}: {ms2 * 1e3:8.1f} us  {flops * hd / 128 / ms2 / 1e9:7.1f} TFLOP/s")
