@@ -12,7 +12,9 @@
 //             the 16-byte chunks t, t + 4, … of its rows, k-step 2u + v uses words (2v, 2v + 1) of chunk u;
 //   O = P V   the C fragment of S is the A fragment of P; the B operand pairs two keys of one column with PRMT and
 //             output tile (h, e) column n is d = 64 h + 8 n + e.
-// The 4 warps of a CTA take neighbouring row blocks of the same head, so their K / V reads hit L1 / L2.
+// The 4 warps of a CTA take neighbouring row blocks of the same head, so their K / V reads hit L1 / L2.  (Two 16-row
+// tiles per warp sharing the K / V fragments were measured at head_dim 64 and lost — 173 vs 160 us per 2k-token layer:
+// fewer, fatter warps hide the load latency worse.)
 #include "common.cuh"
 #include "jllama_b200.h"
 
