@@ -405,6 +405,10 @@ def main() -> None:
         except OSError:
             pass
         hbm = peaks.get("hbm_gbs", 6650.0)
+        kv_main = 2 * len(eng.layers) * B * eng.nkv * eng.hd * 2 * (P + args.warmup + args.steps // 2)
+        for sw in sweep or []:
+            sw["hbm_roofline_incl_kv_frac"] = round(
+                ((weight_bytes + sw["kv_bytes_per_step_per_rank"]) / (sw["ms_per_step"] / 1e3)) / (hbm * 1e9), 4)
         # prefill roofline: the slower of (FLOPs of this rank at the measured sustained cuBLAS bf16 rate) and (bytes
         # this rank must move over NVLink at the measured 770 GB/s per direction), assuming perfect overlap
         M_tok = B * P
@@ -426,6 +430,8 @@ def main() -> None:
                        "cuda_graph": used_graph},
             "p50_ms_per_token": round(ms_per_step, 4),
             "hbm_roofline_frac_of_measured": round((weight_bytes / (ms_per_step / 1e3)) / (hbm * 1e9), 4),
+            # the same with the K/V cache the step must read (what bounds batched decode; negligible at batch 1 x 2k)
+            "hbm_roofline_incl_kv_frac": round(((weight_bytes + kv_main) / (ms_per_step / 1e3)) / (hbm * 1e9), 4),
             "prefill": {"tokens_per_sec": round(B * P / (prefill_best / 1e3), 1), "ms": round(prefill_best, 3),
                         "prompt_len": P, "includes": "embedding..lm_head(last token) of the prompt",
                         "roofline": prefill_roofline,
