@@ -112,7 +112,55 @@ topk_kernel(const float* __restrict__ logits, int V, int ld, int idx_offset, int
     }
   }
   __syncthreads();
-  int n = count < SURV_CAP ? count : SURV_CAP;
+  if (count > SURV_CAP) {
+    // More survivors than the list holds (thousands of elements tie with or exceed the bound: constant rows, masked
+    // vocabularies, quantised heads): which of them got a slot depended on arrival order.  Exact and deterministic
+    // instead: k rounds of a block-wide arg-max over the row, each restricted to elements that come AFTER the
+    // previously emitted one in the total order (value descending, index ascending).  Rare and slow (k passes).
+    __shared__ float sv[32];
+    __shared__ int si[32];
+    __shared__ float last_v;
+    __shared__ int last_i;
+    if (threadIdx.x == 0) { last_v = INFINITY; last_i = -1; }
+    __syncthreads();
+    for (int r = 0; r < k; ++r) {
+      const float lv = last_v;
+      const int li = last_i;
+      float bv = -INFINITY;
+      int bi = 0x7fffffff;
+      for (int i = threadIdx.x; i < V; i += SM_THREADS) {
+        const float x = row[i];
+        const bool after = x < lv || (x == lv && i > li);
+        if (after && better(x, i, bv, bi)) { bv = x; bi = i; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+      }
+      if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
+      __syncthreads();
+      if (threadIdx.x < 32) {
+        bv = sv[threadIdx.x]; bi = si[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+          const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+          if (better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+        }
+        if (threadIdx.x == 0) {
+          const bool ok = bi != 0x7fffffff && bv > -INFINITY;
+          cand_val[(size_t)blockIdx.x * k + r] = ok ? bv : -INFINITY;
+          cand_idx[(size_t)blockIdx.x * k + r] = ok ? bi + idx_offset : -1;
+          last_v = bv; last_i = ok ? bi : 0x7fffffff;
+        }
+      }
+      __syncthreads();
+    }
+    return;
+  }
+  int n = count;
   int n2 = 1;
   while (n2 < n) n2 <<= 1;
   if (n2 < 2) n2 = 2;

@@ -412,6 +412,32 @@ def test_argmax_and_topk():
     assert (i[:, 40:] == -1).all() and torch.isinf(v[:, 40:]).all()
 
 
+def test_topk_with_thousands_of_ties_is_exact_and_repeatable():
+    """More elements tie with the selection bound than the survivor list holds (constant row; 4096 tied maxima; a
+    plateau below a few distinct maxima): the k largest are still exact, ties go to the lower index, and two runs
+    agree (the survivor list used to keep whichever tied elements arrived first)."""
+    V, k = 128256, 50
+    g = torch.Generator().manual_seed(23)
+    rows = torch.randn(4, V, generator=g)
+    rows[0] = 0.0                                                        # constant row
+    tied = torch.randperm(V, generator=g)[:4096]
+    rows[1, tied] = 9.0                                                  # 4096 tied maxima
+    rows[2] = -1.0
+    rows[2, [5, 70000, 128255]] = torch.tensor([3.0, 2.0, 1.0])          # 3 distinct maxima over a plateau
+    rows[3, :3000] = float("-inf")                                       # ordinary row with a masked prefix
+    d = rows.to(DEV)
+    v1, i1 = K.topk_candidates(d, k)
+    v2, i2 = K.topk_candidates(d, k)
+    assert torch.equal(v1, v2) and torch.equal(i1, i2)
+    v, i = v1.cpu(), i1.cpu().long()
+    assert (v[0] == 0).all() and i[0].tolist() == list(range(k))
+    assert (v[1] == 9).all() and i[1].tolist() == sorted(tied.tolist())[:k]
+    assert v[2, :3].tolist() == [3.0, 2.0, 1.0] and i[2, :3].tolist() == [5, 70000, 128255]
+    assert (v[2, 3:] == -1).all() and i[2, 3:].tolist() == [j for j in range(k) if j != 5][:k - 3]
+    wv, wi = torch.topk(rows[3], k)
+    assert torch.equal(v[3], wv) and torch.equal(i[3], wi)
+
+
 def test_sampling_distribution_and_greedy():
     p = torch.tensor([0.5, 0.25, 0.15, 0.07, 0.03])
     B = 4096
