@@ -163,3 +163,25 @@ def test_reference_arm_runner_with_a_stubbed_reference(tmp_path, monkeypatch):
     assert all(c[2] == 0.0 for c in jax_llama.CALLS if c[0] == "generate")
     for name in [m for m in list(sys.modules) if m == "jax" or m.startswith("jax.") or m == "jax_llama"]:
         sys.modules.pop(name, None)
+
+
+def test_c_api_example_compiles_and_links_against_the_library(tmp_path):
+    """include/jllama_b200.h is plain C99 and examples/c_api_example.c builds against the in-tree shared object (it was
+    run on a B200: 4 launches; here only the compile + link, no GPU needed)."""
+    import shutil
+    import subprocess
+    from jax_llama_b200.ops import build
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cuda = "/usr/local/cuda"
+    if shutil.which("gcc") is None or not os.path.exists(os.path.join(cuda, "include", "cuda_runtime_api.h")):
+        pytest.skip("gcc or the CUDA runtime headers are not available")
+    lib = build.build_library()
+    hdr = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c",
+                          os.path.join(root, "include", "jllama_b200.h")], capture_output=True, text=True)
+    assert hdr.returncode == 0, hdr.stderr
+    exe = tmp_path / "c_api_example"
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", f"-I{root}/include", f"-I{cuda}/include",
+                        os.path.join(root, "examples", "c_api_example.c"), f"-L{os.path.dirname(lib)}", "-ljllama_b200",
+                        f"-L{cuda}/lib64", "-lcudart", "-lm", "-o", str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert exe.exists()
