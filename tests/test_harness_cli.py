@@ -4,6 +4,7 @@ import os
 import subprocess
 import sys
 
+import pytest
 import torch
 
 from jax_llama_b200 import LLaMAConfig
@@ -169,7 +170,6 @@ def test_c_api_example_compiles_and_links_against_the_library(tmp_path):
     """include/jllama_b200.h is plain C99 and examples/c_api_example.c builds against the in-tree shared object (it was
     run on a B200: 4 launches; here only the compile + link, no GPU needed)."""
     import shutil
-    import subprocess
     from jax_llama_b200.ops import build
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     cuda = "/usr/local/cuda"
