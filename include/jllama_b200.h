@@ -63,10 +63,11 @@ int jl_gemm(const void* x, const void* w, const void* residual, void* out, int M
             int out_f32, int num_sms, void* stream);
 /* Optional scratch for jl_gemm on the CURRENT device: with it, small-batch (M <= 128) launches that have fewer
  * 128-row weight tiles than half the SMs (N = 4096: 32 tiles) split K over the idle SMs; partial sums meet in `ws`
- * (fp32, ws_bytes) and the last split of a tile, found with `tickets` (n_tickets ints, zero on entry and between
- * calls), adds them in split order and runs the epilogue — results do not depend on arrival order.  The caller
- * owns both buffers and keeps them alive; ws == NULL unregisters.  Calls that share the scratch must be ordered
- * on one stream. */
+ * (fp32, ws_bytes); once all splits of a tile have arrived (`tickets`: n_tickets ints, zero on entry and between
+ * calls, half of them arrival and half completion counters) each split adds the partials of its share of the tokens
+ * in split order and runs the epilogue — results do not depend on arrival order.  The splits of a tile wait for each
+ * other, so such a launch needs its CTAs resident together (at most one per SM is launched).  The caller owns both
+ * buffers and keeps them alive; ws == NULL unregisters.  Calls that share the scratch must be ordered on one stream. */
 int jl_gemm_set_workspace(void* ws, size_t ws_bytes, int* tickets, int n_tickets);
 /* Timeline hook of the single-CTA GEMM kernel for scripts/gemm_trace.py: [grid][16] u64 device buffer of
  * %globaltimer stamps, NULL = off (default). */
