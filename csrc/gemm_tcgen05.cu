@@ -432,8 +432,9 @@ static int launch_gemm(const void* a, const void* b, const GemmParams& p0, int R
   // memory (10 stages).  Short decode GEMMs (wqkv, wo, w2 at batch 9..128) stay under half of it, so that the CTAs of
   // the NEXT kernel of the chain fit on the same SM and their weight prefetch — issued before they wait for this
   // grid — runs under our epilogue and split-K finish; those prologue / tail latencies were most of a 25 us GEMM.
-  // A split-K launch always takes the small ring: its CTAs wait for each other, so all of them must be resident even
-  // when a second such GEMM runs on another stream (two streams of the pipelined prefill): two per SM always fit.
+  // A split-K launch always takes the small ring: its CTAs wait for each other, so all of them must become resident
+  // even while CTAs of a neighbouring kernel (the previous one draining, the next one prefetching) share the SMs:
+  // two ring-sized CTAs per SM always fit.
   int budget = 200 * 1024;
   if (SWAP && (p.ksplit > 1 || (size_t)Ra * K * 2 / grid <= (size_t)1280 * 1024)) budget = 100 * 1024;
   int stages = (int)(budget / STAGE_BYTES);
